@@ -1,0 +1,225 @@
+// bs_assoc_exact.cu — greedy brute-force association with exact fp64 scores.
+// Reference: AssociateGreedy.associate (F/alg/feature/associate/AssociateGreedy.java:65-118) with
+// ScoreAssociateEuclideanSq_F64 -> DescriptorDistance.euclideanSq (F/alg/descriptor/DescriptorDistance.java:55-64):
+//   score(a,b) = sum_k (a_k-b_k)^2, accumulated sequentially in k from 0, no FMA.
+//   forward : per src row, the LAST dst index attaining the row minimum, accepted iff min <= maxFitError (:76-95)
+//   backward: a match (i,m) survives iff W[i][m] is the strict unique minimum of column m (:98-117)
+// The reference stores the N x M score matrix; here the matrix is never materialised: one tiled kernel computes, for every
+// row of A against all rows of B, (min score, first index, last index attaining it).  Run as (src,dst) it is the forward
+// pass; run as (dst,src) it gives the column minima for the backward test ((a-b)^2 == (b-a)^2 exactly, so both runs see
+// bit-identical scores).
+#include "bs_common.cuh"
+
+#include <cfloat>
+#include <math_constants.h>
+
+namespace bs {
+
+constexpr int AT = 64;            // tile: AT rows of A x AT rows of B
+constexpr int AK = 64;            // k-chunk of B held in shared memory
+constexpr int APAD = AT + 1;      // row stride (doubles) of the [k][row] tiles
+constexpr int ATHREADS = 256;     // 16 x 16 threads, 4 x 4 pairs each
+constexpr int AMAX_DOF = 256;
+
+struct RowBest {
+	double best; int first, last;
+	__device__ __forceinline__ void init() { best = CUDART_INF; first = -1; last = -1; }
+	// scores arrive in ascending j
+	__device__ __forceinline__ void push(double f, int j) {
+		if (f < best || (first < 0 && f <= best)) { best = f; first = j; last = j; }
+		else if (f == best) last = j;
+	}
+	// merge a partial result that covers LARGER indices than this one
+	__device__ __forceinline__ void merge_later(double f, int fi, int la) {
+		if (fi < 0) return;
+		if (first < 0 || f < best) { best = f; first = fi; last = la; }
+		else if (f == best) last = la;
+	}
+};
+
+// partial[(split*nA + row)] over the B rows [split*b_per_split, (split+1)*b_per_split)
+__global__ void __launch_bounds__(ATHREADS)
+rowmin_tile_kernel(const double* __restrict__ A, int nA, const double* __restrict__ B, int nB, int dof, int b_per_split,
+                   double* __restrict__ p_min, int* __restrict__ p_first, int* __restrict__ p_last) {
+	extern __shared__ double sm[];
+	double* sA = sm;                       // [dof][APAD]
+	double* sB = sm + (long)dof * APAD;    // [AK][APAD]
+	const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+	const int row0 = blockIdx.x * AT;
+	const int b_begin = blockIdx.y * b_per_split;
+	const int b_end = min(nB, b_begin + b_per_split);
+
+	// A tile, transposed to [k][row]; rows beyond nA are zero (their results are discarded)
+	for (int idx = tid; idx < AT * dof; idx += ATHREADS) {
+		const int r = idx / dof, k = idx - r * dof;
+		sA[k * APAD + r] = (row0 + r < nA) ? A[(long)(row0 + r) * dof + k] : 0.0;
+	}
+	RowBest best[4];
+#pragma unroll
+	for (int r = 0; r < 4; r++) best[r].init();
+
+	for (int col0 = b_begin; col0 < b_end; col0 += AT) {
+		double acc[4][4];
+#pragma unroll
+		for (int r = 0; r < 4; r++)
+#pragma unroll
+			for (int c = 0; c < 4; c++) acc[r][c] = 0.0;
+		for (int k0 = 0; k0 < dof; k0 += AK) {
+			const int kn = min(AK, dof - k0);
+			__syncthreads();       // previous chunk consumed (and sA visible on the first pass)
+			for (int idx = tid; idx < AT * kn; idx += ATHREADS) {
+				const int c = idx / kn, k = idx - c * kn;
+				sB[k * APAD + c] = (col0 + c < b_end) ? B[(long)(col0 + c) * dof + k0 + k] : 0.0;
+			}
+			__syncthreads();
+			for (int k = 0; k < kn; k++) {
+				double a[4], b[4];
+#pragma unroll
+				for (int r = 0; r < 4; r++) a[r] = sA[(k0 + k) * APAD + ty + 16 * r];
+#pragma unroll
+				for (int c = 0; c < 4; c++) b[c] = sB[k * APAD + tx + 16 * c];
+#pragma unroll
+				for (int r = 0; r < 4; r++)
+#pragma unroll
+					for (int c = 0; c < 4; c++) {
+						const double d = a[r] - b[c];
+						acc[r][c] += d * d;      // -fmad=false: a separate multiply and add, like the Java
+					}
+			}
+		}
+#pragma unroll
+		for (int c = 0; c < 4; c++) {
+			const int j = col0 + tx + 16 * c;
+			if (j < b_end) {
+#pragma unroll
+				for (int r = 0; r < 4; r++) best[r].push(acc[r][c], j);
+			}
+		}
+	}
+	// combine the 16 threads (tx) that share a row.  A thread's columns are tx+16c (+tile): not contiguous across threads,
+	// so merge on (score, index) directly: smaller score wins; equal -> first = min, last = max.
+	__syncthreads();
+	double* r_min = sm;                                  // [AT][16]
+	int* r_first = reinterpret_cast<int*>(sm + AT * 16);
+	int* r_last = r_first + AT * 16;
+#pragma unroll
+	for (int r = 0; r < 4; r++) {
+		const int row = ty + 16 * r;
+		r_min[row * 16 + tx] = best[r].best; r_first[row * 16 + tx] = best[r].first; r_last[row * 16 + tx] = best[r].last;
+	}
+	__syncthreads();
+	if (tid < AT && row0 + tid < nA) {
+		double m = CUDART_INF; int fi = -1, la = -1;
+		for (int t = 0; t < 16; t++) {
+			const double f = r_min[tid * 16 + t];
+			const int a = r_first[tid * 16 + t], b = r_last[tid * 16 + t];
+			if (a < 0) continue;
+			if (fi < 0 || f < m) { m = f; fi = a; la = b; }
+			else if (f == m) { fi = min(fi, a); la = max(la, b); }
+		}
+		const long o = (long)blockIdx.y * nA + row0 + tid;
+		p_min[o] = m; p_first[o] = fi; p_last[o] = la;
+	}
+}
+
+// combine the column splits (ascending index ranges).  mode 0: forward -> pairs/fit (threshold applied);
+// mode 1: column statistics with indices shifted by index_offset (global row numbering of a sharded run)
+__global__ void rowmin_finalize_kernel(const double* __restrict__ p_min, const int* __restrict__ p_first, const int* __restrict__ p_last,
+                                       int nA, int splits, int mode, double max_fit, int index_offset, int32_t* __restrict__ pairs,
+                                       double* __restrict__ fit, double* __restrict__ o_min, int32_t* __restrict__ o_first,
+                                       int32_t* __restrict__ o_last) {
+	const int i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= nA) return;
+	RowBest b; b.init();
+	for (int s = 0; s < splits; s++) {
+		const long o = (long)s * nA + i;
+		b.merge_later(p_min[o], p_first[o], p_last[o]);
+	}
+	if (mode == 0) {
+		// bestScore starts at maxFitError and `fit <= bestScore` replaces it (:80-91)
+		const bool hit = b.first >= 0 && b.best <= max_fit;
+		pairs[i] = hit ? b.last : -1;
+		fit[i] = hit ? b.best : max_fit;
+	} else {
+		o_min[i] = b.best;
+		o_first[i] = b.first < 0 ? -1 : b.first + index_offset;
+		o_last[i] = b.last < 0 ? -1 : b.last + index_offset;
+	}
+}
+
+// :98-117 — forward match (i,m) is kept iff no other row j has W[j][m] <= W[i][m]
+__global__ void validate_kernel(int n, int row_offset, int32_t* __restrict__ pairs, double* __restrict__ fit,
+                                const double* __restrict__ col_min, const int32_t* __restrict__ col_first,
+                                const int32_t* __restrict__ col_last) {
+	const int i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n) return;
+	const int m = pairs[i];
+	if (m < 0) return;
+	const int gi = row_offset + i;
+	const bool unique_min = col_min[m] == fit[i] && col_first[m] == gi && col_last[m] == gi;
+	if (!unique_min) { pairs[i] = -1; fit[i] = DBL_MAX; }
+}
+
+// merge the column partials of `ranks` shards (all-gathered): min score; first = min, last = max over the shards attaining it
+__global__ void merge_columns_kernel(int ranks, int m, const double* __restrict__ a_min, const int32_t* __restrict__ a_first,
+                                     const int32_t* __restrict__ a_last, double* __restrict__ o_min, int32_t* __restrict__ o_first,
+                                     int32_t* __restrict__ o_last) {
+	const int j = blockIdx.x * blockDim.x + threadIdx.x;
+	if (j >= m) return;
+	double best = CUDART_INF; int fi = -1, la = -1;
+	for (int r = 0; r < ranks; r++) {
+		const long o = (long)r * m + j;
+		const int a = a_first[o], b = a_last[o];
+		if (a < 0) continue;
+		const double f = a_min[o];
+		if (fi < 0 || f < best) { best = f; fi = a; la = b; }
+		else if (f == best) { fi = min(fi, a); la = max(la, b); }
+	}
+	o_min[j] = best; o_first[j] = fi; o_last[j] = la;
+}
+
+// ---------------------------------------------------------------- host launchers
+
+int rowmin_splits(int nA, int nB, int sm_count) {
+	const int row_ctas = div_up(nA, AT);
+	int splits = div_up(2 * sm_count, row_ctas > 0 ? row_ctas : 1);
+	const int max_splits = div_up(nB, AT);
+	if (splits > max_splits) splits = max_splits;
+	if (splits < 1) splits = 1;
+	return splits;
+}
+
+void launch_rowmin(const double* A, int nA, const double* B, int nB, int dof, int splits, const RowminScratch& s, cudaStream_t st) {
+	if (dof < 1 || dof > AMAX_DOF) fail(BS_ERR_ARG, "descriptor length must be in [1,256]");
+	int per = div_up(div_up(nB, splits), AT) * AT;
+	if (per < AT) per = AT;
+	const size_t smem = ((size_t)dof * APAD + (size_t)AK * APAD) * sizeof(double);
+	static bool attr_set = false;
+	if (!attr_set) {
+		BS_CUDA(cudaFuncSetAttribute(rowmin_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+		                             (int)(((size_t)AMAX_DOF * APAD + (size_t)AK * APAD) * sizeof(double))));
+		attr_set = true;
+	}
+	BS_LAUNCH(rowmin_tile_kernel, dim3(div_up(nA, AT), splits), ATHREADS, smem, st, A, nA, B, nB, dof, per, s.p_min, s.p_first,
+	          s.p_last);
+}
+
+void launch_rowmin_finalize(const RowminScratch& s, int nA, int splits, int mode, double max_fit, int index_offset, int32_t* pairs,
+                            double* fit, double* o_min, int32_t* o_first, int32_t* o_last, cudaStream_t st) {
+	BS_LAUNCH(rowmin_finalize_kernel, div_up(nA, 256), 256, 0, st, s.p_min, s.p_first, s.p_last, nA, splits, mode, max_fit,
+	          index_offset, pairs, fit, o_min, o_first, o_last);
+}
+
+void launch_validate(int n, int row_offset, int32_t* pairs, double* fit, const double* col_min, const int32_t* col_first,
+                     const int32_t* col_last, cudaStream_t st) {
+	if (n <= 0) return;
+	BS_LAUNCH(validate_kernel, div_up(n, 256), 256, 0, st, n, row_offset, pairs, fit, col_min, col_first, col_last);
+}
+
+void launch_merge_columns(int ranks, int m, const double* a_min, const int32_t* a_first, const int32_t* a_last, double* o_min,
+                          int32_t* o_first, int32_t* o_last, cudaStream_t st) {
+	if (m <= 0) return;
+	BS_LAUNCH(merge_columns_kernel, div_up(m, 256), 256, 0, st, ranks, m, a_min, a_first, a_last, o_min, o_first, o_last);
+}
+
+}  // namespace bs

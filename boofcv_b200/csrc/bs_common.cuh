@@ -1,0 +1,174 @@
+// bs_common.cuh — shared declarations of libboofsurf's CUDA translation units (sm_100a only).
+// All device arithmetic that must match the reference's Java (strict IEEE-754, no FMA contraction, left-to-right) relies
+// on this library being compiled with -fmad=false.
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+#include <cstdio>
+#include <stdexcept>
+#include <string>
+
+#include "../../include/boofsurf.h"
+
+namespace bs {
+
+// ---------------------------------------------------------------- errors
+struct Error : std::runtime_error {
+	int code;
+	Error(int c, const std::string& m) : std::runtime_error(m), code(c) {}
+};
+void set_last_error(const std::string& m);
+[[noreturn]] inline void fail(int code, const std::string& m) { throw Error(code, m); }
+
+#define BS_CUDA(expr)                                                                                         \
+	do {                                                                                                      \
+		cudaError_t _e = (expr);                                                                              \
+		if (_e != cudaSuccess)                                                                                \
+			::bs::fail(BS_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(_e) + " (" + __FILE__ + ":" + \
+			                            std::to_string(__LINE__) + ")");                                      \
+	} while (0)
+
+// every kernel launch goes through this so that bs_launch_count() is an honest count
+void count_launch(int n = 1);
+#define BS_LAUNCH(kernel, grid, block, smem, stream, ...)            \
+	do {                                                             \
+		kernel<<<(grid), (block), (smem), (stream)>>>(__VA_ARGS__);  \
+		::bs::count_launch();                                        \
+		BS_CUDA(cudaGetLastError());                                 \
+	} while (0)
+
+inline int div_up(int a, int b) { return (a + b - 1) / b; }
+inline long div_up_l(long a, long b) { return (a + b - 1) / b; }
+
+// ---------------------------------------------------------------- scale-space plan
+constexpr int MAX_OCTAVES = 8;
+constexpr int MAX_SCALES = 8;
+constexpr int MAX_LAYERS = MAX_OCTAVES * MAX_SCALES;
+constexpr int MAX_LEVELS = MAX_OCTAVES * (MAX_SCALES - 2);
+
+// One box-filter layer of the Fast-Hessian scale space (one `size` at one `skip`).
+// Geometry per DerivativeIntegralImage.kernelDerivXX/YY/XY (IP/alg/transform/ii/DerivativeIntegralImage.java:102-158).
+struct Layer {
+	int size, skip;
+	int w, h;             // intensity dimensions = W/skip, H/skip
+	long offset;          // float offset of this layer inside one frame's intensity block
+	int r1, r2, r3;       // XX/YY block radii: r1 = (size/3)/2, r2 = size/3 + r1, r3 = (size - size/3 - 1)/2
+	int b;                // XY block = size/3
+	float norm;           // 1f/(size*size)
+	int octave, index;    // index inside the octave
+};
+
+// One detection level: NMS on `mid`, 3x3 checks in `lower`/`upper`
+// (FastHessianFeatureDetector.findLocalScaleSpaceMax, F/alg/feature/detect/interest/FastHessianFeatureDetector.java:230-298)
+struct Level {
+	int lower, mid, upper;     // layer ids
+	int octave, level;         // level = index of mid inside the octave
+	int border;                // ignoreBorder = size[level]/(2*skip)
+	int nbx, nby;              // NMS blocks of (radius+1)^2 starting at `border`
+	int cta_begin;             // first CTA (of NMS_CTA_BLOCKS blocks each) of this level inside a frame
+	int level_size, level_step;  // sizes[level], sizes[level]-sizes[level-1]
+};
+
+struct Plan {
+	int W, H;
+	int n_layers, n_levels;
+	int radius;                // extractRadius
+	float threshold;           // detectThreshold
+	int max_per_level;         // maxFeaturesPerScale (<=0: off)
+	long inten_per_frame;      // floats
+	int ctas_per_frame;        // NMS CTAs per frame
+	Layer layers[MAX_LAYERS];
+	Level levels[MAX_LEVELS];
+};
+constexpr int NMS_CTA_BLOCKS = 256;   // NMS blocks (=threads) per CTA; also the staging slots per CTA
+
+Plan make_plan(const bs_fh_cfg& cfg, int W, int H);
+void check_fh_cfg(const bs_fh_cfg& c);
+void check_ori_cfg(const bs_ori_cfg& c);
+void check_desc_cfg(const bs_desc_cfg& c);
+
+// Detected point as it leaves the detector kernel (ScalePoint + provenance, F/struct/feature/ScalePoint.java:28-34)
+struct alignas(8) RawPoint {
+	double x, y, scale;
+	float response;
+	int16_t px, py;
+	int16_t octave, level;
+	int32_t pad;
+};
+
+// ---------------------------------------------------------------- weight tables (host, double precision)
+// FactoryKernelGaussian / KernelMath, see bs_plan.cu
+void gaussian2d_odd(double sigma, int radius, double* out);          // (2r+1)^2, sum-normalised
+void gaussian_width_table(double sigma, int width, double* out);     // width^2, sum-normalised
+
+// ---------------------------------------------------------------- describe parameters (device constant block)
+constexpr int MAX_ORI_W = 33;     // orientation sample grid up to 33x33 (radius <= 16)
+constexpr int MAX_DESC_GRID = 32; // descriptor sample grid up to 32x32
+
+struct DescribeParams {
+	// orientation
+	int ori_variant, ori_radius, ori_sample_width;
+	double ori_radius_to_scale, ori_period, ori_window;
+	int ori_weighted;
+	// descriptor
+	int variant, grid, sub, sample_width, overlap, dof;
+	int radius_descriptor;
+};
+
+// ---------------------------------------------------------------- stage launchers (implemented in the .cu files)
+template <typename TI, typename TO>
+void launch_integral(const TI* d_in, long in_frame_stride, int in_stride, TO* d_out, int W, int H, int batch, cudaStream_t st);
+
+template <typename T>
+void launch_hessian_plan(const T* d_ii, const Plan& plan, const Plan* d_plan, float* d_inten, int batch, cudaStream_t st);
+template <typename T>
+void launch_hessian_single(const T* d_ii, int W, int H, int skip, int size, float* d_out, cudaStream_t st);
+
+// Feature pool of one detect call (structure of arrays, capacity `cap` features)
+struct Pool {
+	double* xy;        // [cap][2]   ScalePoint.x, .y
+	double* scale;     // [cap]      ScalePoint.scale
+	int32_t* meta;     // [cap][4]   octave, level, px, py
+	float* response;   // [cap]
+	int32_t* frame;    // [cap]      frame index inside the batch
+	double* angle;     // [cap]
+	double* desc;      // [cap][dof]
+	uint8_t* white;    // [cap]
+	long cap;
+};
+
+void launch_nms(const Plan& plan, const Plan* d_plan, const float* d_inten, int batch, RawPoint* d_stage, int* d_cta_counts,
+                cudaStream_t st);
+// Exclusive scan of the per-CTA counts of the chunk's frames (frame0 .. frame0+batch), continuing from
+// d_frame_offset[frame0]; writes d_frame_offset[frame0+1 .. frame0+batch] and the per-CTA pool offsets, then gathers the
+// staged points into the pool in (frame, octave, level, block-row, block-column) order.
+void launch_compact(const Plan& plan, int batch, int frame0, const RawPoint* d_stage, const int* d_cta_counts, int* d_cta_offsets,
+                    int* d_frame_offset, const Pool& pool, cudaStream_t st);
+
+struct DescribeTables {
+	const double* d_ori_w;     // (2r+1)^2 or null
+	const double* d_w;         // fast: (grid*sub)^2 ; mod: weight_sub (sub+2*overlap)^2
+	const double* d_wgrid;     // mod: grid^2
+};
+// Orientation + descriptor for pool entries [*d_begin, *d_end) (device-side range, persistent warps loop over it).
+// ii of frame f is at d_ii + (f - frame0) * W * H.  !do_orientation: use the angles already in pool.angle.
+template <typename T>
+void launch_describe(const T* d_ii, int W, int H, const DescribeParams& p, const DescribeTables& t, const Pool& pool,
+                     const int* d_begin, const int* d_end, int frame0, bool do_orientation, bool do_describe, cudaStream_t st);
+
+// ---------------------------------------------------------------- exact association (bs_assoc_exact.cu)
+struct RowminScratch { double* p_min; int* p_first; int* p_last; long cap; };
+int rowmin_splits(int nA, int nB, int sm_count);
+void launch_rowmin(const double* A, int nA, const double* B, int nB, int dof, int splits, const RowminScratch& s, cudaStream_t st);
+void launch_rowmin_finalize(const RowminScratch& s, int nA, int splits, int mode, double max_fit, int index_offset, int32_t* pairs,
+                            double* fit, double* o_min, int32_t* o_first, int32_t* o_last, cudaStream_t st);
+void launch_validate(int n, int row_offset, int32_t* pairs, double* fit, const double* col_min, const int32_t* col_first,
+                     const int32_t* col_last, cudaStream_t st);
+void launch_merge_columns(int ranks, int m, const double* a_min, const int32_t* a_first, const int32_t* a_last, double* o_min,
+                          int32_t* o_first, int32_t* o_last, cudaStream_t st);
+
+const char* last_error_cstr();
+long launch_count();
+Layer make_layer(int size, int skip, int W, int H);
+
+}  // namespace bs

@@ -1,0 +1,193 @@
+// bs_detect.cu — non-maximum suppression, scale-space maximum test, sub-pixel refinement and ordered compaction.
+// Reference:
+//   NonMaxBlock.process (F/alg/feature/detect/extract/NonMaxBlock.java:69-94) with
+//   NonMaxBlockSearchStrict.Max.searchBlock / checkLocalMax (…/NonMaxBlockSearchStrict.java:56-79,196-221);
+//   FastHessianFeatureDetector.findLocalScaleSpaceMax / checkMax / polyPeak
+//   (F/alg/feature/detect/interest/FastHessianFeatureDetector.java:230-298,304-313,336-350).
+//
+// One thread owns one (radius+1)^2 NMS block — the reference emits at most one point per block, in block-raster order
+// per level, levels in (octave, level) order.  A CTA owns NMS_CTA_BLOCKS consecutive blocks of one level, so CTA order ==
+// emission order; points are staged per CTA (rank = prefix count inside the CTA) and a scan over the CTA counts gives every
+// point its slot in the reference's single-thread order.  No atomics, no sort: the output order is deterministic.
+#include "bs_common.cuh"
+
+#include <cfloat>
+
+namespace bs {
+
+// polyPeak(float,float,float) :336-350
+__device__ __forceinline__ float poly_peak(float lower, float middle, float upper) {
+	const float a = 0.5f * lower - middle + 0.5f * upper;
+	const float b = 0.5f * upper - 0.5f * lower;
+	if (a == 0.0f) return 0.0f;
+	return -b / (2.0f * a);
+}
+
+// checkMax :304-313 on an ImageBorderValue(0) view: out-of-image reads are 0
+__device__ __forceinline__ bool scale_neighbour_ok(const float* __restrict__ img, int w, int h, float best, int cx, int cy) {
+	for (int y = cy - 1; y <= cy + 1; y++)
+		for (int x = cx - 1; x <= cx + 1; x++) {
+			const float v = (x >= 0 && y >= 0 && x < w && y < h) ? __ldg(img + (long)y * w + x) : 0.0f;
+			if (v >= best) return false;
+		}
+	return true;
+}
+
+__global__ void __launch_bounds__(NMS_CTA_BLOCKS)
+nms_kernel(const Plan* __restrict__ plan, const float* __restrict__ inten_all, RawPoint* __restrict__ stage_all,
+           int* __restrict__ counts_all) {
+	__shared__ int warp_counts[NMS_CTA_BLOCKS / 32];
+	const int cta = blockIdx.x, frame = blockIdx.y;
+	int lv = 0;
+	while (lv + 1 < plan->n_levels && cta >= plan->levels[lv + 1].cta_begin) lv++;
+	const Level& V = plan->levels[lv];
+	const Layer& M = plan->layers[V.mid];
+	const int w = M.w, h = M.h;
+	const float* inten = inten_all + (long)frame * plan->inten_per_frame;
+	const float* mid = inten + M.offset;
+	const int radius = plan->radius, step = radius + 1;
+	const int bid = (cta - V.cta_begin) * NMS_CTA_BLOCKS + threadIdx.x;
+
+	bool found = false;
+	RawPoint pt;
+	if (bid < V.nbx * V.nby) {
+		const int by = bid / V.nbx, bx = bid - by * V.nbx;
+		const int endX = w - V.border, endY = h - V.border;
+		const int x0 = V.border + bx * step, y0 = V.border + by * step;
+		const int x1 = min(x0 + step, endX), y1 = min(y0 + step, endY);
+		// searchBlock: first strict maximum in raster order
+		int peakX = 0, peakY = 0;
+		float peak = -FLT_MAX;
+		for (int y = y0; y < y1; y++)
+			for (int x = x0; x < x1; x++) {
+				const float v = __ldg(mid + (long)y * w + x);
+				if (v > peak) { peak = v; peakX = x; peakY = y; }
+			}
+		bool ok = peak >= plan->threshold && peak != FLT_MAX;
+		if (ok) {
+			// checkLocalMax: strictly greater than everything else in the (2r+1)^2 window clamped to the image
+			const int wx0 = max(peakX - radius, 0), wx1 = min(peakX + radius, w - 1);
+			const int wy0 = max(peakY - radius, 0), wy1 = min(peakY + radius, h - 1);
+			for (int y = wy0; y <= wy1 && ok; y++)
+				for (int x = wx0; x <= wx1; x++) {
+					const float v = __ldg(mid + (long)y * w + x);
+					if (v >= peak && !(x == peakX && y == peakY)) { ok = false; break; }
+				}
+		}
+		if (ok) {
+			// findLocalScaleSpaceMax :248-294
+			const int ir = V.border + radius;
+			if (peakX < ir || peakX >= w - ir || peakY < ir || peakY >= h - ir) ok = false;
+		}
+		if (ok) {
+			const float* lower = inten + plan->layers[V.lower].offset;
+			const float* upper = inten + plan->layers[V.upper].offset;
+			const float val = __ldg(mid + (long)peakY * w + peakX);
+			if (scale_neighbour_ok(lower, w, h, val, peakX, peakY) && scale_neighbour_ok(upper, w, h, val, peakX, peakY)) {
+				const long c = (long)peakY * w + peakX;
+				const float peakXf = poly_peak(__ldg(mid + c - 1), val, __ldg(mid + c + 1));
+				const float peakYf = poly_peak(__ldg(mid + c - w), val, __ldg(mid + c + w));
+				const float peakS = poly_peak(__ldg(lower + c), val, __ldg(upper + c));
+				const float interpX = ((float)peakX + peakXf) * (float)M.skip;
+				const float interpY = ((float)peakY + peakYf) * (float)M.skip;
+				const float interpS = (float)V.level_size + peakS * (float)V.level_step;
+				pt.x = (double)interpX; pt.y = (double)interpY;
+				pt.scale = 1.2 * (double)interpS / 9.0;
+				pt.response = val;
+				pt.px = (int16_t)peakX; pt.py = (int16_t)peakY;
+				pt.octave = (int16_t)V.octave; pt.level = (int16_t)V.level;
+				pt.pad = 0;
+				found = true;
+			}
+		}
+	}
+	// rank inside the CTA in thread (= block-raster) order
+	const unsigned ballot = __ballot_sync(0xffffffffu, found);
+	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+	if (lane == 0) warp_counts[warp] = __popc(ballot);
+	__syncthreads();
+	int base = 0, total = 0;
+	for (int k = 0; k < NMS_CTA_BLOCKS / 32; k++) {
+		const int c = warp_counts[k];
+		if (k < warp) base += c;
+		total += c;
+	}
+	const long slot0 = ((long)frame * plan->ctas_per_frame + cta) * NMS_CTA_BLOCKS;
+	if (found) stage_all[slot0 + base + __popc(ballot & ((1u << lane) - 1u))] = pt;
+	if (threadIdx.x == 0) counts_all[(long)frame * plan->ctas_per_frame + cta] = total;
+}
+
+void launch_nms(const Plan& plan, const Plan* d_plan, const float* d_inten, int batch, RawPoint* d_stage, int* d_cta_counts,
+                cudaStream_t st) {
+	if (plan.ctas_per_frame == 0 || batch <= 0) return;
+	BS_LAUNCH(nms_kernel, dim3(plan.ctas_per_frame, batch), NMS_CTA_BLOCKS, 0, st, d_plan, d_inten, d_stage, d_cta_counts);
+}
+
+// ---------------------------------------------------------------- ordered compaction
+constexpr int SCAN_THREADS = 1024;
+
+// one CTA: running exclusive scan over [batch][ctas] counts
+__global__ void __launch_bounds__(SCAN_THREADS)
+scan_counts_kernel(const int* __restrict__ counts, int ctas, int batch, int frame0, int* __restrict__ offsets,
+                   int* __restrict__ frame_offset) {
+	__shared__ int warp_sums[SCAN_THREADS / 32];
+	__shared__ int carry;
+	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+	if (threadIdx.x == 0) carry = frame_offset[frame0];
+	__syncthreads();
+	for (int f = 0; f < batch; f++) {
+		for (int c0 = 0; c0 < ctas; c0 += SCAN_THREADS) {
+			const int c = c0 + threadIdx.x;
+			const int v = c < ctas ? counts[(long)f * ctas + c] : 0;
+			int incl = v;
+#pragma unroll
+			for (int d = 1; d < 32; d <<= 1) {
+				const int t = __shfl_up_sync(0xffffffffu, incl, d);
+				if (lane >= d) incl += t;
+			}
+			if (lane == 31) warp_sums[warp] = incl;
+			__syncthreads();
+			int wbase = 0, chunk_total = 0;
+			for (int k = 0; k < SCAN_THREADS / 32; k++) {
+				const int s = warp_sums[k];
+				if (k < warp) wbase += s;
+				chunk_total += s;
+			}
+			const int base = carry;
+			if (c < ctas) offsets[(long)f * ctas + c] = base + wbase + incl - v;
+			__syncthreads();
+			if (threadIdx.x == 0) carry = base + chunk_total;
+			__syncthreads();
+		}
+		if (threadIdx.x == 0) frame_offset[frame0 + f + 1] = carry;
+		__syncthreads();
+	}
+}
+
+__global__ void __launch_bounds__(NMS_CTA_BLOCKS)
+gather_points_kernel(const RawPoint* __restrict__ stage, const int* __restrict__ counts, const int* __restrict__ offsets,
+                     int ctas, int frame0, Pool pool) {
+	const long idx = (long)blockIdx.y * ctas + blockIdx.x;
+	const int n = counts[idx];
+	if ((int)threadIdx.x >= n) return;
+	const long dst = (long)offsets[idx] + threadIdx.x;
+	if (dst >= pool.cap) return;      // counted, not stored: the host reports BS_ERR_CAPACITY
+	const RawPoint p = stage[idx * NMS_CTA_BLOCKS + threadIdx.x];
+	pool.xy[2 * dst] = p.x; pool.xy[2 * dst + 1] = p.y;
+	pool.scale[dst] = p.scale;
+	pool.meta[4 * dst] = p.octave; pool.meta[4 * dst + 1] = p.level; pool.meta[4 * dst + 2] = p.px; pool.meta[4 * dst + 3] = p.py;
+	pool.response[dst] = p.response;
+	pool.frame[dst] = frame0 + blockIdx.y;
+}
+
+void launch_compact(const Plan& plan, int batch, int frame0, const RawPoint* d_stage, const int* d_cta_counts, int* d_cta_offsets,
+                    int* d_frame_offset, const Pool& pool, cudaStream_t st) {
+	if (batch <= 0) return;
+	BS_LAUNCH(scan_counts_kernel, 1, SCAN_THREADS, 0, st, d_cta_counts, plan.ctas_per_frame, batch, frame0, d_cta_offsets,
+	          d_frame_offset);
+	if (plan.ctas_per_frame == 0) return;
+	BS_LAUNCH(gather_points_kernel, dim3(plan.ctas_per_frame, batch), NMS_CTA_BLOCKS, 0, st, d_stage, d_cta_counts, d_cta_offsets,
+	          plan.ctas_per_frame, frame0, pool);
+}
+
+}  // namespace bs

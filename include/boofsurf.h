@@ -1,0 +1,227 @@
+/*
+ * boofsurf.h — C ABI of libboofsurf.so: BoofCV's SURF detect/describe/associate path on one B200 (sm_100a).
+ *
+ * This is the drop-in boundary.  Every entry point names the reference interface it replaces; paths are
+ * relative to the reference tree:
+ *   F  = main/boofcv-feature/src/main/java/boofcv        IP = main/boofcv-ip/src/main/java/boofcv
+ * A JNI / Panama binding for the two Java interfaces is shown in INTEGRATION.md.
+ *
+ * Conventions
+ *   - plain C, opaque handles, int status (BS_OK = 0).  No exception crosses the boundary; bs_last_error() returns the
+ *     message of the last failure on the calling thread.
+ *   - caller owns every input/output array.  The library owns device workspaces inside a handle and frees them in
+ *     *_destroy.  Calls on ONE handle must be serialised by the caller (the Java objects are not thread safe either,
+ *     F/abst/feature/detdesc/DetectDescribePoint.java:38-40); different handles are independent.
+ *   - pointers named d_* are DEVICE pointers on the handle's device; all others are host pointers.
+ *   - `stream` arguments are cudaStream_t passed as void* (NULL = the handle's own stream).
+ *   - there is no CPU fallback: without a CUDA device every *_create fails with BS_ERR_CUDA.
+ */
+#ifndef BOOFSURF_H
+#define BOOFSURF_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define BS_OK 0
+#define BS_ERR_ARG 1      /* IllegalArgumentException on the Java side */
+#define BS_ERR_CUDA 2     /* CUDA runtime failure (message has the cudaError string) */
+#define BS_ERR_CAPACITY 3 /* an output pool was too small; counts are still valid, see bs_surf_total */
+#define BS_ERR_STATE 4    /* e.g. associate() before setSource/setDestination */
+
+/* pixel types accepted by detect (GIntegralImageOps.getIntegralType, IP/alg/transform/ii/GIntegralImageOps.java:35-46) */
+#define BS_PIXEL_F32 0 /* GrayF32 -> GrayF32 integral */
+#define BS_PIXEL_U8 1  /* GrayU8  -> GrayS32 integral */
+#define BS_PIXEL_S32 2 /* GrayS32 -> GrayS32 integral */
+
+/* ConfigFastHessian (F/abst/feature/detect/interest/ConfigFastHessian.java:33-70) */
+typedef struct bs_fh_cfg {
+	float detect_threshold;     /* detectThreshold = 1 */
+	int extract_radius;         /* extractRadius = 2 */
+	int max_features_per_scale; /* maxFeaturesPerScale = -1 */
+	int initial_sample_size;    /* initialSampleSize = 1 */
+	int initial_size;           /* initialSize = 9 */
+	int scales_per_octave;      /* numberScalesPerOctave = 4 */
+	int octaves;                /* numberOfOctaves = 4 */
+	int scale_step_size;        /* scaleStepSize = 6 */
+} bs_fh_cfg;
+
+/* ConfigAverageIntegral / ConfigSlidingIntegral (F/abst/feature/orientation/ConfigAverageIntegral.java:34-51,
+ * ConfigSlidingIntegral.java:34-54) */
+typedef struct bs_ori_cfg {
+	int variant;                   /* 0 = average gradient (surfFast), 1 = sliding window (surfStable) */
+	double object_radius_to_scale; /* objectRadiusToScale = 1/2 */
+	int radius;                    /* 6 (average) / 8 (sliding) */
+	double sample_period;          /* samplePeriod = 1 / 0.65 */
+	int sample_width;              /* sampleWidth = 6 */
+	double weight_sigma;           /* weightSigma = -1 (derive from radius); 0 = unweighted */
+	double window_size;            /* windowSize = PI/3 (sliding only) */
+} bs_ori_cfg;
+
+/* ConfigSurfDescribe.Speed / .Stability (F/abst/feature/describe/ConfigSurfDescribe.java:34-79) */
+typedef struct bs_desc_cfg {
+	int variant;             /* 0 = DescribePointSurf (Speed), 1 = DescribePointSurfMod (Stability) */
+	int width_large_grid;    /* widthLargeGrid = 4 */
+	int width_sub_region;    /* widthSubRegion = 5 */
+	int width_sample;        /* widthSample = 3 */
+	int use_haar;            /* useHaar = false; true is rejected with BS_ERR_ARG (not on the north-star path) */
+	double weight_sigma;     /* Speed.weightSigma = 4.5 */
+	int overlap;             /* Stability.overLap = 2 */
+	double sigma_large_grid; /* Stability.sigmaLargeGrid = 2.5 */
+	double sigma_sub_region; /* Stability.sigmaSubRegion = 2.5 */
+} bs_desc_cfg;
+
+/* defaults == passing null configs to FactoryDetectDescribe.surfFast / surfStable */
+void bs_fh_cfg_default(bs_fh_cfg* c);
+void bs_ori_cfg_default(bs_ori_cfg* c, int variant);
+void bs_desc_cfg_default(bs_desc_cfg* c, int variant);
+
+const char* bs_last_error(void);
+const char* bs_version(void);
+int bs_device_count(int* n);
+
+/* ------------------------------------------------------------------------------------------------------------------
+ * DetectDescribePoint<T,BrightFeature>: FactoryDetectDescribe.surfFast / surfStable
+ * (F/factory/feature/detdesc/FactoryDetectDescribe.java:118-135, 209-226) -> WrapDetectDescribeSurf
+ * (F/abst/feature/detdesc/WrapDetectDescribeSurf.java:75-141).
+ * ------------------------------------------------------------------------------------------------------------------ */
+typedef struct bs_surf bs_surf;
+
+/* Constructor.  Validates the configs the way Configuration.checkValidity does (BS_ERR_ARG). */
+int bs_surf_create(int device, const bs_fh_cfg* fh, const bs_ori_cfg* ori, const bs_desc_cfg* desc, int pixel_type,
+                   bs_surf** out);
+int bs_surf_destroy(bs_surf* s);
+
+/* Workspace tuning (optional, before the first detect).  chunk_frames = frames processed per kernel wave (bounds the
+ * intensity workspace: 4*sum(layers) bytes per frame); pool_features = capacity of the feature pool of one detect call
+ * (0 = batch * width*height/64). */
+int bs_surf_set_workspace(bs_surf* s, int chunk_frames, long pool_features);
+
+/* WrapDetectDescribeSurf.detect(T input) :75-96.  HOST image with BoofCV's {data,startIndex,stride,width,height}
+ * (sub-images legal, main/boofcv-types/src/main/java/boofcv/struct/image/ImageBase.java:34-52).  Copies the pixels in,
+ * runs the whole pipeline, returns when the results are readable.  Replaces any previous result. */
+int bs_surf_detect(bs_surf* s, const void* pixels, int start_index, int stride, int width, int height);
+
+/* Same pipeline on a DEVICE-resident batch: frame f starts at d_pixels + f*frame_stride (elements), rows `stride`
+ * elements apart.  Asynchronous on `stream`; the first accessor call synchronises. */
+int bs_surf_detect_device(bs_surf* s, const void* d_pixels, long frame_stride, int stride, int width, int height,
+                          int batch, void* stream);
+
+/* getNumberOfFeatures() :112-114 for one frame of the last detect; bs_surf_total = sum over frames (and the number the
+ * pool would have needed when BS_ERR_CAPACITY was returned). */
+int bs_surf_count(bs_surf* s, int frame, int* n);
+int bs_surf_total(bs_surf* s, long* n);
+
+/* getLocation/getRadius/getOrientation/getDescription :116-141 for all features of `frame`, in the reference's
+ * single-thread emission order.  Any output pointer may be NULL.  radius = scale*BoofDefaults.SURF_SCALE_TO_RADIUS (=2).
+ *   xy[2n] scale[n] angle[n] desc[dof*n] white[n]; dof = bs_surf_dof().
+ *   meta[4n] = {octave, level, px, py} of the detection (for parity tests), response[n] = Fast-Hessian value. */
+int bs_surf_read(bs_surf* s, int frame, double* xy, double* scale, double* angle, double* desc, uint8_t* white,
+                 int32_t* meta, float* response);
+int bs_surf_dof(const bs_surf* s); /* DescriptorInfo.createDescription().size() */
+
+/* Device views of the last result (valid until the next detect on this handle): feature i of frame f is at pool index
+ * frame_offset[f] + i.  d_desc is [total][dof] doubles — feed it to bs_assoc_run_device without leaving the GPU. */
+typedef struct bs_surf_device_view {
+	const double* d_xy;      /* [total][2] */
+	const double* d_scale;   /* [total] */
+	const double* d_angle;   /* [total] */
+	const double* d_desc;    /* [total][dof] */
+	const uint8_t* d_white;  /* [total] */
+	const int32_t* d_frame_offset; /* [batch+1] exclusive prefix of per-frame counts */
+	long total;
+	int batch;
+	int dof;
+} bs_surf_device_view;
+int bs_surf_view(bs_surf* s, bs_surf_device_view* v);
+
+/* ------------------------------------------------------------------------------------------------------------------
+ * Stage-level entry points (parity tests call these; each runs exactly the kernel the full pipeline uses).
+ * Host pointers in, host pointers out.
+ * ------------------------------------------------------------------------------------------------------------------ */
+/* GIntegralImageOps.transform, IP/alg/transform/ii/GIntegralImageOps.java:56-70 -> ImplIntegralImageOps.transform
+ * (IP/alg/transform/ii/impl/ImplIntegralImageOps.java:42-66 F32, :94-118 U8->S32, :120-144 S32).  out is dense
+ * width*height (float for F32, int32 otherwise).  in_stride in elements. */
+int bs_integral(int device, int pixel_type, const void* in, int in_stride, int width, int height, void* out);
+
+/* IntegralImageFeatureIntensity.hessian (F/alg/feature/detect/intensity/IntegralImageFeatureIntensity.java:43-79).
+ * ii dense width*height of integral type (ii_type: BS_PIXEL_F32 -> float, else int32); out dense (w/skip)*(h/skip). */
+int bs_hessian(int device, int ii_type, const void* ii, int width, int height, int skip, int size, float* out);
+
+/* FastHessianFeatureDetector.detect on a given integral image
+ * (F/alg/feature/detect/interest/FastHessianFeatureDetector.java:156-188).  Returns the number found in *n and fills
+ * up to max_out entries: xys[3k] = {x, y, scale}, meta[4k] = {octave, level, px, py}, response[k]. */
+int bs_fh_detect(int device, int ii_type, const void* ii, int width, int height, const bs_fh_cfg* cfg, int max_out,
+                 int* n, double* xys, int32_t* meta, float* response);
+
+/* OrientationIntegral.compute after setObjectRadius(2*scale) (WrapDetectDescribeSurf.java:98-110;
+ * F/alg/feature/orientation/impl/ImplOrientationAverageGradientIntegral.java:54-127,
+ * ImplOrientationSlidingWindowIntegral.java:81-188).  xys[3n] = {x, y, scale}. */
+int bs_orientation(int device, int ii_type, const void* ii, int width, int height, const bs_ori_cfg* cfg,
+                   const double* xys, int n, double* angle);
+
+/* DescribePointSurf(.Mod).describe (F/alg/feature/describe/DescribePointSurf.java:169-213,
+ * DescribePointSurfMod.java:121-192).  desc[dof*n], white[n]. */
+int bs_describe(int device, int ii_type, const void* ii, int width, int height, const bs_desc_cfg* cfg,
+                const double* xys, const double* angle, int n, double* desc, uint8_t* white);
+
+/* ------------------------------------------------------------------------------------------------------------------
+ * AssociateDescription<BrightFeature>: FactoryAssociation.greedy(ScoreAssociateEuclideanSq_F64, maxError, backwards)
+ * (F/factory/feature/associate/FactoryAssociation.java:51-65) -> WrapAssociateGreedy
+ * (F/abst/feature/associate/WrapAssociateGreedy.java:58-123) -> AssociateGreedy.associate
+ * (F/alg/feature/associate/AssociateGreedy.java:65-118) with DescriptorDistance.euclideanSq
+ * (F/alg/descriptor/DescriptorDistance.java:55-64).
+ * ------------------------------------------------------------------------------------------------------------------ */
+typedef struct bs_assoc bs_assoc;
+
+int bs_assoc_create(int device, double max_fit_error, int backwards_validation, bs_assoc** out);
+int bs_assoc_destroy(bs_assoc* a);
+int bs_assoc_set_max_fit_error(bs_assoc* a, double max_fit_error); /* Associate.setMaxScoreThreshold */
+
+/* Filter mode: 0 = exact fp64 distances for every pair; 1 = tensor-core candidate filter (tcgen05 bf16 hi/lo split)
+ * followed by an exact fp64 re-score of the candidates (same pairs/fit, much faster for large N*M).  Default = auto:
+ * mode 1 when n*m >= 2^22 and dof is a multiple of 16, else mode 0. */
+int bs_assoc_set_mode(bs_assoc* a, int mode);
+
+/* AssociateGreedy.associate: src[n][dof], dst[m][dof] row-major doubles (the TupleDesc_F64.value arrays back to back).
+ * pairs[n] = index into dst or -1 (AssociateGreedyBase.getPairs), fit[n] = score of the match
+ * (getFitQuality; Double.MAX_VALUE where backward validation rejected, the running best otherwise). */
+int bs_assoc_run(bs_assoc* a, const double* src, int n, const double* dst, int m, int dof, int32_t* pairs,
+                 double* fit);
+/* Same on device pointers, asynchronous on `stream`; d_pairs/d_fit are device arrays. */
+int bs_assoc_run_device(bs_assoc* a, const double* d_src, int n, const double* d_dst, int m, int dof,
+                        int32_t* d_pairs, double* d_fit, void* stream);
+
+/* Sharded association: the src rows of one rank against ALL dst rows.
+ * Step 1 (bs_assoc_forward_device): forward pass for the local rows + per-column partial minima over the local rows:
+ *   d_col_min[m] (score), d_col_first[m], d_col_last[m] (GLOBAL row index = row_offset + local row; -1 if none).
+ * The caller combines the partials of all ranks (min of col_min; first = min / last = max over the ranks attaining it)
+ * with NCCL all-gather + bs_assoc_merge_columns_device, then
+ * Step 2 (bs_assoc_validate_device): applies AssociateGreedy.java:98-117 to the local rows. */
+int bs_assoc_forward_device(bs_assoc* a, const double* d_src, int n, int row_offset, const double* d_dst, int m,
+                            int dof, int32_t* d_pairs, double* d_fit, double* d_col_min, int32_t* d_col_first,
+                            int32_t* d_col_last, void* stream);
+int bs_assoc_merge_columns_device(bs_assoc* a, int ranks, int m, const double* d_all_min, const int32_t* d_all_first,
+                                  const int32_t* d_all_last, double* d_col_min, int32_t* d_col_first,
+                                  int32_t* d_col_last, void* stream);
+int bs_assoc_validate_device(bs_assoc* a, int n, int row_offset, int32_t* d_pairs, double* d_fit,
+                             const double* d_col_min, const int32_t* d_col_first, const int32_t* d_col_last,
+                             void* stream);
+
+/* WrapAssociateGreedy.associate :85-92 + FindUnassociated.checkDestination
+ * (F/alg/feature/associate/FindUnassociated.java:56-72): turn pairs/fit into the match list (ascending src) and the two
+ * unassociated index lists.  Host-side helper (pure index bookkeeping).  Outputs sized n, n, n, n, m; counts returned. */
+int bs_assoc_matches(const int32_t* pairs, const double* fit, int n, int m, int32_t* match_src, int32_t* match_dst,
+                     double* match_score, int* n_matches, int32_t* unassoc_src, int* n_unassoc_src,
+                     int32_t* unassoc_dst, int* n_unassoc_dst);
+
+/* kernel launch counter (all kernels this library launched on the calling process since load) — bench.py's
+ * gpu_launches */
+long bs_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* BOOFSURF_H */
