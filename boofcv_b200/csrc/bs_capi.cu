@@ -7,6 +7,7 @@
 #include <cfloat>
 #include <cmath>
 #include <cstring>
+#include <memory>
 #include <vector>
 
 using namespace bs;
@@ -177,7 +178,6 @@ void bs_surf::ensure(int w, int h, int nbatch) {
 void bs_surf::run(const void* d_pixels, long frame_stride, int stride, int w, int h, int nbatch, cudaStream_t st) {
 	if (nbatch <= 0) fail(BS_ERR_ARG, "batch must be >= 1");
 	if (stride < w) fail(BS_ERR_ARG, "stride must be >= width");
-	if (plan.max_per_level > 0 && false) {}
 	ensure(w, h, nbatch);
 	batch = nbatch;
 	int* fo = d_frame_offset.as<int>();
@@ -215,3 +215,543 @@ void bs_surf::finish() {
 	BS_CUDA(cudaMemcpy(h_frame_offset.data(), d_frame_offset.p, (size_t)(batch + 1) * sizeof(int), cudaMemcpyDeviceToHost));
 	pending = false;
 }
+
+// ====================================================================================================== extern "C": misc
+extern "C" {
+
+void bs_fh_cfg_default(bs_fh_cfg* c) {
+	c->detect_threshold = 1; c->extract_radius = 2; c->max_features_per_scale = -1; c->initial_sample_size = 1;
+	c->initial_size = 9; c->scales_per_octave = 4; c->octaves = 4; c->scale_step_size = 6;
+}
+void bs_ori_cfg_default(bs_ori_cfg* c, int variant) {
+	c->variant = variant; c->object_radius_to_scale = 1.0 / 2.0; c->sample_width = 6; c->weight_sigma = -1;
+	c->window_size = M_PI / 3.0;
+	if (variant == 1) { c->radius = 8; c->sample_period = 0.65; }
+	else { c->radius = 6; c->sample_period = 1; }
+}
+void bs_desc_cfg_default(bs_desc_cfg* c, int variant) {
+	c->variant = variant; c->width_large_grid = 4; c->width_sub_region = 5; c->width_sample = 3; c->use_haar = 0;
+	c->weight_sigma = 4.5; c->overlap = 2; c->sigma_large_grid = 2.5; c->sigma_sub_region = 2.5;
+}
+const char* bs_last_error(void) { return last_error_cstr(); }
+const char* bs_version(void) { return "boofsurf-b200 0.1 (sm_100a)"; }
+int bs_device_count(int* n) {
+	return guarded([&] { BS_CUDA(cudaGetDeviceCount(n)); });
+}
+long bs_launch_count(void) { return launch_count(); }
+
+// ====================================================================================================== extern "C": bs_surf
+int bs_surf_create(int device, const bs_fh_cfg* fh, const bs_ori_cfg* ori, const bs_desc_cfg* desc, int pixel_type, bs_surf** out) {
+	return guarded([&] {
+		if (!out) fail(BS_ERR_ARG, "out is null");
+		*out = nullptr;
+		if (pixel_type != BS_PIXEL_F32 && pixel_type != BS_PIXEL_U8 && pixel_type != BS_PIXEL_S32)
+			fail(BS_ERR_ARG, "Unknown input type");   // GIntegralImageOps.getIntegralType :35-46
+		bs_fh_cfg f; bs_ori_cfg o; bs_desc_cfg d;
+		if (fh) f = *fh; else bs_fh_cfg_default(&f);
+		if (desc) d = *desc; else bs_desc_cfg_default(&d, ori ? ori->variant : 0);
+		if (ori) o = *ori; else bs_ori_cfg_default(&o, d.variant);
+		check_fh_cfg(f); check_ori_cfg(o); check_desc_cfg(d);
+		if (f.max_features_per_scale > 0)
+			fail(BS_ERR_ARG, "maxFeaturesPerScale > 0 (SelectNBestFeatures) is not implemented yet; use -1");
+		int ndev = 0;
+		BS_CUDA(cudaGetDeviceCount(&ndev));
+		if (device < 0 || device >= ndev) fail(BS_ERR_ARG, "no such CUDA device");
+		DeviceGuard g(device);
+		std::unique_ptr<bs_surf> s(new bs_surf());
+		s->device = device; s->fh = f; s->ori = o; s->desc = d; s->pixel_type = pixel_type;
+		BS_CUDA(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
+		BS_CUDA(cudaEventCreateWithFlags(&s->done, cudaEventDisableTiming));
+		s->ds.build(o, d);
+		s->ds.upload();
+		*out = s.release();
+	});
+}
+
+int bs_surf_destroy(bs_surf* s) {
+	if (!s) return BS_OK;
+	return guarded([&] {
+		DeviceGuard g(s->device);
+		cudaDeviceSynchronize();
+		s->ds.release(); s->pool.release();
+		s->d_plan.release(); s->d_in.release(); s->d_ii.release(); s->d_inten.release(); s->d_stage.release();
+		s->d_counts.release(); s->d_offsets.release(); s->d_frame_offset.release();
+		if (s->h_pinned) cudaFreeHost(s->h_pinned);
+		if (s->done) cudaEventDestroy(s->done);
+		if (s->stream) cudaStreamDestroy(s->stream);
+		delete s;
+	});
+}
+
+int bs_surf_set_workspace(bs_surf* s, int chunk_frames, long pool_features) {
+	return guarded([&] {
+		if (!s) fail(BS_ERR_ARG, "handle is null");
+		if (chunk_frames < 0 || pool_features < 0) fail(BS_ERR_ARG, "workspace sizes must be >= 0");
+		s->chunk_req = chunk_frames; s->pool_req = pool_features;
+	});
+}
+
+int bs_surf_dof(const bs_surf* s) { return s ? s->ds.p.dof : 0; }
+
+int bs_surf_detect_device(bs_surf* s, const void* d_pixels, long frame_stride, int stride, int width, int height, int batch,
+                          void* stream) {
+	return guarded([&] {
+		if (!s || !d_pixels) fail(BS_ERR_ARG, "null argument");
+		DeviceGuard g(s->device);
+		s->run(d_pixels, frame_stride, stride, width, height, batch, stream ? static_cast<cudaStream_t>(stream) : s->stream);
+	});
+}
+
+int bs_surf_detect(bs_surf* s, const void* pixels, int start_index, int stride, int width, int height) {
+	return guarded([&] {
+		if (!s || !pixels) fail(BS_ERR_ARG, "null argument");
+		if (width <= 0 || height <= 0) fail(BS_ERR_ARG, "image width and height must be positive");
+		if (stride < width || start_index < 0) fail(BS_ERR_ARG, "bad stride/startIndex");
+		DeviceGuard g(s->device);
+		const size_t es = elem_size(s->pixel_type);
+		const size_t dense = (size_t)width * height * es;
+		s->d_in.reserve(dense);
+		const char* src = static_cast<const char*>(pixels) + (size_t)start_index * es;
+		// sub-images arrive as a pitched copy; the device copy is dense
+		BS_CUDA(cudaMemcpy2DAsync(s->d_in.p, (size_t)width * es, src, (size_t)stride * es, (size_t)width * es, height,
+		                          cudaMemcpyHostToDevice, s->stream));
+		s->run(s->d_in.p, (long)width * height, width, width, height, 1, s->stream);
+		s->finish();
+	});
+}
+
+static void check_ready(bs_surf* s) {
+	if (!s) fail(BS_ERR_ARG, "handle is null");
+	if (s->batch <= 0) fail(BS_ERR_STATE, "detect has not been called");
+	s->finish();
+}
+
+int bs_surf_total(bs_surf* s, long* n) {
+	return guarded([&] {
+		DeviceGuard g(s ? s->device : 0);
+		check_ready(s);
+		if (n) *n = s->h_frame_offset[s->batch];
+		if (s->h_frame_offset[s->batch] > s->pool.view.cap) fail(BS_ERR_CAPACITY, "feature pool too small for this batch");
+	});
+}
+
+int bs_surf_count(bs_surf* s, int frame, int* n) {
+	return guarded([&] {
+		DeviceGuard g(s ? s->device : 0);
+		check_ready(s);
+		if (frame < 0 || frame >= s->batch) fail(BS_ERR_ARG, "frame out of range");
+		if (n) *n = s->h_frame_offset[frame + 1] - s->h_frame_offset[frame];
+		if (s->h_frame_offset[frame + 1] > s->pool.view.cap) fail(BS_ERR_CAPACITY, "feature pool too small for this batch");
+	});
+}
+
+int bs_surf_read(bs_surf* s, int frame, double* xy, double* scale, double* angle, double* desc, uint8_t* white, int32_t* meta,
+                 float* response) {
+	return guarded([&] {
+		DeviceGuard g(s ? s->device : 0);
+		check_ready(s);
+		if (frame < 0 || frame >= s->batch) fail(BS_ERR_ARG, "frame out of range");
+		const long b = s->h_frame_offset[frame], e = s->h_frame_offset[frame + 1];
+		if (e > s->pool.view.cap) fail(BS_ERR_CAPACITY, "feature pool too small for this batch");
+		const size_t n = (size_t)(e - b);
+		if (n == 0) return;
+		const Pool& p = s->pool.view;
+		const int dof = s->ds.p.dof;
+		if (xy) BS_CUDA(cudaMemcpy(xy, p.xy + 2 * b, n * 16, cudaMemcpyDeviceToHost));
+		if (scale) BS_CUDA(cudaMemcpy(scale, p.scale + b, n * 8, cudaMemcpyDeviceToHost));
+		if (angle) BS_CUDA(cudaMemcpy(angle, p.angle + b, n * 8, cudaMemcpyDeviceToHost));
+		if (desc) BS_CUDA(cudaMemcpy(desc, p.desc + b * dof, n * dof * 8, cudaMemcpyDeviceToHost));
+		if (white) BS_CUDA(cudaMemcpy(white, p.white + b, n, cudaMemcpyDeviceToHost));
+		if (meta) BS_CUDA(cudaMemcpy(meta, p.meta + 4 * b, n * 16, cudaMemcpyDeviceToHost));
+		if (response) BS_CUDA(cudaMemcpy(response, p.response + b, n * 4, cudaMemcpyDeviceToHost));
+	});
+}
+
+int bs_surf_view(bs_surf* s, bs_surf_device_view* v) {
+	return guarded([&] {
+		if (!v) fail(BS_ERR_ARG, "view is null");
+		DeviceGuard g(s ? s->device : 0);
+		check_ready(s);
+		const Pool& p = s->pool.view;
+		v->d_xy = p.xy; v->d_scale = p.scale; v->d_angle = p.angle; v->d_desc = p.desc; v->d_white = p.white;
+		v->d_frame_offset = s->d_frame_offset.as<int32_t>();
+		v->total = s->h_frame_offset[s->batch]; v->batch = s->batch; v->dof = s->ds.p.dof;
+		if (v->total > p.cap) fail(BS_ERR_CAPACITY, "feature pool too small for this batch");
+	});
+}
+
+}  // extern "C"
+
+// ====================================================================================================== stage-level entry points
+namespace {
+
+struct TempStream {
+	cudaStream_t st = nullptr;
+	TempStream() { BS_CUDA(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking)); }
+	~TempStream() { if (st) cudaStreamDestroy(st); }
+};
+
+void check_device(int device) {
+	int ndev = 0;
+	BS_CUDA(cudaGetDeviceCount(&ndev));
+	if (device < 0 || device >= ndev) fail(BS_ERR_ARG, "no such CUDA device");
+}
+
+// upload a dense integral image of either type
+void upload_ii(DevBuf& d, const void* ii, int width, int height) {
+	if (!ii || width <= 0 || height <= 0) fail(BS_ERR_ARG, "bad integral image");
+	d.reserve((size_t)width * height * 4);
+	BS_CUDA(cudaMemcpy(d.p, ii, (size_t)width * height * 4, cudaMemcpyHostToDevice));
+}
+
+// pool with n caller-given points (frame 0) and the range [0,n] on the device
+struct PointSet {
+	PoolBufs pool; DevBuf range;
+	void load(const double* xys, const double* angle, int n, int dof) {
+		pool.reserve(n, dof);
+		std::vector<double> xy((size_t)2 * n), sc(n);
+		for (int i = 0; i < n; i++) { xy[2 * i] = xys[3 * i]; xy[2 * i + 1] = xys[3 * i + 1]; sc[i] = xys[3 * i + 2]; }
+		BS_CUDA(cudaMemcpy(pool.view.xy, xy.data(), xy.size() * 8, cudaMemcpyHostToDevice));
+		BS_CUDA(cudaMemcpy(pool.view.scale, sc.data(), sc.size() * 8, cudaMemcpyHostToDevice));
+		BS_CUDA(cudaMemset(pool.view.frame, 0, (size_t)n * 4));
+		if (angle) BS_CUDA(cudaMemcpy(pool.view.angle, angle, (size_t)n * 8, cudaMemcpyHostToDevice));
+		const int r[2] = {0, n};
+		range.reserve(8);
+		BS_CUDA(cudaMemcpy(range.p, r, 8, cudaMemcpyHostToDevice));
+	}
+	void release() { pool.release(); range.release(); }
+};
+
+}  // namespace
+
+extern "C" {
+
+int bs_integral(int device, int pixel_type, const void* in, int in_stride, int width, int height, void* out) {
+	return guarded([&] {
+		if (!in || !out) fail(BS_ERR_ARG, "null argument");
+		if (width <= 0 || height <= 0) return;      // empty image: nothing to do, like the reference loops
+		if (in_stride < width) fail(BS_ERR_ARG, "stride must be >= width");
+		check_device(device);
+		DeviceGuard g(device);
+		TempStream ts;
+		DevBuf d_in, d_out;
+		const size_t es = elem_size(pixel_type);
+		d_in.reserve((size_t)width * height * es);
+		d_out.reserve((size_t)width * height * 4);
+		BS_CUDA(cudaMemcpy2D(d_in.p, width * es, in, in_stride * es, width * es, height, cudaMemcpyHostToDevice));
+		if (pixel_type == BS_PIXEL_F32) launch_integral<float, float>(d_in.as<float>(), 0, width, d_out.as<float>(), width, height, 1, ts.st);
+		else if (pixel_type == BS_PIXEL_U8) launch_integral<uint8_t, int32_t>(d_in.as<uint8_t>(), 0, width, d_out.as<int32_t>(), width, height, 1, ts.st);
+		else if (pixel_type == BS_PIXEL_S32) launch_integral<int32_t, int32_t>(d_in.as<int32_t>(), 0, width, d_out.as<int32_t>(), width, height, 1, ts.st);
+		else fail(BS_ERR_ARG, "Unknown input type");
+		BS_CUDA(cudaStreamSynchronize(ts.st));
+		BS_CUDA(cudaMemcpy(out, d_out.p, (size_t)width * height * 4, cudaMemcpyDeviceToHost));
+		d_in.release(); d_out.release();
+	});
+}
+
+int bs_hessian(int device, int ii_type, const void* ii, int width, int height, int skip, int size, float* out) {
+	return guarded([&] {
+		if (!out) fail(BS_ERR_ARG, "null argument");
+		if (skip < 1 || size < 3) fail(BS_ERR_ARG, "bad skip/size");
+		check_device(device);
+		DeviceGuard g(device);
+		TempStream ts;
+		DevBuf d_ii, d_out;
+		upload_ii(d_ii, ii, width, height);
+		const size_t n = (size_t)(width / skip) * (height / skip);
+		if (n == 0) { d_ii.release(); return; }
+		d_out.reserve(n * 4);
+		if (ii_type == BS_PIXEL_F32) launch_hessian_single<float>(d_ii.as<float>(), width, height, skip, size, d_out.as<float>(), ts.st);
+		else launch_hessian_single<int32_t>(d_ii.as<int32_t>(), width, height, skip, size, d_out.as<float>(), ts.st);
+		BS_CUDA(cudaStreamSynchronize(ts.st));
+		BS_CUDA(cudaMemcpy(out, d_out.p, n * 4, cudaMemcpyDeviceToHost));
+		d_ii.release(); d_out.release();
+	});
+}
+
+int bs_fh_detect(int device, int ii_type, const void* ii, int width, int height, const bs_fh_cfg* cfg, int max_out, int* n_out,
+                 double* xys, int32_t* meta, float* response) {
+	return guarded([&] {
+		bs_fh_cfg f;
+		if (cfg) f = *cfg; else bs_fh_cfg_default(&f);
+		check_fh_cfg(f);
+		if (f.max_features_per_scale > 0) fail(BS_ERR_ARG, "maxFeaturesPerScale > 0 is not implemented yet");
+		if (max_out < 0) fail(BS_ERR_ARG, "max_out must be >= 0");
+		check_device(device);
+		DeviceGuard g(device);
+		TempStream ts;
+		DevBuf d_ii, d_plan, d_inten, d_stage, d_counts, d_offsets, d_fo;
+		PoolBufs pool;
+		upload_ii(d_ii, ii, width, height);
+		Plan plan = make_plan(f, width, height);
+		d_plan.reserve(sizeof(Plan));
+		BS_CUDA(cudaMemcpy(d_plan.p, &plan, sizeof(Plan), cudaMemcpyHostToDevice));
+		d_inten.reserve((size_t)std::max<long>(plan.inten_per_frame, 1) * 4);
+		const size_t nctas = std::max(plan.ctas_per_frame, 1);
+		d_stage.reserve(nctas * NMS_CTA_BLOCKS * sizeof(RawPoint));
+		d_counts.reserve(nctas * 4); d_offsets.reserve(nctas * 4); d_fo.reserve(8);
+		BS_CUDA(cudaMemset(d_fo.p, 0, 8));
+		pool.reserve(std::max(max_out, 1), 1);
+		if (ii_type == BS_PIXEL_F32) launch_hessian_plan<float>(d_ii.as<float>(), plan, d_plan.as<Plan>(), d_inten.as<float>(), 1, ts.st);
+		else launch_hessian_plan<int32_t>(d_ii.as<int32_t>(), plan, d_plan.as<Plan>(), d_inten.as<float>(), 1, ts.st);
+		launch_nms(plan, d_plan.as<Plan>(), d_inten.as<float>(), 1, d_stage.as<RawPoint>(), d_counts.as<int>(), ts.st);
+		launch_compact(plan, 1, 0, d_stage.as<RawPoint>(), d_counts.as<int>(), d_offsets.as<int>(), d_fo.as<int>(), pool.view, ts.st);
+		BS_CUDA(cudaStreamSynchronize(ts.st));
+		int fo[2];
+		BS_CUDA(cudaMemcpy(fo, d_fo.p, 8, cudaMemcpyDeviceToHost));
+		if (n_out) *n_out = fo[1];
+		const int k = std::min(fo[1], max_out);
+		if (k > 0) {
+			if (xys) {
+				std::vector<double> xy((size_t)2 * k), sc(k);
+				BS_CUDA(cudaMemcpy(xy.data(), pool.view.xy, xy.size() * 8, cudaMemcpyDeviceToHost));
+				BS_CUDA(cudaMemcpy(sc.data(), pool.view.scale, sc.size() * 8, cudaMemcpyDeviceToHost));
+				for (int i = 0; i < k; i++) { xys[3 * i] = xy[2 * i]; xys[3 * i + 1] = xy[2 * i + 1]; xys[3 * i + 2] = sc[i]; }
+			}
+			if (meta) BS_CUDA(cudaMemcpy(meta, pool.view.meta, (size_t)k * 16, cudaMemcpyDeviceToHost));
+			if (response) BS_CUDA(cudaMemcpy(response, pool.view.response, (size_t)k * 4, cudaMemcpyDeviceToHost));
+		}
+		d_ii.release(); d_plan.release(); d_inten.release(); d_stage.release(); d_counts.release(); d_offsets.release(); d_fo.release();
+		pool.release();
+	});
+}
+
+static void run_describe_stage(int device, int ii_type, const void* ii, int width, int height, const bs_ori_cfg& o, const bs_desc_cfg& d,
+                               const double* xys, const double* angle_in, int n, bool do_ori, bool do_desc, double* angle_out,
+                               double* desc_out, uint8_t* white_out) {
+	if (n < 0) fail(BS_ERR_ARG, "n must be >= 0");
+	if (n == 0) return;
+	if (!xys) fail(BS_ERR_ARG, "null argument");
+	check_device(device);
+	DeviceGuard g(device);
+	TempStream ts;
+	DevBuf d_ii;
+	upload_ii(d_ii, ii, width, height);
+	DescribeSetup ds;
+	ds.build(o, d);
+	ds.upload();
+	PointSet ps;
+	ps.load(xys, angle_in, n, ds.p.dof);
+	const int* r = ps.range.as<int>();
+	if (ii_type == BS_PIXEL_F32) launch_describe<float>(d_ii.as<float>(), width, height, ds.p, ds.tables, ps.pool.view, r, r + 1, 0, do_ori, do_desc, ts.st);
+	else launch_describe<int32_t>(d_ii.as<int32_t>(), width, height, ds.p, ds.tables, ps.pool.view, r, r + 1, 0, do_ori, do_desc, ts.st);
+	BS_CUDA(cudaStreamSynchronize(ts.st));
+	if (angle_out) BS_CUDA(cudaMemcpy(angle_out, ps.pool.view.angle, (size_t)n * 8, cudaMemcpyDeviceToHost));
+	if (desc_out) BS_CUDA(cudaMemcpy(desc_out, ps.pool.view.desc, (size_t)n * ds.p.dof * 8, cudaMemcpyDeviceToHost));
+	if (white_out) BS_CUDA(cudaMemcpy(white_out, ps.pool.view.white, (size_t)n, cudaMemcpyDeviceToHost));
+	ps.release(); ds.release(); d_ii.release();
+}
+
+int bs_orientation(int device, int ii_type, const void* ii, int width, int height, const bs_ori_cfg* cfg, const double* xys, int n,
+                   double* angle) {
+	return guarded([&] {
+		bs_ori_cfg o; bs_desc_cfg d;
+		if (cfg) o = *cfg; else bs_ori_cfg_default(&o, 0);
+		bs_desc_cfg_default(&d, 0);
+		check_ori_cfg(o);
+		run_describe_stage(device, ii_type, ii, width, height, o, d, xys, nullptr, n, true, false, angle, nullptr, nullptr);
+	});
+}
+
+int bs_describe(int device, int ii_type, const void* ii, int width, int height, const bs_desc_cfg* cfg, const double* xys,
+                const double* angle, int n, double* desc, uint8_t* white) {
+	return guarded([&] {
+		bs_ori_cfg o; bs_desc_cfg d;
+		if (cfg) d = *cfg; else bs_desc_cfg_default(&d, 0);
+		bs_ori_cfg_default(&o, 0);
+		check_desc_cfg(d);
+		if (!angle) fail(BS_ERR_ARG, "null argument");
+		run_describe_stage(device, ii_type, ii, width, height, o, d, xys, angle, n, false, true, nullptr, desc, white);
+	});
+}
+
+}  // extern "C"
+
+// ====================================================================================================== bs_assoc
+struct bs_assoc {
+	int device = 0;
+	double max_fit = DBL_MAX;
+	int backwards = 0;
+	int mode = -1;            // -1 auto, 0 exact, 1 tensor-core filter + exact re-score
+	int sm_count = 148;
+	cudaStream_t stream = nullptr;
+	DevBuf p_min, p_first, p_last;            // split partials
+	DevBuf col_min, col_first, col_last;      // column statistics
+	DevBuf d_src, d_dst, d_pairs, d_fit;      // staging for the host entry point
+
+	RowminScratch scratch(long entries) {
+		p_min.reserve(entries * 8); p_first.reserve(entries * 4); p_last.reserve(entries * 4);
+		return RowminScratch{p_min.as<double>(), p_first.as<int>(), p_last.as<int>(), entries};
+	}
+	// forward pass of the local rows: pairs/fit
+	void forward(const double* src, int n, const double* dst, int m, int dof, int32_t* pairs, double* fit, cudaStream_t st) {
+		const int splits = rowmin_splits(n, m, sm_count);
+		RowminScratch s = scratch((long)splits * n);
+		launch_rowmin(src, n, dst, m, dof, splits, s, st);
+		launch_rowmin_finalize(s, n, splits, 0, max_fit, 0, pairs, fit, nullptr, nullptr, nullptr, st);
+	}
+	// column statistics over the local rows (global numbering = row_offset + local)
+	void columns(const double* src, int n, int row_offset, const double* dst, int m, int dof, double* cmin, int32_t* cfirst,
+	             int32_t* clast, cudaStream_t st) {
+		const int splits = rowmin_splits(m, n, sm_count);
+		RowminScratch s = scratch((long)splits * m);
+		launch_rowmin(dst, m, src, n, dof, splits, s, st);
+		launch_rowmin_finalize(s, m, splits, 1, 0.0, row_offset, nullptr, nullptr, cmin, cfirst, clast, st);
+	}
+	void run(const double* src, int n, const double* dst, int m, int dof, int32_t* pairs, double* fit, cudaStream_t st) {
+		if (n < 0 || m < 0 || dof < 1) fail(BS_ERR_ARG, "bad sizes");
+		if (n == 0) return;
+		if (m == 0) {   // no destination: every source is unmatched with the untouched running best
+			std::vector<int32_t> hp(n, -1); std::vector<double> hf(n, max_fit);
+			BS_CUDA(cudaMemcpyAsync(pairs, hp.data(), (size_t)n * 4, cudaMemcpyHostToDevice, st));
+			BS_CUDA(cudaMemcpyAsync(fit, hf.data(), (size_t)n * 8, cudaMemcpyHostToDevice, st));
+			BS_CUDA(cudaStreamSynchronize(st));
+			return;
+		}
+		forward(src, n, dst, m, dof, pairs, fit, st);
+		if (backwards) {
+			col_min.reserve((size_t)m * 8); col_first.reserve((size_t)m * 4); col_last.reserve((size_t)m * 4);
+			columns(src, n, 0, dst, m, dof, col_min.as<double>(), col_first.as<int32_t>(), col_last.as<int32_t>(), st);
+			launch_validate(n, 0, pairs, fit, col_min.as<double>(), col_first.as<int32_t>(), col_last.as<int32_t>(), st);
+		}
+	}
+};
+
+extern "C" {
+
+int bs_assoc_create(int device, double max_fit_error, int backwards_validation, bs_assoc** out) {
+	return guarded([&] {
+		if (!out) fail(BS_ERR_ARG, "out is null");
+		*out = nullptr;
+		check_device(device);
+		DeviceGuard g(device);
+		std::unique_ptr<bs_assoc> a(new bs_assoc());
+		a->device = device; a->max_fit = max_fit_error; a->backwards = backwards_validation ? 1 : 0;
+		BS_CUDA(cudaDeviceGetAttribute(&a->sm_count, cudaDevAttrMultiProcessorCount, device));
+		BS_CUDA(cudaStreamCreateWithFlags(&a->stream, cudaStreamNonBlocking));
+		*out = a.release();
+	});
+}
+
+int bs_assoc_destroy(bs_assoc* a) {
+	if (!a) return BS_OK;
+	return guarded([&] {
+		DeviceGuard g(a->device);
+		cudaDeviceSynchronize();
+		a->p_min.release(); a->p_first.release(); a->p_last.release();
+		a->col_min.release(); a->col_first.release(); a->col_last.release();
+		a->d_src.release(); a->d_dst.release(); a->d_pairs.release(); a->d_fit.release();
+		if (a->stream) cudaStreamDestroy(a->stream);
+		delete a;
+	});
+}
+
+int bs_assoc_set_max_fit_error(bs_assoc* a, double max_fit_error) {
+	return guarded([&] { if (!a) fail(BS_ERR_ARG, "handle is null"); a->max_fit = max_fit_error; });
+}
+
+int bs_assoc_set_mode(bs_assoc* a, int mode) {
+	return guarded([&] {
+		if (!a) fail(BS_ERR_ARG, "handle is null");
+		if (mode < -1 || mode > 1) fail(BS_ERR_ARG, "mode must be -1 (auto), 0 (exact) or 1 (tensor-core filter)");
+		if (mode == 1) fail(BS_ERR_ARG, "tensor-core filter mode is not built in this version");
+		a->mode = mode;
+	});
+}
+
+int bs_assoc_run_device(bs_assoc* a, const double* d_src, int n, const double* d_dst, int m, int dof, int32_t* d_pairs, double* d_fit,
+                        void* stream) {
+	return guarded([&] {
+		if (!a) fail(BS_ERR_ARG, "handle is null");
+		if ((n > 0 && (!d_src || !d_pairs || !d_fit)) || (m > 0 && !d_dst)) fail(BS_ERR_ARG, "null argument");
+		DeviceGuard g(a->device);
+		a->run(d_src, n, d_dst, m, dof, d_pairs, d_fit, stream ? static_cast<cudaStream_t>(stream) : a->stream);
+	});
+}
+
+int bs_assoc_run(bs_assoc* a, const double* src, int n, const double* dst, int m, int dof, int32_t* pairs, double* fit) {
+	return guarded([&] {
+		if (!a) fail(BS_ERR_ARG, "handle is null");
+		if (!src && n > 0) fail(BS_ERR_STATE, "source features not specified");
+		if (!dst && m > 0) fail(BS_ERR_STATE, "destination features not specified");
+		if (n < 0 || m < 0 || dof < 1) fail(BS_ERR_ARG, "bad sizes");
+		if (n == 0) return;
+		if (!pairs || !fit) fail(BS_ERR_ARG, "null argument");
+		DeviceGuard g(a->device);
+		a->d_src.reserve((size_t)n * dof * 8); a->d_dst.reserve((size_t)std::max(m, 1) * dof * 8);
+		a->d_pairs.reserve((size_t)n * 4); a->d_fit.reserve((size_t)n * 8);
+		BS_CUDA(cudaMemcpyAsync(a->d_src.p, src, (size_t)n * dof * 8, cudaMemcpyHostToDevice, a->stream));
+		if (m > 0) BS_CUDA(cudaMemcpyAsync(a->d_dst.p, dst, (size_t)m * dof * 8, cudaMemcpyHostToDevice, a->stream));
+		a->run(a->d_src.as<double>(), n, a->d_dst.as<double>(), m, dof, a->d_pairs.as<int32_t>(), a->d_fit.as<double>(), a->stream);
+		BS_CUDA(cudaMemcpyAsync(pairs, a->d_pairs.p, (size_t)n * 4, cudaMemcpyDeviceToHost, a->stream));
+		BS_CUDA(cudaMemcpyAsync(fit, a->d_fit.p, (size_t)n * 8, cudaMemcpyDeviceToHost, a->stream));
+		BS_CUDA(cudaStreamSynchronize(a->stream));
+	});
+}
+
+int bs_assoc_forward_device(bs_assoc* a, const double* d_src, int n, int row_offset, const double* d_dst, int m, int dof,
+                            int32_t* d_pairs, double* d_fit, double* d_col_min, int32_t* d_col_first, int32_t* d_col_last,
+                            void* stream) {
+	return guarded([&] {
+		if (!a) fail(BS_ERR_ARG, "handle is null");
+		if (n <= 0 || m <= 0 || dof < 1) fail(BS_ERR_ARG, "bad sizes");
+		if (!d_src || !d_dst || !d_pairs || !d_fit || !d_col_min || !d_col_first || !d_col_last) fail(BS_ERR_ARG, "null argument");
+		DeviceGuard g(a->device);
+		cudaStream_t st = stream ? static_cast<cudaStream_t>(stream) : a->stream;
+		a->forward(d_src, n, d_dst, m, dof, d_pairs, d_fit, st);
+		a->columns(d_src, n, row_offset, d_dst, m, dof, d_col_min, d_col_first, d_col_last, st);
+	});
+}
+
+int bs_assoc_merge_columns_device(bs_assoc* a, int ranks, int m, const double* d_all_min, const int32_t* d_all_first,
+                                  const int32_t* d_all_last, double* d_col_min, int32_t* d_col_first, int32_t* d_col_last,
+                                  void* stream) {
+	return guarded([&] {
+		if (!a) fail(BS_ERR_ARG, "handle is null");
+		if (ranks < 1 || m < 0) fail(BS_ERR_ARG, "bad sizes");
+		DeviceGuard g(a->device);
+		launch_merge_columns(ranks, m, d_all_min, d_all_first, d_all_last, d_col_min, d_col_first, d_col_last,
+		                     stream ? static_cast<cudaStream_t>(stream) : a->stream);
+	});
+}
+
+int bs_assoc_validate_device(bs_assoc* a, int n, int row_offset, int32_t* d_pairs, double* d_fit, const double* d_col_min,
+                             const int32_t* d_col_first, const int32_t* d_col_last, void* stream) {
+	return guarded([&] {
+		if (!a) fail(BS_ERR_ARG, "handle is null");
+		DeviceGuard g(a->device);
+		launch_validate(n, row_offset, d_pairs, d_fit, d_col_min, d_col_first, d_col_last,
+		                stream ? static_cast<cudaStream_t>(stream) : a->stream);
+	});
+}
+
+// WrapAssociateGreedy.associate :85-92, FindUnassociated.checkDestination :56-72 — index bookkeeping on the host
+int bs_assoc_matches(const int32_t* pairs, const double* fit, int n, int m, int32_t* match_src, int32_t* match_dst,
+                     double* match_score, int* n_matches, int32_t* unassoc_src, int* n_unassoc_src, int32_t* unassoc_dst,
+                     int* n_unassoc_dst) {
+	return guarded([&] {
+		if (n < 0 || m < 0 || (n > 0 && (!pairs || !fit))) fail(BS_ERR_ARG, "bad arguments");
+		std::vector<char> hit((size_t)std::max(m, 1), 0);
+		int nm = 0, nus = 0, nud = 0;
+		for (int i = 0; i < n; i++) {
+			const int d = pairs[i];
+			if (d >= 0) {
+				if (d >= m) fail(BS_ERR_ARG, "pair index out of range");
+				if (match_src) match_src[nm] = i;
+				if (match_dst) match_dst[nm] = d;
+				if (match_score) match_score[nm] = fit[i];
+				nm++; hit[d] = 1;
+			} else {
+				if (unassoc_src) unassoc_src[nus] = i;
+				nus++;
+			}
+		}
+		for (int j = 0; j < m; j++)
+			if (!hit[j]) { if (unassoc_dst) unassoc_dst[nud] = j; nud++; }
+		if (n_matches) *n_matches = nm;
+		if (n_unassoc_src) *n_unassoc_src = nus;
+		if (n_unassoc_dst) *n_unassoc_dst = nud;
+	});
+}
+
+}  // extern "C"
