@@ -1,0 +1,142 @@
+"""FactoryAssociation.greedy -> AssociateDescription<TupleDesc_F64> over the C ABI (bs_assoc_*).
+
+Reference: F/factory/feature/associate/FactoryAssociation.java:51-65, WrapAssociateGreedy
+(F/abst/feature/associate/WrapAssociateGreedy.java:58-123), AssociateGreedy (F/alg/feature/associate/AssociateGreedy.java:65-118),
+ScoreAssociateEuclideanSq_F64 (F/abst/feature/associate/ScoreAssociateEuclideanSq_F64.java:33-43)."""
+import ctypes as C
+
+import numpy as np
+
+from . import _native as N
+from .surf import AssociatedIndex
+
+DOUBLE_MAX = float(np.finfo(np.float64).max)      # Double.MAX_VALUE
+
+
+class MatchScoreType:
+    NORM_ERROR = "NORM_ERROR"
+
+
+class ScoreAssociateEuclideanSq_F64:
+    """The only score the GPU path implements (the one FactoryAssociation.defaultScore picks for TupleDesc_F64 / SURF)."""
+    def getScoreType(self):
+        return MatchScoreType.NORM_ERROR
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+def _as_matrix(features):
+    """FastQueue<TupleDesc_F64> -> [n][dof] float64.  Accepts an ndarray or a sequence of objects with `.value`."""
+    if features is None:
+        return None
+    if isinstance(features, np.ndarray):
+        a = features
+    else:
+        features = list(features)
+        if len(features) == 0:
+            return np.zeros((0, 0), np.float64)
+        a = np.stack([np.asarray(getattr(f, "value", f), np.float64) for f in features])
+    if a.ndim == 1:
+        a = a[:, None]
+    return np.ascontiguousarray(a, np.float64)
+
+
+class AssociateGreedyGPU:
+    def __init__(self, score, maxError, backwardsValidation, device=0):
+        if not isinstance(score, ScoreAssociateEuclideanSq_F64):
+            raise ValueError("only ScoreAssociateEuclideanSq_F64 is supported by the GPU associator")
+        self._score = score
+        self._backwards = bool(backwardsValidation)
+        self._h = C.c_void_p()
+        N.check(N.lib().bs_assoc_create(device, float(maxError), int(self._backwards), C.byref(self._h)))
+        self.device = device
+        self._src = None; self._dst = None
+        self._matches = []; self._unassoc_src = np.zeros(0, np.int32); self._unassoc_dst = np.zeros(0, np.int32)
+        self._pairs = None; self._fit = None
+
+    def close(self):
+        if getattr(self, "_h", None) and self._h.value:
+            N.lib().bs_assoc_destroy(self._h)
+            self._h = C.c_void_p()
+
+    __del__ = close
+
+    def setSource(self, listSrc):
+        self._src = _as_matrix(listSrc)
+
+    def setDestination(self, listDst):
+        self._dst = _as_matrix(listDst)
+
+    def associate(self):
+        if self._src is None:
+            raise ValueError("source features not specified")
+        if self._dst is None:
+            raise ValueError("destination features not specified")
+        n, m = len(self._src), len(self._dst)
+        dof = max(self._src.shape[1] if n else 0, self._dst.shape[1] if m else 0, 1)
+        if (n and self._src.shape[1] != dof) or (m and self._dst.shape[1] != dof):
+            raise ValueError("source and destination descriptors differ in length")
+        self._pairs = np.full(n, -1, np.int32); self._fit = np.zeros(n, np.float64)
+        if n:
+            N.check(N.lib().bs_assoc_run(self._h, _p(self._src), n, _p(self._dst) if m else None, m, dof, _p(self._pairs),
+                                         _p(self._fit)))
+        ms = np.zeros(n, np.int32); md = np.zeros(n, np.int32); sc = np.zeros(n, np.float64)
+        us = np.zeros(n, np.int32); ud = np.zeros(m, np.int32)
+        nm, nus, nud = C.c_int(0), C.c_int(0), C.c_int(0)
+        N.check(N.lib().bs_assoc_matches(_p(self._pairs), _p(self._fit), n, m, _p(ms), _p(md), _p(sc), C.byref(nm), _p(us),
+                                         C.byref(nus), _p(ud), C.byref(nud)))
+        self._matches = [AssociatedIndex(int(ms[k]), int(md[k]), float(sc[k])) for k in range(nm.value)]
+        self._unassoc_src = us[:nus.value].copy()
+        self._unassoc_dst = ud[:nud.value].copy()
+
+    def getMatches(self):
+        return self._matches
+
+    def getUnassociatedSource(self):
+        return self._unassoc_src
+
+    def getUnassociatedDestination(self):
+        return self._unassoc_dst
+
+    def getPairs(self):            # AssociateGreedyBase.getPairs
+        return self._pairs
+
+    def getFitQuality(self):       # AssociateGreedyBase.getFitQuality
+        return self._fit
+
+    def setMaxScoreThreshold(self, score):
+        N.check(N.lib().bs_assoc_set_max_fit_error(self._h, float(score)))
+
+    def setMode(self, mode):
+        N.check(N.lib().bs_assoc_set_mode(self._h, int(mode)))
+
+    def getScoreType(self):
+        return self._score.getScoreType()
+
+    def uniqueSource(self):
+        return True
+
+    def uniqueDestination(self):
+        return self._backwards
+
+    # device-resident variant (torch float64 tensors [n,dof], [m,dof]); returns (pairs int32[n], fit float64[n]) tensors
+    def associateDevice(self, src, dst, stream=None):
+        import torch
+        n, dof = src.shape; m = dst.shape[0]
+        pairs = torch.empty(n, dtype=torch.int32, device=src.device); fit = torch.empty(n, dtype=torch.float64, device=src.device)
+        st = stream if stream is not None else torch.cuda.current_stream(src.device).cuda_stream
+        N.check(N.lib().bs_assoc_run_device(self._h, C.c_void_p(src.data_ptr()), n, C.c_void_p(dst.data_ptr()), m, dof,
+                                            C.c_void_p(pairs.data_ptr()), C.c_void_p(fit.data_ptr()), C.c_void_p(st)))
+        return pairs, fit
+
+
+class FactoryAssociation:
+    @staticmethod
+    def greedy(score, maxError, backwardsValidation, device=0):
+        return AssociateGreedyGPU(score, maxError, backwardsValidation, device)
+
+    @staticmethod
+    def defaultScore(tupleType=None):
+        return ScoreAssociateEuclideanSq_F64()

@@ -1,0 +1,216 @@
+"""GPU parity of the drop-in interfaces (DetectDescribePoint / AssociateDescription mirrors) vs the CPU oracle.
+Templates: TestWrapDetectDescribeSurf_MT.java:54-101 (same features, here also in the same order and bit for bit),
+GenericTestsDetectDescribePoint.java:83-211, TestAssociateGreedy.java:38-102, StandardAssociateDescriptionChecks.java:76-239,
+TestAssociateGreedy_MT.java:32-59."""
+import numpy as np
+import pytest
+
+from synth import blob_image, shifted_pair, descriptors, planted_descriptors
+
+pytestmark = pytest.mark.gpu
+DMAX = float(np.finfo(np.float64).max)
+
+
+@pytest.fixture(scope="module")
+def bs():
+    import boofcv_b200
+    return boofcv_b200
+
+
+def _same(r, o):
+    assert len(r["x"]) == len(o["x"])
+    for k in ("x", "y", "scale", "angle", "desc", "white"):
+        assert np.array_equal(r[k], o[k]), k
+
+
+# ------------------------------------------------------------------ detect + describe
+@pytest.mark.parametrize("which", ["fast", "stable"])
+@pytest.mark.parametrize("shape,seed", [((400, 300), 234), ((640, 480), 3)])
+def test_surf_matches_oracle_bit_exact(bs, orc, which, shape, seed):
+    img = blob_image(shape[0], shape[1], seed)
+    det = getattr(bs.FactoryDetectDescribe, "surfFast" if which == "fast" else "surfStable")(None, None, None, np.float32)
+    det.detect(img)
+    o = (orc.surf_fast if which == "fast" else orc.surf_stable)(img)
+    assert len(o["x"]) > 100
+    _same(det.readFrame(0), o)
+    det.close()
+
+
+def test_surf_noise_image_interface_contract(bs, orc):
+    # GenericTestsDetectDescribePoint: 100x120 uniform noise, N>5, finite, in bounds, repeatable, sub-image identical
+    rng = np.random.default_rng(234)
+    img = rng.uniform(0, 100, (120, 100)).astype(np.float32)
+    det = bs.FactoryDetectDescribe.surfFast(None, None, None, np.float32)
+    det.detect(img)
+    n = det.getNumberOfFeatures()
+    assert n > 5 and det.hasScale() and det.hasOrientation() and det.getDescriptionType() is bs.BrightFeature
+    assert det.createDescription().size() == 64
+    first = det.readFrame(0)
+    for i in range(n):
+        p = det.getLocation(i)
+        assert 0 <= p.x < 100 and 0 <= p.y < 120 and (p.x != 0 or p.y != 0)
+        assert np.isfinite(det.getRadius(i)) and det.getRadius(i) > 0 and -np.pi <= det.getOrientation(i) <= np.pi
+        d = det.getDescription(i)
+        assert np.isfinite(d.value).all() and d.size() == 64
+    _same(first, orc.surf_fast(img))
+    det.detect(img)                                  # two calls -> identical
+    _same(det.readFrame(0), first)
+    big = np.zeros((150, 140), np.float32); big[20:140, 30:130] = img
+    det.detect(big[20:140, 30:130])                  # sub-image -> identical
+    _same(det.readFrame(0), first)
+    det.close()
+
+
+def test_surf_u8_input(bs, orc):
+    img = np.clip(blob_image(320, 240, 9), 0, 255).astype(np.uint8)
+    det = bs.FactoryDetectDescribe.surfFast(None, None, None, np.uint8)
+    det.detect(img)
+    o = orc.surf(img)
+    assert len(o["x"]) > 20
+    _same(det.readFrame(0), o)
+    with pytest.raises(ValueError):
+        det.detect(img.astype(np.float32))
+    det.close()
+
+
+def test_surf_configs(bs, orc):
+    img = blob_image(320, 240, 10)
+    cfg = bs.ConfigFastHessian(10.0, 3, -1, 2, 15, 5, 3)
+    det = bs.FactoryDetectDescribe.surfStable(cfg, None, None, np.float32)
+    det.detect(img)
+    o = orc.surf(img, dict(detect_threshold=10.0, extract_radius=3, initial_sample_size=2, initial_size=15,
+                           scales_per_octave=5, octaves=3), orc.ORI_SLIDING, orc.DESC_STABILITY)
+    _same(det.readFrame(0), o)
+    det.close()
+    bad = bs.ConfigFastHessian(); bad.extractRadius = 0
+    with pytest.raises(ValueError):
+        bs.FactoryDetectDescribe.surfFast(bad, None, None, np.float32)
+
+
+def test_surf_device_batch_equals_single_frames(bs, orc):
+    import torch
+    from boofcv_b200.synth import blob_images_torch
+    frames = blob_images_torch(320, 240, 5, seed=40, device="cuda")
+    det = bs.FactoryDetectDescribe.surfFast(None, None, None, np.float32)
+    det.setWorkspace(2, 0)                           # 5 frames in chunks of 2: exercises the chunk loop and the carry
+    det.detectBatch(frames)
+    host = frames.cpu().numpy()
+    total = 0
+    for f in range(5):
+        assert np.array_equal(host[f], blob_image(320, 240, 40 + f))      # torch and numpy generators agree
+        r = det.readFrame(f)
+        _same(r, orc.surf_fast(host[f]))
+        total += len(r["x"])
+    assert det.totalFeatures() == total
+    v = det.deviceView()
+    assert v.total == total and v.batch == 5 and v.dof == 64
+    det.close()
+
+
+def test_surf_pool_overflow_is_reported(bs):
+    from boofcv_b200._native import BoofSurfError, BS_ERR_CAPACITY
+    img = blob_image(320, 240, 41)
+    det = bs.FactoryDetectDescribe.surfFast(None, None, None, np.float32)
+    det.setWorkspace(0, 8)
+    with pytest.raises(BoofSurfError) as e:
+        det.detect(img)
+        det.readFrame(0)
+    assert e.value.code == BS_ERR_CAPACITY
+    det.close()
+
+
+# ------------------------------------------------------------------ association
+def _assoc(bs, src, dst, max_err, backwards):
+    a = bs.FactoryAssociation.greedy(bs.ScoreAssociateEuclideanSq_F64(), max_err, backwards)
+    a.setSource(src); a.setDestination(dst); a.associate()
+    return a
+
+
+def test_associate_known_answers(bs):
+    # TestAssociateGreedy.java:38-102 (1-d descriptors; thresholds squared because the GPU score is Euclidean^2)
+    a = _assoc(bs, np.array([1.0, 2, 3, 4]), np.array([3.0, 4, 1, 40]), 0.5 ** 2, False)
+    assert list(a.getPairs()) == [2, -1, 0, 1] and a.getFitQuality()[0] == 0 and a.getFitQuality()[2] == 0
+    assert list(_assoc(bs, np.array([1.0, 2, 3, 4]), np.array([3.0, 4, 1.1, 40]), 10.0 ** 2, False).getPairs())[1] == 2
+    assert list(_assoc(bs, np.array([1.0, 2, 3, 4]), np.array([3.0, 4, 1.1, 40]), 0.1 ** 2, False).getPairs())[1] == -1
+    a = _assoc(bs, np.array([1.0, 2, 3, 8]), np.array([3.0, 4, 1, 10]), 10.0 ** 2, True)
+    assert list(a.getPairs()) == [2, -1, 0, 3] and a.getFitQuality()[3] == 4.0 and a.getFitQuality()[1] == DMAX
+    # inclusive threshold (StandardAssociateDescriptionChecks.java:158-161) and unique destination (:221-239)
+    assert list(_assoc(bs, np.array([1.0]), np.array([1.5]), 0.25, False).getPairs()) == [0]
+    a = _assoc(bs, np.array([1.0, 1.001]), np.array([1.0]), DMAX, True)
+    assert len(a.getMatches()) == 1 and a.uniqueDestination() and a.uniqueSource()
+    assert a.getScoreType() == bs.MatchScoreType.NORM_ERROR
+
+
+def test_associate_errors_and_empty(bs):
+    a = bs.FactoryAssociation.greedy(bs.ScoreAssociateEuclideanSq_F64(), DMAX, True)
+    with pytest.raises(ValueError):
+        a.associate()
+    a.setSource(np.zeros((0, 64)))
+    with pytest.raises(ValueError):
+        a.associate()
+    a.setDestination(descriptors(5))
+    a.associate()
+    assert len(a.getMatches()) == 0 and list(a.getUnassociatedDestination()) == [0, 1, 2, 3, 4]
+    a.setSource(descriptors(3)); a.setDestination(np.zeros((0, 64))); a.associate()
+    assert list(a.getPairs()) == [-1, -1, -1] and list(a.getUnassociatedSource()) == [0, 1, 2]
+
+
+@pytest.mark.parametrize("n,m", [(200, 200), (1000, 777), (65, 3000), (3000, 65), (1, 1)])
+@pytest.mark.parametrize("backwards", [False, True])
+def test_associate_random_bit_exact(bs, orc, n, m, backwards):
+    src, dst = descriptors(n, seed=1234), descriptors(m, seed=4321)
+    a = _assoc(bs, src, dst, DMAX, backwards)
+    pairs, fit = orc.associate(src, dst, DMAX, backwards)
+    assert np.array_equal(a.getPairs(), pairs) and np.array_equal(a.getFitQuality(), fit)
+    matches, us, ud = orc.matches_from_pairs(pairs, fit, m)
+    assert [(x.src, x.dst, x.fitScore) for x in a.getMatches()] == matches
+    assert np.array_equal(a.getUnassociatedSource(), us) and np.array_equal(a.getUnassociatedDestination(), ud)
+
+
+def test_associate_ties_and_duplicates(bs, orc):
+    # duplicate rows on both sides: forward picks the LAST equal minimum, backward rejects non-unique column minima
+    base = descriptors(50, seed=5)
+    src = np.concatenate([base, base[:10], base[20:25]])
+    dst = np.concatenate([base[::-1], base[5:15]])
+    for backwards in (False, True):
+        for thr in (DMAX, 0.5, 0.0):
+            a = _assoc(bs, src, dst, thr, backwards)
+            pairs, fit = orc.associate(src, dst, thr, backwards)
+            assert np.array_equal(a.getPairs(), pairs) and np.array_equal(a.getFitQuality(), fit)
+
+
+def test_associate_planted_and_threshold(bs, orc):
+    src, dst, perm = planted_descriptors(1500, seed=77)
+    a = _assoc(bs, src, dst, 0.05, True)
+    pairs, fit = orc.associate(src, dst, 0.05, True)
+    assert np.array_equal(a.getPairs(), pairs) and np.array_equal(a.getFitQuality(), fit)
+    assert (a.getPairs() == perm).mean() > 0.9
+    a.setMaxScoreThreshold(1e-3); a.associate()
+    pairs, fit = orc.associate(src, dst, 1e-3, True)
+    assert np.array_equal(a.getPairs(), pairs) and np.array_equal(a.getFitQuality(), fit)
+
+
+def test_associate_other_dof(bs, orc):
+    for dof in (1, 7, 64, 100, 192):
+        src, dst = descriptors(300, dof, 1), descriptors(257, dof, 2)
+        a = _assoc(bs, src, dst, DMAX, True)
+        pairs, fit = orc.associate(src, dst, DMAX, True)
+        assert np.array_equal(a.getPairs(), pairs) and np.array_equal(a.getFitQuality(), fit)
+
+
+def test_config1_shifted_pair_end_to_end(bs, orc):
+    # BASELINE config 1: surfFast on 640x480 + greedy vs a shifted copy
+    A, B = shifted_pair(640, 480)
+    det = bs.FactoryDetectDescribe.surfFast(None, None, None, np.float32)
+    det.detect(A); ra = det.readFrame(0)
+    det.detect(B); rb = det.readFrame(0)
+    oa, ob = orc.surf_fast(A), orc.surf_fast(B)
+    _same(ra, oa); _same(rb, ob)
+    a = _assoc(bs, ra["desc"], rb["desc"], DMAX, True)
+    pairs, fit = orc.associate(oa["desc"], ob["desc"], DMAX, True)
+    assert np.array_equal(a.getPairs(), pairs) and np.array_equal(a.getFitQuality(), fit)
+    ms = a.getMatches()
+    dx = np.array([ra["x"][k.src] - rb["x"][k.dst] for k in ms]); dy = np.array([ra["y"][k.src] - rb["y"][k.dst] for k in ms])
+    good = (np.abs(dx - 7) < 1.0) & (np.abs(dy - 3) < 1.0)
+    assert len(ms) > 100 and good.mean() > 0.8
+    det.close()

@@ -1,0 +1,209 @@
+"""GPU parity, stage by stage, through the C ABI vs the CPU oracle.  Bit-exact everywhere (the kernels keep the reference's
+evaluation order); the reference's own tolerance for these stages is 1e-4 (BoofDefaults.TEST_FLOAT_TOL), stated where used.
+Mirrors: TestImplIntegralImageOps, TestIntegralImageFeatureIntensity, GenericNonMaxTests / GenericFeatureDetectorTests,
+GenericOrientationIntegralTests, BaseTestDescribeSurf."""
+import numpy as np
+import pytest
+
+from synth import blob_image
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def st():
+    from boofcv_b200 import stages
+    return stages
+
+
+def _noise(w, h, seed=234, lo=0.0, hi=100.0):
+    return np.random.default_rng(seed).uniform(lo, hi, (h, w)).astype(np.float32)
+
+
+# ------------------------------------------------------------------ integral image
+@pytest.mark.parametrize("shape", [(20, 30), (640, 480), (1920, 1080), (33, 65), (1, 1), (1, 77), (77, 1), (257, 3)])
+def test_integral_f32_bit_exact(st, orc, shape):
+    w, h = shape
+    img = _noise(w, h, 1, 0, 255)
+    assert np.array_equal(st.integral(img), orc.integral(img))
+
+
+@pytest.mark.parametrize("shape", [(20, 30), (641, 479), (1920, 1080)])
+def test_integral_u8_s32_bit_exact(st, orc, shape):
+    w, h = shape
+    rng = np.random.default_rng(2)
+    u8 = rng.integers(0, 256, (h, w), dtype=np.uint8)
+    assert np.array_equal(st.integral(u8), orc.integral(u8))
+    s32 = rng.integers(-2**31, 2**31 - 1, (h, w), dtype=np.int64).astype(np.int32)     # wraps like Java int
+    assert np.array_equal(st.integral(s32), orc.integral(s32))
+
+
+def test_integral_brute_force_definition(st):
+    # TestImplIntegralImageOps.java:69-88 — integral = sum over the rectangle, tol 1e-1, 20x30
+    img = _noise(20, 30, 3)
+    ii = st.integral(img)
+    ref = np.cumsum(np.cumsum(img.astype(np.float64), 0), 1)
+    assert np.abs(ii - ref).max() < 1e-1
+
+
+def test_integral_sub_image(st, orc):
+    big = _noise(100, 80, 4)
+    sub = big[10:50, 20:90]                   # row-strided view == BoofCV sub-image
+    assert np.array_equal(st.integral(sub), orc.integral(np.ascontiguousarray(sub)))
+
+
+def test_integral_empty(st):
+    assert st.integral(np.zeros((0, 0), np.float32)).shape == (0, 0)
+
+
+# ------------------------------------------------------------------ Fast-Hessian intensity
+@pytest.mark.parametrize("skip,size", [(1, 9), (2, 9), (3, 9), (4, 9), (1, 15), (1, 27), (2, 51), (4, 99), (8, 195)])
+def test_hessian_bit_exact_f32(st, orc, skip, size):
+    img = _noise(400, 300, 5, 0, 200)
+    ii = orc.integral(img)
+    g = st.hessian(ii, skip, size)
+    assert np.array_equal(g, orc.hessian(ii, skip, size))
+    # the reference's own check: fast == naive within 1e-4 (TestIntegralImageFeatureIntensity.java:44-89)
+    assert np.abs(g - orc.hessian(ii, skip, size, naive=True)).max() <= 1e-4 * max(1.0, np.abs(g).max())
+
+
+@pytest.mark.parametrize("skip,size", [(1, 9), (2, 15), (4, 27)])
+def test_hessian_bit_exact_s32(st, orc, skip, size):
+    u8 = np.random.default_rng(6).integers(0, 256, (120, 160), dtype=np.uint8)
+    ii = orc.integral(u8)
+    assert np.array_equal(st.hessian(ii, skip, size), orc.hessian(ii, skip, size))
+
+
+def test_hessian_small_image(st, orc):
+    ii = orc.integral(_noise(12, 10, 7))
+    assert np.array_equal(st.hessian(ii, 1, 9), orc.hessian(ii, 1, 9))
+
+
+# ------------------------------------------------------------------ detector
+def _same_detection(g, o):
+    assert len(g["x"]) == len(o["x"])
+    for k in ("x", "y", "scale", "octave", "level", "px", "py", "response"):
+        assert np.array_equal(g[k], o[k]), k
+
+
+@pytest.mark.parametrize("shape,seed", [((400, 300), 234), ((640, 480), 11), ((250, 197), 12)])
+def test_fh_detect_same_points_same_order(st, orc, shape, seed):
+    img = blob_image(shape[0], shape[1], seed)
+    ii = orc.integral(img)
+    g, o = st.fh_detect(ii), orc.fh_detect(ii)
+    assert len(o["x"]) > 50
+    _same_detection(g, o)
+
+
+def test_fh_detect_noise_image(st, orc):
+    # the reference's detector tests use uniform noise (GenericTestsDetectDescribePoint.java:83-211, Random(234))
+    ii = orc.integral(_noise(400, 300, 234))
+    g, o = st.fh_detect(ii), orc.fh_detect(ii)
+    assert len(o["x"]) > 200
+    _same_detection(g, o)
+
+
+@pytest.mark.parametrize("cfg", [dict(extract_radius=1), dict(extract_radius=3, detect_threshold=10.0),
+                                 dict(octaves=2, scales_per_octave=5), dict(initial_sample_size=2, initial_size=15)])
+def test_fh_detect_configs(st, orc, cfg):
+    ii = orc.integral(blob_image(320, 240, 5))
+    _same_detection(st.fh_detect(ii, cfg), orc.fh_detect(ii, cfg))
+
+
+def test_fh_detect_integer_integral(st, orc):
+    u8 = np.clip(blob_image(320, 240, 8), 0, 255).astype(np.uint8)
+    ii = orc.integral(u8)
+    g, o = st.fh_detect(ii), orc.fh_detect(ii)
+    assert len(o["x"]) > 20
+    _same_detection(g, o)
+
+
+def test_fh_detect_too_small_for_any_octave(st):
+    ii = np.ones((20, 20), np.float32).cumsum(0).cumsum(1).astype(np.float32)
+    assert len(st.fh_detect(ii)["x"]) == 0
+
+
+def test_fh_detect_constant_image_has_no_points(st, orc):
+    ii = orc.integral(np.full((200, 200), 50, np.float32))
+    assert len(st.fh_detect(ii)["x"]) == len(orc.fh_detect(ii)["x"]) == 0
+
+
+# ------------------------------------------------------------------ orientation / descriptor
+def _points(orc, img):
+    ii = orc.integral(img)
+    d = orc.fh_detect(ii)
+    return ii, d
+
+
+@pytest.mark.parametrize("variant", ["average", "sliding"])
+def test_orientation_bit_exact(st, orc, variant):
+    ii, d = _points(orc, blob_image(400, 300, 21))
+    cfg = orc.ORI_AVERAGE if variant == "average" else orc.ORI_SLIDING
+    g = st.orientation(ii, d["x"], d["y"], d["scale"], cfg)
+    o = orc.orientation(ii, d["x"], d["y"], d["scale"], cfg)
+    assert len(o) > 50 and np.array_equal(g, o)
+
+
+def test_orientation_unweighted_and_border_points(st, orc):
+    ii = orc.integral(_noise(120, 100, 22))
+    x = np.array([2.0, 117.5, 60.0, 0.0, 119.0]); y = np.array([3.0, 50.0, 98.0, 0.0, 99.0]); s = np.array([1.2, 2.5, 4.0, 1.0, 6.0])
+    for base in (orc.ORI_AVERAGE, orc.ORI_SLIDING):
+        for sigma in (-1.0, 0.0, 2.0):
+            cfg = dict(base, weight_sigma=sigma)
+            assert np.array_equal(st.orientation(ii, x, y, s, cfg), orc.orientation(ii, x, y, s, cfg))
+
+
+def test_orientation_ramp_recovers_angle(st, orc):
+    # GenericOrientationIntegralTests.java:102-143 — intensity ramp along theta -> that angle
+    yy, xx = np.mgrid[0:100, 0:100].astype(np.float64)
+    for theta in np.linspace(-np.pi, np.pi, 9)[1:]:
+        img = (np.cos(theta) * xx + np.sin(theta) * yy + 200).astype(np.float32)
+        ii = orc.integral(img)
+        a = st.orientation(ii, [50.0], [50.0], [2.0])[0]
+        assert abs(np.arctan2(np.sin(a - theta), np.cos(a - theta))) < 0.05
+
+
+@pytest.mark.parametrize("variant", ["speed", "stability"])
+def test_describe_bit_exact(st, orc, variant):
+    ii, d = _points(orc, blob_image(400, 300, 23))
+    ang = orc.orientation(ii, d["x"], d["y"], d["scale"])
+    cfg = orc.DESC_SPEED if variant == "speed" else orc.DESC_STABILITY
+    gd, gw = st.describe(ii, d["x"], d["y"], ang, d["scale"], cfg)
+    od, ow = orc.describe(ii, d["x"], d["y"], ang, d["scale"], cfg)
+    assert len(od) > 50 and np.array_equal(gd, od) and np.array_equal(gw, ow)
+    assert np.allclose(np.linalg.norm(gd, axis=1), 1.0, atol=1e-12)
+
+
+def test_describe_border_and_constant(st, orc):
+    # BaseTestDescribeSurf.java:125-151 — features at the border do not blow up; constant image -> all zeros
+    ii = orc.integral(_noise(80, 60, 24))
+    x = np.array([0.0, 79.0, 40.0, 5.0]); y = np.array([0.0, 59.0, 30.0, 55.0]); s = np.array([1.5, 2.0, 3.0, 4.0])
+    a = np.array([0.0, 1.0, -2.0, 3.0])
+    for cfg in (orc.DESC_SPEED, orc.DESC_STABILITY):
+        gd, gw = st.describe(ii, x, y, a, s, cfg)
+        od, ow = orc.describe(ii, x, y, a, s, cfg)
+        assert np.array_equal(gd, od) and np.array_equal(gw, ow) and np.isfinite(gd).all()
+    flat = orc.integral(np.full((100, 100), 50, np.float32))
+    gd, _ = st.describe(flat, [50.0], [50.0], [0.3], [2.0])
+    assert np.all(gd == 0)
+
+
+def test_describe_ramp_pattern(st, orc):
+    # BaseTestDescribeSurf.java:159-186 — x-ramp: v[i]==v[i+1]>0, v[i+2]==v[i+3]==0 per sub-region
+    yy, xx = np.mgrid[0:100, 0:100]
+    ii = orc.integral((xx * 2.0).astype(np.float32))
+    gd, _ = st.describe(ii, [50.0], [50.0], [0.0], [1.0])
+    v = gd[0].reshape(16, 4)
+    assert np.allclose(v[:, 0], v[:, 1]) and (v[:, 0] > 0).all() and np.allclose(v[:, 2:], 0)
+
+
+def test_describe_integer_integral(st, orc):
+    u8 = np.clip(blob_image(320, 240, 25), 0, 255).astype(np.uint8)
+    ii = orc.integral(u8)
+    d = orc.fh_detect(ii)
+    for ocfg, dcfg in ((orc.ORI_AVERAGE, orc.DESC_SPEED), (orc.ORI_SLIDING, orc.DESC_STABILITY)):
+        ga = st.orientation(ii, d["x"], d["y"], d["scale"], ocfg)
+        assert np.array_equal(ga, orc.orientation(ii, d["x"], d["y"], d["scale"], ocfg))
+        gd, gw = st.describe(ii, d["x"], d["y"], ga, d["scale"], dcfg)
+        od, ow = orc.describe(ii, d["x"], d["y"], ga, d["scale"], dcfg)
+        assert np.array_equal(gd, od) and np.array_equal(gw, ow)
