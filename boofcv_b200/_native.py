@@ -61,6 +61,8 @@ SIGNATURES = {
     "bs_surf_total": (_i, [_vp, C.POINTER(_l)]),
     "bs_surf_read": (_i, [_vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "bs_surf_dof": (_i, [_vp]),
+    "bs_surf_set_timing": (_i, [_vp, _i]),
+    "bs_surf_get_timing": (_i, [_vp, _vp, _vp]),
     "bs_surf_view": (_i, [_vp, C.POINTER(DeviceView)]),
     "bs_integral": (_i, [_i, _i, _vp, _i, _i, _i, _vp]),
     "bs_hessian": (_i, [_i, _i, _vp, _i, _i, _i, _i, _vp]),

@@ -143,6 +143,17 @@ struct bs_surf {
 	int batch = 0;
 	bool pending = false;
 	std::vector<int> h_frame_offset;
+	// optional per-stage timing (CUDA events on the launching stream)
+	bool timing = false;
+	std::vector<cudaEvent_t> ev;
+	size_t ev_used = 0;
+	double stage_ms[BS_N_STAGES] = {0, 0, 0, 0, 0};
+	long stage_launches[BS_N_STAGES] = {0, 0, 0, 0, 0};
+	void mark(cudaStream_t st) {
+		if (!timing) return;
+		if (ev_used == ev.size()) { cudaEvent_t e; BS_CUDA(cudaEventCreate(&e)); ev.push_back(e); }
+		BS_CUDA(cudaEventRecord(ev[ev_used++], st));
+	}
 
 	void ensure(int w, int h, int nbatch);
 	void run(const void* d_pixels, long frame_stride, int stride, int w, int h, int nbatch, cudaStream_t st);
@@ -182,27 +193,36 @@ void bs_surf::run(const void* d_pixels, long frame_stride, int stride, int w, in
 	batch = nbatch;
 	int* fo = d_frame_offset.as<int>();
 	BS_CUDA(cudaMemsetAsync(fo, 0, sizeof(int), st));
+	ev_used = 0;
 	for (int f0 = 0; f0 < nbatch; f0 += chunk) {
 		const int c = std::min(chunk, nbatch - f0);
+		mark(st);
 		if (pixel_type == BS_PIXEL_F32) {
 			const float* in = static_cast<const float*>(d_pixels) + (long)f0 * frame_stride;
 			launch_integral<float, float>(in, frame_stride, stride, d_ii.as<float>(), W, H, c, st);
+			mark(st);
 			launch_hessian_plan<float>(d_ii.as<float>(), plan, d_plan.as<Plan>(), d_inten.as<float>(), c, st);
 		} else if (pixel_type == BS_PIXEL_U8) {
 			const uint8_t* in = static_cast<const uint8_t*>(d_pixels) + (long)f0 * frame_stride;
 			launch_integral<uint8_t, int32_t>(in, frame_stride, stride, d_ii.as<int32_t>(), W, H, c, st);
+			mark(st);
 			launch_hessian_plan<int32_t>(d_ii.as<int32_t>(), plan, d_plan.as<Plan>(), d_inten.as<float>(), c, st);
 		} else {
 			const int32_t* in = static_cast<const int32_t*>(d_pixels) + (long)f0 * frame_stride;
 			launch_integral<int32_t, int32_t>(in, frame_stride, stride, d_ii.as<int32_t>(), W, H, c, st);
+			mark(st);
 			launch_hessian_plan<int32_t>(d_ii.as<int32_t>(), plan, d_plan.as<Plan>(), d_inten.as<float>(), c, st);
 		}
+		mark(st);
 		launch_nms(plan, d_plan.as<Plan>(), d_inten.as<float>(), c, d_stage.as<RawPoint>(), d_counts.as<int>(), st);
+		mark(st);
 		launch_compact(plan, c, f0, d_stage.as<RawPoint>(), d_counts.as<int>(), d_offsets.as<int>(), fo, pool.view, st);
+		mark(st);
 		if (pixel_type == BS_PIXEL_F32)
 			launch_describe<float>(d_ii.as<float>(), W, H, ds.p, ds.tables, pool.view, fo + f0, fo + f0 + c, f0, true, true, st);
 		else
 			launch_describe<int32_t>(d_ii.as<int32_t>(), W, H, ds.p, ds.tables, pool.view, fo + f0, fo + f0 + c, f0, true, true, st);
+		mark(st);
 	}
 	BS_CUDA(cudaEventRecord(done, st));
 	pending = true;
@@ -214,6 +234,15 @@ void bs_surf::finish() {
 	h_frame_offset.assign(batch + 1, 0);
 	BS_CUDA(cudaMemcpy(h_frame_offset.data(), d_frame_offset.p, (size_t)(batch + 1) * sizeof(int), cudaMemcpyDeviceToHost));
 	pending = false;
+	// 6 marks per chunk: [integral][hessian][nms][compact][describe]
+	for (size_t k = 0; k + 5 < ev_used; k += 6)
+		for (int sidx = 0; sidx < BS_N_STAGES; sidx++) {
+			float ms = 0;
+			BS_CUDA(cudaEventElapsedTime(&ms, ev[k + sidx], ev[k + sidx + 1]));
+			stage_ms[sidx] += ms;
+			stage_launches[sidx] += 1;
+		}
+	ev_used = 0;
 }
 
 // ====================================================================================================== extern "C": misc
@@ -278,6 +307,7 @@ int bs_surf_destroy(bs_surf* s) {
 		s->d_counts.release(); s->d_offsets.release(); s->d_frame_offset.release();
 		if (s->h_pinned) cudaFreeHost(s->h_pinned);
 		if (s->done) cudaEventDestroy(s->done);
+		for (cudaEvent_t e : s->ev) cudaEventDestroy(e);
 		if (s->stream) cudaStreamDestroy(s->stream);
 		delete s;
 	});
@@ -292,6 +322,27 @@ int bs_surf_set_workspace(bs_surf* s, int chunk_frames, long pool_features) {
 }
 
 int bs_surf_dof(const bs_surf* s) { return s ? s->ds.p.dof : 0; }
+
+int bs_surf_set_timing(bs_surf* s, int on) {
+	return guarded([&] {
+		if (!s) fail(BS_ERR_ARG, "handle is null");
+		s->finish();
+		s->timing = on != 0;
+		for (int k = 0; k < BS_N_STAGES; k++) { s->stage_ms[k] = 0; s->stage_launches[k] = 0; }
+	});
+}
+
+int bs_surf_get_timing(bs_surf* s, double* stage_ms, long* stage_calls) {
+	return guarded([&] {
+		if (!s) fail(BS_ERR_ARG, "handle is null");
+		DeviceGuard g(s->device);
+		s->finish();
+		for (int k = 0; k < BS_N_STAGES; k++) {
+			if (stage_ms) stage_ms[k] = s->stage_ms[k];
+			if (stage_calls) stage_calls[k] = s->stage_launches[k];
+		}
+	});
+}
 
 int bs_surf_detect_device(bs_surf* s, const void* d_pixels, long frame_stride, int stride, int width, int height, int batch,
                           void* stream) {

@@ -177,6 +177,17 @@ class DetectDescribeSurf:
         r["white"] = r["white"].astype(bool)
         return r
 
+    STAGES = ("integral", "fast_hessian", "nms_refine", "compaction", "orient_describe")
+
+    def setTiming(self, on=True):
+        N.check(N.lib().bs_surf_set_timing(self._h, int(on)))
+
+    def getTiming(self):
+        """{stage: (accumulated device ms, chunks timed)} since setTiming(True)"""
+        ms = (C.c_double * 5)(); calls = (C.c_long * 5)()
+        N.check(N.lib().bs_surf_get_timing(self._h, ms, calls))
+        return {k: (ms[i], calls[i]) for i, k in enumerate(self.STAGES)}
+
     def deviceView(self):
         v = N.DeviceView()
         N.check(N.lib().bs_surf_view(self._h, C.byref(v)))

@@ -122,6 +122,13 @@ int bs_surf_read(bs_surf* s, int frame, double* xy, double* scale, double* angle
                  int32_t* meta, float* response);
 int bs_surf_dof(const bs_surf* s); /* DescriptorInfo.createDescription().size() */
 
+/* Per-stage device time of the detect calls since bs_surf_set_timing(s, 1): CUDA events recorded on the launching stream
+ * around each stage of every chunk.  stage_ms[BS_N_STAGES] = accumulated milliseconds of
+ * {integral, fast-hessian, nms+refine, compaction, orientation+describe}; stage_calls = how many chunks were timed. */
+#define BS_N_STAGES 5
+int bs_surf_set_timing(bs_surf* s, int on);
+int bs_surf_get_timing(bs_surf* s, double* stage_ms, long* stage_calls);
+
 /* Device views of the last result (valid until the next detect on this handle): feature i of frame f is at pool index
  * frame_offset[f] + i.  d_desc is [total][dof] doubles — feed it to bs_assoc_run_device without leaving the GPU. */
 typedef struct bs_surf_device_view {
