@@ -119,3 +119,202 @@ def run_reference(args, rank, world):
         "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }))
+
+
+def run_gpu(args, rank, world, local_rank):
+    import torch
+    import torch.distributed as dist
+    from boofcv_b200 import FactoryDetectDescribe, _native
+    from boofcv_b200.synth import blob_images_torch, blob_image
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    B = args.batch
+    # every rank gets its own batch (weak scaling): frame f of rank r has seed 234 + r*B + f
+    frames = blob_images_torch(W, H, B, seed=234 + rank * B, device=dev)
+    det = FactoryDetectDescribe.surfFast(None, None, None, np.float32, device=local_rank)
+    if args.chunk:
+        det.setWorkspace(args.chunk, 0)
+
+    def barrier():
+        torch.cuda.synchronize(dev)
+        if world > 1:
+            dist.barrier()
+
+    def step():
+        det.detectBatch(frames)
+
+    for _ in range(args.warmup):
+        step()
+    total_features = det.totalFeatures()          # synchronises; also proves the pool did not overflow
+    det.setTiming(True)
+    launches0 = _native.lib().bs_launch_count()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        step()
+    e1.record()
+    barrier()
+    ms = e0.elapsed_time(e1)
+    clocks = sampler.stop() if rank == 0 else None
+    launches = _native.lib().bs_launch_count() - launches0
+    timing = det.getTiming()
+    det.setTiming(False)
+    return dict(torch=torch, dist=dist, dev=dev, det=det, frames=frames, ms=ms, clocks=clocks, launches=launches,
+                timing=timing, total_features=total_features, B=B)
+
+
+def run_e2e(g, steps, sub=32):
+    """Same metric with HOST frames in and HOST feature lists out: per sub-batch, pinned->device copy of the frames,
+    detect, device->pinned copy of (frame offsets, xy, scale, angle, desc, white).  Returns (frames/s, h2d, d2h bytes/step)."""
+    torch, det, dev, B = g["torch"], g["det"], g["dev"], g["B"]
+    import ctypes as C
+    sub = min(sub, B)
+    host = g["frames"].cpu().pin_memory()                       # the step's input lives on the host
+    stage = torch.empty((sub, H, W), dtype=torch.float32, device=dev)
+    cap = int(g["total_features"] * 1.25 / max(B // sub, 1)) + 4096
+    h_desc = torch.empty((cap, 64), dtype=torch.float64).pin_memory()
+    h_misc = torch.empty((cap, 4), dtype=torch.float64).pin_memory()     # x, y, scale, angle
+    h_white = torch.empty(cap, dtype=torch.uint8).pin_memory()
+
+    def view(ptr, n, dtype, shape):
+        nbytes = n * torch.tensor([], dtype=dtype).element_size()
+        buf = (C.c_char * nbytes).from_address(ptr)
+        return torch.frombuffer(buf, dtype=dtype, count=n).view(shape) if n else None
+
+    def one_step():
+        h2d = d2h = 0
+        for f0 in range(0, B, sub):
+            n = min(sub, B - f0)
+            stage[:n].copy_(host[f0:f0 + n], non_blocking=True); h2d += n * H * W * 4
+            det.detectBatch(stage[:n])
+            v = det.deviceView()                              # synchronises this sub-batch; device pointers of the result
+            t = int(v.total)
+            if t > cap:
+                raise RuntimeError("e2e host buffers too small")
+            if t:
+                # device pointers are wrapped without a copy, then copied device->pinned host
+                for (ptr, cols, dst, col0) in ((v.d_xy, 2, h_misc, 0), (v.d_scale, 1, h_misc, 2), (v.d_angle, 1, h_misc, 3)):
+                    src = _wrap(torch, ptr, t * cols, torch.float64, dev).view(t, cols)
+                    dst[:t, col0:col0 + cols].copy_(src, non_blocking=True)
+                h_desc[:t].copy_(_wrap(torch, v.d_desc, t * 64, torch.float64, dev).view(t, 64), non_blocking=True)
+                h_white[:t].copy_(_wrap(torch, v.d_white, t, torch.uint8, dev), non_blocking=True)
+                d2h += t * (64 * 8 + 4 * 8 + 1) + (n + 1) * 4
+            torch.cuda.synchronize(dev)
+        return h2d, d2h
+
+    one_step()                                                  # warm the pinned buffers / allocator
+    torch.cuda.synchronize(dev)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        h2d, d2h = one_step()
+    torch.cuda.synchronize(dev)
+    dt = time.perf_counter() - t0
+    return B * steps / dt, h2d, d2h
+
+
+def _wrap(torch, ptr, count, dtype, dev):
+    """zero-copy torch view of a device pointer owned by libboofsurf (valid until the next detect)."""
+    class _Holder:
+        pass
+    h = _Holder()
+    es = torch.tensor([], dtype=dtype).element_size()
+    h.__cuda_array_interface__ = {"shape": (count,), "typestr": {torch.float64: "<f8", torch.uint8: "|u1"}[dtype],
+                                  "data": (int(ptr), False), "version": 2, "strides": None}
+    return torch.as_tensor(h, device=dev)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="native", choices=["native", "reference"])
+    ap.add_argument("--batch", type=int, default=1024, help="1080p frames per step per GPU (BASELINE configs[1]: 1024)")
+    ap.add_argument("--chunk", type=int, default=0, help="frames per kernel wave (0 = library default)")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-e2e", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "native" else args.warmup
+    rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+
+    import torch
+    import torch.distributed as dist
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    g = run_gpu(args, rank, world, local_rank)
+    dev = g["dev"]
+    ms = torch.tensor([g["ms"]], device=dev, dtype=torch.float64)
+    feats = torch.tensor([float(g["total_features"])], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        dist.all_reduce(feats, op=dist.ReduceOp.SUM)
+    ms = float(ms.item())
+    B = g["B"]
+    value = world * B * args.steps / (ms / 1000.0)
+
+    e2e = None
+    if not args.no_e2e:
+        fps, h2d, d2h = run_e2e(g, max(1, min(args.steps, 2)))
+        t = torch.tensor([fps], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MIN)          # slowest rank bounds the job
+        e2e = {"value": float(t.item()) * world, "unit": UNIT, "h2d_bytes_per_step": int(h2d) * world,
+               "d2h_bytes_per_step": int(d2h) * world}
+
+    if rank == 0:
+        pk, pk_kind = peaks()
+        tm = g["timing"]
+        stage_ms = {k: v[0] for k, v in tm.items()}
+        total_stage = sum(stage_ms.values()) or 1.0
+        hess_ms, hess_calls = tm["fast_hessian"]
+        chunk_frames = B * args.steps / max(hess_calls, 1)
+        # algorithmic bytes of one Fast-Hessian launch: the integral image of its frames, read once (SURVEY.md §8d; the
+        # intensity layers are avoidable traffic and are not counted)
+        alg_bytes = chunk_frames * 4.0 * W * H
+        achieved = alg_bytes / (hess_ms / max(hess_calls, 1) / 1000.0) / 1e9 if hess_ms > 0 else 0.0
+        nfeat = float(feats.item()) / (world * B)
+        pipeline_bytes = 3 * 4.0 * W * H + 545.0 * nfeat
+        out = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "surfFast detect+describe, %d x 1920x1080 GrayF32 per GPU per step (BASELINE configs[1])" % B,
+                       "batch_per_gpu": B, "features_per_frame": nfeat,
+                       "l2": "inputs larger than L2 (%.1f GB batch per step)" % (B * W * H * 4 / 1e9)},
+            "roofline": {"bound": "hbm", "kernel": "hessian_generic_kernel", "achieved": achieved, "peak": pk["hbm_gbs"],
+                         "unit": "GB/s", "frac": achieved / pk["hbm_gbs"], "traffic": None, "peak_kind": pk_kind,
+                         "share_of_step": hess_ms / total_stage,
+                         "pipeline_achieved_gbs": value / world * pipeline_bytes / 1e9,
+                         "pipeline_frac": value / world * pipeline_bytes / 1e9 / pk["hbm_gbs"]},
+            "stage_ms_per_step": {k: v / args.steps for k, v in stage_ms.items()},
+            "gpu_launches": int(g["launches"]),
+            "clocks": g["clocks"],
+        }
+        if e2e:
+            out["e2e"] = e2e
+        if not args.no_cpu:
+            from boofcv_b200.synth import blob_image
+            cores = os.cpu_count() or 1
+            frames = [blob_image(W, H, 234 + i) for i in range(2)]
+            fps, n, _ = cpu_surf_fps(frames, cores, min_seconds=12.0, max_frames=32)
+            out["cpu_baseline"] = {"value": fps, "unit": UNIT, "cores": cores, "kind": "port",
+                                   "sample": "%d x 1080p frames (same generator, seeds 234..235 cycled), surfFast, %d threads; "
+                                             "C++ restatement of the reference Java (no JVM on this box)" % (n, cores)}
+        print(json.dumps(out))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
