@@ -126,7 +126,7 @@ class AssociateGreedyGPU:
         import torch
         n, dof = src.shape; m = dst.shape[0]
         pairs = torch.empty(n, dtype=torch.int32, device=src.device); fit = torch.empty(n, dtype=torch.float64, device=src.device)
-        st = stream if stream is not None else torch.cuda.current_stream(src.device).cuda_stream
+        st = (stream if stream is not None else torch.cuda.current_stream(src.device).cuda_stream) or 1   # 0 -> cudaStreamLegacy
         N.check(N.lib().bs_assoc_run_device(self._h, C.c_void_p(src.data_ptr()), n, C.c_void_p(dst.data_ptr()), m, dof,
                                             C.c_void_p(pairs.data_ptr()), C.c_void_p(fit.data_ptr()), C.c_void_p(st)))
         return pairs, fit

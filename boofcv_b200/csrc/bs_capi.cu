@@ -47,6 +47,14 @@ template <typename F> int guarded(F&& f) {
 
 size_t elem_size(int pixel_type) { return pixel_type == BS_PIXEL_U8 ? 1 : 4; }
 
+// Host->device copy for setup paths.  cudaMemcpy from pageable memory may return once the data is staged, before the DMA
+// has landed; the library's streams are cudaStreamNonBlocking and would not wait for it, so drain the device here.
+void h2d_sync(void* dst, const void* src, size_t bytes) {
+	if (bytes == 0) return;
+	BS_CUDA(cudaMemcpy(dst, src, bytes, cudaMemcpyHostToDevice));
+	BS_CUDA(cudaDeviceSynchronize());
+}
+
 // OrientationIntegralBase ctor (:75-92) + DescribePointSurf / DescribePointSurfMod ctors
 // (DescribePointSurf.java:112-139, DescribePointSurfMod.java:71-99): parameters and weight tables
 struct DescribeSetup {
@@ -95,7 +103,7 @@ struct DescribeSetup {
 		auto up = [](DevBuf& b, const std::vector<double>& v) -> const double* {
 			if (v.empty()) return nullptr;
 			b.reserve(v.size() * sizeof(double));
-			BS_CUDA(cudaMemcpy(b.p, v.data(), v.size() * sizeof(double), cudaMemcpyHostToDevice));
+			h2d_sync(b.p, v.data(), v.size() * sizeof(double));
 			return b.as<double>();
 		};
 		tables.d_ori_w = p.ori_weighted ? up(d_ori_w, ori_w) : nullptr;
@@ -166,7 +174,7 @@ void bs_surf::ensure(int w, int h, int nbatch) {
 	if (w != W || h != H) {
 		plan = make_plan(fh, w, h);
 		d_plan.reserve(sizeof(Plan));
-		BS_CUDA(cudaMemcpy(d_plan.p, &plan, sizeof(Plan), cudaMemcpyHostToDevice));
+		h2d_sync(d_plan.p, &plan, sizeof(Plan));
 		W = w; H = h;
 	}
 	// frames per wave: enough to fill the GPU, small enough to keep the intensity workspace L2-friendly
@@ -452,7 +460,7 @@ void check_device(int device) {
 void upload_ii(DevBuf& d, const void* ii, int width, int height) {
 	if (!ii || width <= 0 || height <= 0) fail(BS_ERR_ARG, "bad integral image");
 	d.reserve((size_t)width * height * 4);
-	BS_CUDA(cudaMemcpy(d.p, ii, (size_t)width * height * 4, cudaMemcpyHostToDevice));
+	h2d_sync(d.p, ii, (size_t)width * height * 4);
 }
 
 // pool with n caller-given points (frame 0) and the range [0,n] on the device
@@ -462,13 +470,14 @@ struct PointSet {
 		pool.reserve(n, dof);
 		std::vector<double> xy((size_t)2 * n), sc(n);
 		for (int i = 0; i < n; i++) { xy[2 * i] = xys[3 * i]; xy[2 * i + 1] = xys[3 * i + 1]; sc[i] = xys[3 * i + 2]; }
-		BS_CUDA(cudaMemcpy(pool.view.xy, xy.data(), xy.size() * 8, cudaMemcpyHostToDevice));
-		BS_CUDA(cudaMemcpy(pool.view.scale, sc.data(), sc.size() * 8, cudaMemcpyHostToDevice));
+		h2d_sync(pool.view.xy, xy.data(), xy.size() * 8);
+		h2d_sync(pool.view.scale, sc.data(), sc.size() * 8);
 		BS_CUDA(cudaMemset(pool.view.frame, 0, (size_t)n * 4));
-		if (angle) BS_CUDA(cudaMemcpy(pool.view.angle, angle, (size_t)n * 8, cudaMemcpyHostToDevice));
+		BS_CUDA(cudaDeviceSynchronize());
+		if (angle) h2d_sync(pool.view.angle, angle, (size_t)n * 8);
 		const int r[2] = {0, n};
 		range.reserve(8);
-		BS_CUDA(cudaMemcpy(range.p, r, 8, cudaMemcpyHostToDevice));
+		h2d_sync(range.p, r, 8);
 	}
 	void release() { pool.release(); range.release(); }
 };
@@ -490,6 +499,7 @@ int bs_integral(int device, int pixel_type, const void* in, int in_stride, int w
 		d_in.reserve((size_t)width * height * es);
 		d_out.reserve((size_t)width * height * 4);
 		BS_CUDA(cudaMemcpy2D(d_in.p, width * es, in, in_stride * es, width * es, height, cudaMemcpyHostToDevice));
+		BS_CUDA(cudaDeviceSynchronize());
 		if (pixel_type == BS_PIXEL_F32) launch_integral<float, float>(d_in.as<float>(), 0, width, d_out.as<float>(), width, height, 1, ts.st);
 		else if (pixel_type == BS_PIXEL_U8) launch_integral<uint8_t, int32_t>(d_in.as<uint8_t>(), 0, width, d_out.as<int32_t>(), width, height, 1, ts.st);
 		else if (pixel_type == BS_PIXEL_S32) launch_integral<int32_t, int32_t>(d_in.as<int32_t>(), 0, width, d_out.as<int32_t>(), width, height, 1, ts.st);
@@ -536,12 +546,13 @@ int bs_fh_detect(int device, int ii_type, const void* ii, int width, int height,
 		upload_ii(d_ii, ii, width, height);
 		Plan plan = make_plan(f, width, height);
 		d_plan.reserve(sizeof(Plan));
-		BS_CUDA(cudaMemcpy(d_plan.p, &plan, sizeof(Plan), cudaMemcpyHostToDevice));
+		h2d_sync(d_plan.p, &plan, sizeof(Plan));
 		d_inten.reserve((size_t)std::max<long>(plan.inten_per_frame, 1) * 4);
 		const size_t nctas = std::max(plan.ctas_per_frame, 1);
 		d_stage.reserve(nctas * NMS_CTA_BLOCKS * sizeof(RawPoint));
 		d_counts.reserve(nctas * 4); d_offsets.reserve(nctas * 4); d_fo.reserve(8);
 		BS_CUDA(cudaMemset(d_fo.p, 0, 8));
+		BS_CUDA(cudaDeviceSynchronize());
 		pool.reserve(std::max(max_out, 1), 1);
 		if (ii_type == BS_PIXEL_F32) launch_hessian_plan<float>(d_ii.as<float>(), plan, d_plan.as<Plan>(), d_inten.as<float>(), 1, ts.st);
 		else launch_hessian_plan<int32_t>(d_ii.as<int32_t>(), plan, d_plan.as<Plan>(), d_inten.as<float>(), 1, ts.st);

@@ -151,7 +151,7 @@ class DetectDescribeSurf:
         if {torch.float32: N.PIXEL_F32, torch.uint8: N.PIXEL_U8, torch.int32: N.PIXEL_S32}.get(frames.dtype) != self._pixel:
             raise ValueError("Unknown input type")
         b, h, w = frames.shape
-        st = stream if stream is not None else torch.cuda.current_stream(frames.device).cuda_stream
+        st = (stream if stream is not None else torch.cuda.current_stream(frames.device).cuda_stream) or 1   # 0 -> cudaStreamLegacy
         N.check(N.lib().bs_surf_detect_device(self._h, C.c_void_p(frames.data_ptr()), frames.stride(0), frames.stride(1),
                                               w, h, b, C.c_void_p(st)))
         self._batch = b

@@ -13,7 +13,8 @@
  *     *_destroy.  Calls on ONE handle must be serialised by the caller (the Java objects are not thread safe either,
  *     F/abst/feature/detdesc/DetectDescribePoint.java:38-40); different handles are independent.
  *   - pointers named d_* are DEVICE pointers on the handle's device; all others are host pointers.
- *   - `stream` arguments are cudaStream_t passed as void* (NULL = the handle's own stream).
+ *   - `stream` arguments are cudaStream_t passed as void*.  NULL = the handle's own (non-blocking) stream; to run on the
+ *     CUDA default stream pass cudaStreamLegacy ((void*)0x1) or cudaStreamPerThread ((void*)0x2).
  *   - there is no CPU fallback: without a CUDA device every *_create fails with BS_ERR_CUDA.
  */
 #ifndef BOOFSURF_H
