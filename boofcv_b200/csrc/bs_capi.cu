@@ -151,18 +151,35 @@ struct bs_surf {
 	int batch = 0;
 	bool pending = false;
 	std::vector<int> h_frame_offset;
-	// optional per-stage timing (CUDA events on the launching stream)
+	// optional per-stage timing: a pair of CUDA events on the launching stream around every stage launch
 	bool timing = false;
-	std::vector<cudaEvent_t> ev;
-	size_t ev_used = 0;
+	std::vector<cudaEvent_t> ev;          // event pool
+	std::vector<int> ev_stage;            // stage of pair k (events 2k, 2k+1)
 	double stage_ms[BS_N_STAGES] = {0, 0, 0, 0, 0};
 	long stage_launches[BS_N_STAGES] = {0, 0, 0, 0, 0};
-	void mark(cudaStream_t st) {
+	void stage_begin(int stage, cudaStream_t st) {
 		if (!timing) return;
-		if (ev_used == ev.size()) { cudaEvent_t e; BS_CUDA(cudaEventCreate(&e)); ev.push_back(e); }
-		BS_CUDA(cudaEventRecord(ev[ev_used++], st));
+		while (ev.size() < 2 * (ev_stage.size() + 1)) { cudaEvent_t e; BS_CUDA(cudaEventCreate(&e)); ev.push_back(e); }
+		BS_CUDA(cudaEventRecord(ev[2 * ev_stage.size()], st));
+		ev_stage.push_back(stage);
+	}
+	void stage_end(cudaStream_t st) {
+		if (!timing) return;
+		BS_CUDA(cudaEventRecord(ev[2 * ev_stage.size() - 1], st));
+	}
+	void collect_timing() {
+		for (size_t k = 0; k < ev_stage.size(); k++) {
+			float ms = 0;
+			BS_CUDA(cudaEventElapsedTime(&ms, ev[2 * k], ev[2 * k + 1]));
+			stage_ms[ev_stage[k]] += ms;
+			stage_launches[ev_stage[k]] += 1;
+		}
+		ev_stage.clear();
 	}
 
+	int group = 0;
+	template <typename TI, typename TII>
+	void run_typed(const void* d_pixels, long frame_stride, int stride, int nbatch, cudaStream_t st);
 	void ensure(int w, int h, int nbatch);
 	void run(const void* d_pixels, long frame_stride, int stride, int w, int h, int nbatch, cudaStream_t st);
 	void finish();
@@ -182,7 +199,12 @@ void bs_surf::ensure(int w, int h, int nbatch) {
 	c = std::min(c, nbatch);
 	chunk = std::max(c, 1);
 	const size_t px = (size_t)W * H;
-	d_ii.reserve(px * 4 * chunk);
+	// integral group: a multiple of the chunk, about 32 frames (or ~1 GB of integral images, whichever is smaller)
+	int gframes = (int)std::max<size_t>(1, std::min<size_t>(32, ((size_t)1 << 30) / (px * 4)));
+	gframes = std::max(chunk, (gframes / chunk) * chunk);
+	group = std::min(std::max(gframes, chunk), std::max(nbatch, 1));
+	if (group < chunk) group = chunk;
+	d_ii.reserve(px * 4 * group);
 	d_inten.reserve((size_t)std::max<long>(plan.inten_per_frame, 1) * 4 * chunk);
 	const size_t nctas = (size_t)std::max(plan.ctas_per_frame, 1) * chunk;
 	d_stage.reserve(nctas * NMS_CTA_BLOCKS * sizeof(RawPoint));
@@ -193,45 +215,50 @@ void bs_surf::ensure(int w, int h, int nbatch) {
 	pool.reserve(cap, ds.p.dof);
 }
 
-// the whole pipeline for a device-resident batch, chunk by chunk, all on `st`
+// the whole pipeline for a device-resident batch, all on `st`.  Two granularities:
+//   group  (<= group frames): integral images.  The ordered float scan only has rows x frames / columns x frames worth of
+//          parallelism, so it wants many frames per launch;
+//   chunk  (<= chunk frames): Fast-Hessian -> NMS -> compaction -> describe.  Small, so that the intensity layers a chunk
+//          writes are still in L2 when the NMS kernel reads them.
+template <typename TI, typename TII>
+void bs_surf::run_typed(const void* d_pixels, long frame_stride, int stride, int nbatch, cudaStream_t st) {
+	int* fo = d_frame_offset.as<int>();
+	TII* ii = d_ii.as<TII>();
+	const long px = (long)W * H;
+	for (int g0 = 0; g0 < nbatch; g0 += group) {
+		const int g = std::min(group, nbatch - g0);
+		const TI* in = static_cast<const TI*>(d_pixels) + (long)g0 * frame_stride;
+		stage_begin(0, st);
+		launch_integral<TI, TII>(in, frame_stride, stride, ii, W, H, g, st);
+		stage_end(st);
+		for (int f0 = g0; f0 < g0 + g; f0 += chunk) {
+			const int c = std::min(chunk, g0 + g - f0);
+			const TII* cii = ii + (long)(f0 - g0) * px;
+			stage_begin(1, st);
+			launch_hessian_plan<TII>(cii, plan, d_plan.as<Plan>(), d_inten.as<float>(), c, st);
+			stage_end(st);
+			stage_begin(2, st);
+			launch_nms(plan, d_plan.as<Plan>(), d_inten.as<float>(), c, d_stage.as<RawPoint>(), d_counts.as<int>(), st);
+			stage_end(st);
+			stage_begin(3, st);
+			launch_compact(plan, c, f0, d_stage.as<RawPoint>(), d_counts.as<int>(), d_offsets.as<int>(), fo, pool.view, st);
+			stage_end(st);
+			stage_begin(4, st);
+			launch_describe<TII>(cii, W, H, ds.p, ds.tables, pool.view, fo + f0, fo + f0 + c, f0, true, true, st);
+			stage_end(st);
+		}
+	}
+}
+
 void bs_surf::run(const void* d_pixels, long frame_stride, int stride, int w, int h, int nbatch, cudaStream_t st) {
 	if (nbatch <= 0) fail(BS_ERR_ARG, "batch must be >= 1");
 	if (stride < w) fail(BS_ERR_ARG, "stride must be >= width");
 	ensure(w, h, nbatch);
 	batch = nbatch;
-	int* fo = d_frame_offset.as<int>();
-	BS_CUDA(cudaMemsetAsync(fo, 0, sizeof(int), st));
-	ev_used = 0;
-	for (int f0 = 0; f0 < nbatch; f0 += chunk) {
-		const int c = std::min(chunk, nbatch - f0);
-		mark(st);
-		if (pixel_type == BS_PIXEL_F32) {
-			const float* in = static_cast<const float*>(d_pixels) + (long)f0 * frame_stride;
-			launch_integral<float, float>(in, frame_stride, stride, d_ii.as<float>(), W, H, c, st);
-			mark(st);
-			launch_hessian_plan<float>(d_ii.as<float>(), plan, d_plan.as<Plan>(), d_inten.as<float>(), c, st);
-		} else if (pixel_type == BS_PIXEL_U8) {
-			const uint8_t* in = static_cast<const uint8_t*>(d_pixels) + (long)f0 * frame_stride;
-			launch_integral<uint8_t, int32_t>(in, frame_stride, stride, d_ii.as<int32_t>(), W, H, c, st);
-			mark(st);
-			launch_hessian_plan<int32_t>(d_ii.as<int32_t>(), plan, d_plan.as<Plan>(), d_inten.as<float>(), c, st);
-		} else {
-			const int32_t* in = static_cast<const int32_t*>(d_pixels) + (long)f0 * frame_stride;
-			launch_integral<int32_t, int32_t>(in, frame_stride, stride, d_ii.as<int32_t>(), W, H, c, st);
-			mark(st);
-			launch_hessian_plan<int32_t>(d_ii.as<int32_t>(), plan, d_plan.as<Plan>(), d_inten.as<float>(), c, st);
-		}
-		mark(st);
-		launch_nms(plan, d_plan.as<Plan>(), d_inten.as<float>(), c, d_stage.as<RawPoint>(), d_counts.as<int>(), st);
-		mark(st);
-		launch_compact(plan, c, f0, d_stage.as<RawPoint>(), d_counts.as<int>(), d_offsets.as<int>(), fo, pool.view, st);
-		mark(st);
-		if (pixel_type == BS_PIXEL_F32)
-			launch_describe<float>(d_ii.as<float>(), W, H, ds.p, ds.tables, pool.view, fo + f0, fo + f0 + c, f0, true, true, st);
-		else
-			launch_describe<int32_t>(d_ii.as<int32_t>(), W, H, ds.p, ds.tables, pool.view, fo + f0, fo + f0 + c, f0, true, true, st);
-		mark(st);
-	}
+	BS_CUDA(cudaMemsetAsync(d_frame_offset.p, 0, sizeof(int), st));
+	if (pixel_type == BS_PIXEL_F32) run_typed<float, float>(d_pixels, frame_stride, stride, nbatch, st);
+	else if (pixel_type == BS_PIXEL_U8) run_typed<uint8_t, int32_t>(d_pixels, frame_stride, stride, nbatch, st);
+	else run_typed<int32_t, int32_t>(d_pixels, frame_stride, stride, nbatch, st);
 	BS_CUDA(cudaEventRecord(done, st));
 	pending = true;
 }
@@ -242,15 +269,7 @@ void bs_surf::finish() {
 	h_frame_offset.assign(batch + 1, 0);
 	BS_CUDA(cudaMemcpy(h_frame_offset.data(), d_frame_offset.p, (size_t)(batch + 1) * sizeof(int), cudaMemcpyDeviceToHost));
 	pending = false;
-	// 6 marks per chunk: [integral][hessian][nms][compact][describe]
-	for (size_t k = 0; k + 5 < ev_used; k += 6)
-		for (int sidx = 0; sidx < BS_N_STAGES; sidx++) {
-			float ms = 0;
-			BS_CUDA(cudaEventElapsedTime(&ms, ev[k + sidx], ev[k + sidx + 1]));
-			stage_ms[sidx] += ms;
-			stage_launches[sidx] += 1;
-		}
-	ev_used = 0;
+	collect_timing();
 }
 
 // ====================================================================================================== extern "C": misc
