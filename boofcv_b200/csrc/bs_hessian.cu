@@ -152,23 +152,45 @@ hessian_generic_kernel(const T* __restrict__ ii_all, const Plan* __restrict__ pl
 	}
 }
 
+}  // namespace bs
+#include "bs_hessian_tile.cuh"
+namespace bs {
+
+// octaves the shared-memory kernel is specialised for (float integral, FH-9 default sizes); returns true if launched
+template <typename T>
+static bool try_tiled(const T*, const Plan&, int, int, float*, int, cudaStream_t) { return false; }
+template <>
+bool try_tiled<float>(const float* d_ii, const Plan& plan, int first, int ns, float* d_inten, int batch, cudaStream_t st) {
+	if (ns != 4) return false;
+	const Layer& L0 = plan.layers[first];
+	const int step = plan.layers[first + 1].size - L0.size;
+	for (int i = 1; i < ns; i++)
+		if (plan.layers[first + i].size != L0.size + i * step) return false;
+	if (L0.skip == 1 && L0.size == 9 && step == 6) { launch_hessian_tile<1, 9, 6, 4, 64, 16>(d_ii, plan, first, d_inten, batch, st); return true; }
+	if (L0.skip == 2 && L0.size == 15 && step == 12) { launch_hessian_tile<2, 15, 12, 4, 32, 16>(d_ii, plan, first, d_inten, batch, st); return true; }
+	return false;
+}
+
 template <typename T>
 void launch_hessian_plan(const T* d_ii, const Plan& plan, const Plan* d_plan, float* d_inten, int batch, cudaStream_t st) {
+	if (batch <= 0) return;
 	OctaveTiles ot{};
-	int tiles = 0, o = -1;
-	for (int l = 0; l < plan.n_layers; l++) {
-		const Layer& L = plan.layers[l];
-		if (L.index == 0) {
-			o++;
-			ot.first_layer[o] = l; ot.n_scales[o] = 0; ot.tile_begin[o] = tiles;
+	int tiles = 0, o = 0;
+	for (int l = 0; l < plan.n_layers;) {
+		int ns = 1;
+		while (l + ns < plan.n_layers && plan.layers[l + ns].index != 0) ns++;
+		if (!try_tiled<T>(d_ii, plan, l, ns, d_inten, batch, st)) {
+			const Layer& L = plan.layers[l];
+			ot.first_layer[o] = l; ot.n_scales[o] = ns; ot.tile_begin[o] = tiles;
 			ot.tiles_x[o] = div_up(L.w, HT_X);
 			tiles += ot.tiles_x[o] * div_up(L.h, HT_Y);
+			o++;
 		}
-		ot.n_scales[o]++;
+		l += ns;
 	}
-	ot.n_oct = o + 1;
-	ot.tile_begin[ot.n_oct] = tiles;
-	if (tiles == 0 || batch <= 0) return;
+	ot.n_oct = o;
+	ot.tile_begin[o] = tiles;
+	if (tiles == 0) return;
 	BS_LAUNCH((hessian_generic_kernel<T>), dim3(tiles, batch), HT_X * HT_Y, 0, st, d_ii, d_plan, ot, d_inten);
 }
 template void launch_hessian_plan<float>(const float*, const Plan&, const Plan*, float*, int, cudaStream_t);
