@@ -144,7 +144,7 @@ struct bs_surf {
 	int chunk_req = 0; long pool_req = 0;
 	int W = 0, H = 0, chunk = 0;
 	Plan plan{};
-	DevBuf d_plan, d_in, d_ii, d_inten, d_stage, d_counts, d_offsets, d_frame_offset;
+	DevBuf d_plan, d_in, d_ii, d_inten, d_stage, d_counts, d_offsets, d_frame_offset, d_keys, d_keep;
 	PoolBufs pool;
 	void* h_pinned = nullptr; size_t h_pinned_bytes = 0;
 	// last result
@@ -210,6 +210,10 @@ void bs_surf::ensure(int w, int h, int nbatch) {
 	d_stage.reserve(nctas * NMS_CTA_BLOCKS * sizeof(RawPoint));
 	d_counts.reserve(nctas * sizeof(int));
 	d_offsets.reserve(nctas * sizeof(int));
+	if (plan.max_per_level > 0) {          // SelectNBestFeatures scratch: one key and one flag per NMS block
+		d_keys.reserve(nctas * NMS_CTA_BLOCKS * sizeof(unsigned));
+		d_keep.reserve(nctas * NMS_CTA_BLOCKS);
+	}
 	d_frame_offset.reserve((size_t)(nbatch + 1) * sizeof(int));
 	long cap = pool_req > 0 ? pool_req : (long)nbatch * std::max<long>((long)px / 64, 256);
 	pool.reserve(cap, ds.p.dof);
@@ -238,7 +242,8 @@ void bs_surf::run_typed(const void* d_pixels, long frame_stride, int stride, int
 			launch_hessian_plan<TII>(cii, plan, d_plan.as<Plan>(), d_inten.as<float>(), c, st);
 			stage_end(st);
 			stage_begin(2, st);
-			launch_nms(plan, d_plan.as<Plan>(), d_inten.as<float>(), c, d_stage.as<RawPoint>(), d_counts.as<int>(), st);
+			launch_nms(plan, d_plan.as<Plan>(), d_inten.as<float>(), c, d_stage.as<RawPoint>(), d_counts.as<int>(), d_keys.as<unsigned>(),
+			           d_keep.as<unsigned char>(), st);
 			stage_end(st);
 			stage_begin(3, st);
 			launch_compact(plan, c, f0, d_stage.as<RawPoint>(), d_counts.as<int>(), d_offsets.as<int>(), fo, pool.view, st);
@@ -308,8 +313,6 @@ int bs_surf_create(int device, const bs_fh_cfg* fh, const bs_ori_cfg* ori, const
 		if (desc) d = *desc; else bs_desc_cfg_default(&d, ori ? ori->variant : 0);
 		if (ori) o = *ori; else bs_ori_cfg_default(&o, d.variant);
 		check_fh_cfg(f); check_ori_cfg(o); check_desc_cfg(d);
-		if (f.max_features_per_scale > 0)
-			fail(BS_ERR_ARG, "maxFeaturesPerScale > 0 (SelectNBestFeatures) is not implemented yet; use -1");
 		int ndev = 0;
 		BS_CUDA(cudaGetDeviceCount(&ndev));
 		if (device < 0 || device >= ndev) fail(BS_ERR_ARG, "no such CUDA device");
@@ -331,7 +334,7 @@ int bs_surf_destroy(bs_surf* s) {
 		cudaDeviceSynchronize();
 		s->ds.release(); s->pool.release();
 		s->d_plan.release(); s->d_in.release(); s->d_ii.release(); s->d_inten.release(); s->d_stage.release();
-		s->d_counts.release(); s->d_offsets.release(); s->d_frame_offset.release();
+		s->d_counts.release(); s->d_offsets.release(); s->d_frame_offset.release(); s->d_keys.release(); s->d_keep.release();
 		if (s->h_pinned) cudaFreeHost(s->h_pinned);
 		if (s->done) cudaEventDestroy(s->done);
 		for (cudaEvent_t e : s->ev) cudaEventDestroy(e);
@@ -555,12 +558,11 @@ int bs_fh_detect(int device, int ii_type, const void* ii, int width, int height,
 		bs_fh_cfg f;
 		if (cfg) f = *cfg; else bs_fh_cfg_default(&f);
 		check_fh_cfg(f);
-		if (f.max_features_per_scale > 0) fail(BS_ERR_ARG, "maxFeaturesPerScale > 0 is not implemented yet");
 		if (max_out < 0) fail(BS_ERR_ARG, "max_out must be >= 0");
 		check_device(device);
 		DeviceGuard g(device);
 		TempStream ts;
-		DevBuf d_ii, d_plan, d_inten, d_stage, d_counts, d_offsets, d_fo;
+		DevBuf d_ii, d_plan, d_inten, d_stage, d_counts, d_offsets, d_fo, d_keys, d_keep;
 		PoolBufs pool;
 		upload_ii(d_ii, ii, width, height);
 		Plan plan = make_plan(f, width, height);
@@ -570,12 +572,14 @@ int bs_fh_detect(int device, int ii_type, const void* ii, int width, int height,
 		const size_t nctas = std::max(plan.ctas_per_frame, 1);
 		d_stage.reserve(nctas * NMS_CTA_BLOCKS * sizeof(RawPoint));
 		d_counts.reserve(nctas * 4); d_offsets.reserve(nctas * 4); d_fo.reserve(8);
+		if (plan.max_per_level > 0) { d_keys.reserve(nctas * NMS_CTA_BLOCKS * 4); d_keep.reserve(nctas * NMS_CTA_BLOCKS); }
 		BS_CUDA(cudaMemset(d_fo.p, 0, 8));
 		BS_CUDA(cudaDeviceSynchronize());
 		pool.reserve(std::max(max_out, 1), 1);
 		if (ii_type == BS_PIXEL_F32) launch_hessian_plan<float>(d_ii.as<float>(), plan, d_plan.as<Plan>(), d_inten.as<float>(), 1, ts.st);
 		else launch_hessian_plan<int32_t>(d_ii.as<int32_t>(), plan, d_plan.as<Plan>(), d_inten.as<float>(), 1, ts.st);
-		launch_nms(plan, d_plan.as<Plan>(), d_inten.as<float>(), 1, d_stage.as<RawPoint>(), d_counts.as<int>(), ts.st);
+		launch_nms(plan, d_plan.as<Plan>(), d_inten.as<float>(), 1, d_stage.as<RawPoint>(), d_counts.as<int>(), d_keys.as<unsigned>(),
+		           d_keep.as<unsigned char>(), ts.st);
 		launch_compact(plan, 1, 0, d_stage.as<RawPoint>(), d_counts.as<int>(), d_offsets.as<int>(), d_fo.as<int>(), pool.view, ts.st);
 		BS_CUDA(cudaStreamSynchronize(ts.st));
 		int fo[2];
@@ -593,6 +597,7 @@ int bs_fh_detect(int device, int ii_type, const void* ii, int width, int height,
 			if (response) BS_CUDA(cudaMemcpy(response, pool.view.response, (size_t)k * 4, cudaMemcpyDeviceToHost));
 		}
 		d_ii.release(); d_plan.release(); d_inten.release(); d_stage.release(); d_counts.release(); d_offsets.release(); d_fo.release();
+		d_keys.release(); d_keep.release();
 		pool.release();
 	});
 }

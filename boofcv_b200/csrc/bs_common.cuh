@@ -137,8 +137,9 @@ struct Pool {
 	long cap;
 };
 
+// d_keys / d_keep: [batch][ctas_per_frame * NMS_CTA_BLOCKS] scratch, needed only when plan.max_per_level > 0
 void launch_nms(const Plan& plan, const Plan* d_plan, const float* d_inten, int batch, RawPoint* d_stage, int* d_cta_counts,
-                cudaStream_t st);
+                unsigned* d_keys, unsigned char* d_keep, cudaStream_t st);
 // Exclusive scan of the per-CTA counts of the chunk's frames (frame0 .. frame0+batch), continuing from
 // d_frame_offset[frame0]; writes d_frame_offset[frame0+1 .. frame0+batch] and the per-CTA pool offsets, then gathers the
 // staged points into the pool in (frame, octave, level, block-row, block-column) order.

@@ -344,17 +344,36 @@ describe_kernel(const T* __restrict__ ii_all, int W, int H, DescribeParams P, De
 				orientation_sample(ii_all + sj.frame * frame_words, W, H, P, t_ori, sj.og, k, dX, dY, dY + S.ori_n);
 			}
 			__syncthreads();
-			if (me.f >= 0) {
+			if (P.ori_variant == 0) {
+				// average: the serial sums of all slots at once, lane 2j sums x and lane 2j+1 sums y of slot j (sample order),
+				// instead of one mostly idle warp per feature
+				if (warp == 0) {
+					const int j = lane >> 1;
+					const bool on = lane < 2 * DESC_WARPS && slots[j < DESC_WARPS ? j : 0].f >= 0;
+					double total = 0.0;
+					if (on) {
+						const double* src = reinterpret_cast<const double*>(scratch + (size_t)j * S.per_warp) + (lane & 1) * S.ori_n;
+						for (int k = 0; k < S.ori_n; k++) total += src[k];
+					}
+					const double Dy = __shfl_down_sync(0xffffffffu, total, 1);
+					if (on && (lane & 1) == 0) {
+						const double angle = sm_atan2(Dy, total);
+						slots[j].angle = angle;
+						pool.angle[slots[j].f] = angle;
+					}
+				}
+			} else if (me.f >= 0) {
 				double* dX = reinterpret_cast<double*>(mine);
 				double* dY = dX + S.ori_n;
 				double* ang = dY + S.ori_n;
 				const double angle = orientation_reduce(P, dX, dY, ang, reinterpret_cast<int*>(ang + S.ori_n));
 				if (lane == 0) { me.angle = angle; pool.angle[me.f] = angle; }
 			}
-			__syncwarp();
+			__syncthreads();                   // angles are in the slots
 		}
 		if (do_describe) {
-			if (lane == 0 && me.f >= 0) { me.c = sm_cos(me.angle); me.s = sm_sin(me.angle); }
+			// cos/sin of all slots by the first lanes of warp 0
+			if (warp == 0 && lane < DESC_WARPS && slots[lane].f >= 0) { slots[lane].c = sm_cos(slots[lane].angle); slots[lane].s = sm_sin(slots[lane].angle); }
 			__syncthreads();                   // every slot has cos/sin; the orientation scratch is free
 			for (int idx = tid; idx < live * S.desc_g2; idx += NT) {
 				const int j = (int)(((float)idx + 0.5f) * inv_desc), k = idx - j * S.desc_g2;

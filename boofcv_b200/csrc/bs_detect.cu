@@ -33,9 +33,17 @@ __device__ __forceinline__ bool scale_neighbour_ok(const float* __restrict__ img
 	return true;
 }
 
+enum { NMS_PLAIN = 0, NMS_KEYS = 1, NMS_KEPT = 2 };
+
+// order-preserving map float -> uint32 (larger response = larger key); 0 is never produced by a finite value
+__device__ __forceinline__ unsigned response_key(float v) {
+	const unsigned b = __float_as_uint(v);
+	return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+}
+
 __global__ void __launch_bounds__(NMS_CTA_BLOCKS)
 nms_kernel(const Plan* __restrict__ plan, const float* __restrict__ inten_all, RawPoint* __restrict__ stage_all,
-           int* __restrict__ counts_all) {
+           int* __restrict__ counts_all, int mode, unsigned* __restrict__ keys_all, const unsigned char* __restrict__ keep_all) {
 	__shared__ int warp_counts[NMS_CTA_BLOCKS / 32];
 	const int cta = blockIdx.x, frame = blockIdx.y;
 	int lv = 0;
@@ -50,20 +58,22 @@ nms_kernel(const Plan* __restrict__ plan, const float* __restrict__ inten_all, R
 
 	bool found = false;
 	RawPoint pt;
+	// the extractor: at most one strict maximum per block
+	bool ok = false;
+	int peakX = 0, peakY = 0;
+	float peak = -FLT_MAX;
 	if (bid < V.nbx * V.nby) {
 		const int by = bid / V.nbx, bx = bid - by * V.nbx;
 		const int endX = w - V.border, endY = h - V.border;
 		const int x0 = V.border + bx * step, y0 = V.border + by * step;
 		const int x1 = min(x0 + step, endX), y1 = min(y0 + step, endY);
 		// searchBlock: first strict maximum in raster order
-		int peakX = 0, peakY = 0;
-		float peak = -FLT_MAX;
 		for (int y = y0; y < y1; y++)
 			for (int x = x0; x < x1; x++) {
 				const float v = __ldg(mid + (long)y * w + x);
 				if (v > peak) { peak = v; peakX = x; peakY = y; }
 			}
-		bool ok = peak >= plan->threshold && peak != FLT_MAX;
+		ok = peak >= plan->threshold && peak != FLT_MAX;
 		if (ok) {
 			// checkLocalMax: strictly greater than everything else in the (2r+1)^2 window clamped to the image
 			const int wx0 = max(peakX - radius, 0), wx1 = min(peakX + radius, w - 1);
@@ -74,31 +84,37 @@ nms_kernel(const Plan* __restrict__ plan, const float* __restrict__ inten_all, R
 					if (v >= peak && !(x == peakX && y == peakY)) { ok = false; break; }
 				}
 		}
-		if (ok) {
-			// findLocalScaleSpaceMax :248-294
-			const int ir = V.border + radius;
-			if (peakX < ir || peakX >= w - ir || peakY < ir || peakY >= h - ir) ok = false;
-		}
-		if (ok) {
-			const float* lower = inten + plan->layers[V.lower].offset;
-			const float* upper = inten + plan->layers[V.upper].offset;
-			const float val = __ldg(mid + (long)peakY * w + peakX);
-			if (scale_neighbour_ok(lower, w, h, val, peakX, peakY) && scale_neighbour_ok(upper, w, h, val, peakX, peakY)) {
-				const long c = (long)peakY * w + peakX;
-				const float peakXf = poly_peak(__ldg(mid + c - 1), val, __ldg(mid + c + 1));
-				const float peakYf = poly_peak(__ldg(mid + c - w), val, __ldg(mid + c + w));
-				const float peakS = poly_peak(__ldg(lower + c), val, __ldg(upper + c));
-				const float interpX = ((float)peakX + peakXf) * (float)M.skip;
-				const float interpY = ((float)peakY + peakYf) * (float)M.skip;
-				const float interpS = (float)V.level_size + peakS * (float)V.level_step;
-				pt.x = (double)interpX; pt.y = (double)interpY;
-				pt.scale = 1.2 * (double)interpS / 9.0;
-				pt.response = val;
-				pt.px = (int16_t)peakX; pt.py = (int16_t)peakY;
-				pt.octave = (int16_t)V.octave; pt.level = (int16_t)V.level;
-				pt.pad = 0;
-				found = true;
-			}
+	}
+	if (mode != NMS_PLAIN) {
+		// SelectNBestFeatures works on the extractor's output, i.e. on what passed the tests above (whole CTA takes this branch)
+		const long slot = ((long)frame * plan->ctas_per_frame + cta) * NMS_CTA_BLOCKS + threadIdx.x;
+		if (mode == NMS_KEYS) { keys_all[slot] = ok ? response_key(peak) : 0u; return; }
+		ok = ok && keep_all[slot] != 0;
+	}
+	if (ok) {
+		// findLocalScaleSpaceMax :248-294
+		const int ir = V.border + radius;
+		if (peakX < ir || peakX >= w - ir || peakY < ir || peakY >= h - ir) ok = false;
+	}
+	if (ok) {
+		const float* lower = inten + plan->layers[V.lower].offset;
+		const float* upper = inten + plan->layers[V.upper].offset;
+		const float val = __ldg(mid + (long)peakY * w + peakX);
+		if (scale_neighbour_ok(lower, w, h, val, peakX, peakY) && scale_neighbour_ok(upper, w, h, val, peakX, peakY)) {
+			const long c = (long)peakY * w + peakX;
+			const float peakXf = poly_peak(__ldg(mid + c - 1), val, __ldg(mid + c + 1));
+			const float peakYf = poly_peak(__ldg(mid + c - w), val, __ldg(mid + c + w));
+			const float peakS = poly_peak(__ldg(lower + c), val, __ldg(upper + c));
+			const float interpX = ((float)peakX + peakXf) * (float)M.skip;
+			const float interpY = ((float)peakY + peakYf) * (float)M.skip;
+			const float interpS = (float)V.level_size + peakS * (float)V.level_step;
+			pt.x = (double)interpX; pt.y = (double)interpY;
+			pt.scale = 1.2 * (double)interpS / 9.0;
+			pt.response = val;
+			pt.px = (int16_t)peakX; pt.py = (int16_t)peakY;
+			pt.octave = (int16_t)V.octave; pt.level = (int16_t)V.level;
+			pt.pad = 0;
+			found = true;
 		}
 	}
 	// rank inside the CTA in thread (= block-raster) order
@@ -117,10 +133,110 @@ nms_kernel(const Plan* __restrict__ plan, const float* __restrict__ inten_all, R
 	if (threadIdx.x == 0) counts_all[(long)frame * plan->ctas_per_frame + cta] = total;
 }
 
+// ---------------------------------------------------------------- SelectNBestFeatures
+// Reference: SelectNBestFeatures.process (F/alg/feature/detect/extract/SelectNBestFeatures.java:51-93), applied per detect
+// level to the extractor's maxima before the scale-space test (FastHessianFeatureDetector.java:257-260).  If a level has more
+// than N maxima the N with the largest response survive.  Which of several EQUAL responses survives is decided by ddogleg's
+// QuickSelect in the reference (unpinned); here ties go to the earlier block (the rule the parity tests check), and
+// the survivors keep their block-raster order.
+// One CTA per (level, frame): 4-pass radix select of the N-th largest key, then an ordered pass that hands out the quota of
+// keys equal to it.
+constexpr int SELECT_THREADS = 1024;
+
+__global__ void __launch_bounds__(SELECT_THREADS)
+select_nbest_kernel(const Plan* __restrict__ plan, const unsigned* __restrict__ keys_all, unsigned char* __restrict__ keep_all) {
+	__shared__ unsigned hist[256];
+	__shared__ unsigned s_prefix, s_remaining, s_total;
+	__shared__ int warp_sums[SELECT_THREADS / 32];
+	__shared__ int s_carry;
+	const int lv = blockIdx.x, frame = blockIdx.y;
+	const int cta0 = plan->levels[lv].cta_begin;
+	const int cta1 = lv + 1 < plan->n_levels ? plan->levels[lv + 1].cta_begin : plan->ctas_per_frame;
+	const long first = ((long)frame * plan->ctas_per_frame + cta0) * NMS_CTA_BLOCKS;
+	const int n = (cta1 - cta0) * NMS_CTA_BLOCKS;
+	const unsigned* keys = keys_all + first;
+	unsigned char* keep = keep_all + first;
+	const unsigned N = (unsigned)plan->max_per_level;
+	const int tid = threadIdx.x;
+
+	// number of maxima on the level
+	if (tid == 0) s_total = 0;
+	__syncthreads();
+	unsigned mine = 0;
+	for (int i = tid; i < n; i += SELECT_THREADS) mine += keys[i] != 0u;
+	if (mine) atomicAdd(&s_total, mine);
+	__syncthreads();
+	if (s_total <= N) {
+		for (int i = tid; i < n; i += SELECT_THREADS) keep[i] = keys[i] != 0u;
+		return;
+	}
+	// radix select, most significant byte first: after the loop s_prefix is the N-th largest key and s_remaining how many
+	// keys EQUAL to it are still wanted
+	if (tid == 0) { s_prefix = 0; s_remaining = N; }
+	for (int shift = 24; shift >= 0; shift -= 8) {
+		if (tid < 256) hist[tid] = 0;
+		__syncthreads();
+		const unsigned prefix = s_prefix;
+		const unsigned himask = shift == 24 ? 0u : (0xffffffffu << (shift + 8));
+		for (int i = tid; i < n; i += SELECT_THREADS) {
+			const unsigned k = keys[i];
+			if (k != 0u && (k & himask) == prefix) atomicAdd(&hist[(k >> shift) & 255u], 1u);
+		}
+		__syncthreads();
+		if (tid == 0) {
+			unsigned want = s_remaining;
+			int b = 255;
+			for (; b > 0; b--) {
+				if (hist[b] >= want) break;
+				want -= hist[b];
+			}
+			s_prefix = prefix | ((unsigned)b << shift);
+			s_remaining = want;
+		}
+		__syncthreads();
+	}
+	const unsigned T = s_prefix;
+	const int quota = (int)s_remaining;
+	// ordered pass: keys above T survive; of the keys equal to T the first `quota` in block order
+	if (tid == 0) s_carry = 0;
+	__syncthreads();
+	const int lane = tid & 31, warp = tid >> 5;
+	for (int i0 = 0; i0 < n; i0 += SELECT_THREADS) {
+		const int i = i0 + tid;
+		const unsigned k = i < n ? keys[i] : 0u;
+		const bool eq = k != 0u && k == T;
+		const unsigned ballot = __ballot_sync(0xffffffffu, eq);
+		if (lane == 0) warp_sums[warp] = __popc(ballot);
+		__syncthreads();
+		int before = s_carry, chunk = 0;
+		for (int w = 0; w < SELECT_THREADS / 32; w++) {
+			const int c = warp_sums[w];
+			if (w < warp) before += c;
+			chunk += c;
+		}
+		before += __popc(ballot & ((1u << lane) - 1u));
+		if (i < n) keep[i] = (k != 0u && k > T) || (eq && before < quota);
+		__syncthreads();
+		if (tid == 0) s_carry += chunk;
+		__syncthreads();
+	}
+}
+
 void launch_nms(const Plan& plan, const Plan* d_plan, const float* d_inten, int batch, RawPoint* d_stage, int* d_cta_counts,
-                cudaStream_t st) {
+                unsigned* d_keys, unsigned char* d_keep, cudaStream_t st) {
 	if (plan.ctas_per_frame == 0 || batch <= 0) return;
-	BS_LAUNCH(nms_kernel, dim3(plan.ctas_per_frame, batch), NMS_CTA_BLOCKS, 0, st, d_plan, d_inten, d_stage, d_cta_counts);
+	const dim3 grid(plan.ctas_per_frame, batch);
+	if (plan.max_per_level > 0) {
+		if (!d_keys || !d_keep) fail(BS_ERR_STATE, "n-best selection needs its workspace");
+		BS_LAUNCH(nms_kernel, grid, NMS_CTA_BLOCKS, 0, st, d_plan, d_inten, d_stage, d_cta_counts, (int)NMS_KEYS, d_keys,
+		          (const unsigned char*)d_keep);
+		BS_LAUNCH(select_nbest_kernel, dim3(plan.n_levels, batch), SELECT_THREADS, 0, st, d_plan, (const unsigned*)d_keys, d_keep);
+		BS_LAUNCH(nms_kernel, grid, NMS_CTA_BLOCKS, 0, st, d_plan, d_inten, d_stage, d_cta_counts, (int)NMS_KEPT, d_keys,
+		          (const unsigned char*)d_keep);
+	} else {
+		BS_LAUNCH(nms_kernel, grid, NMS_CTA_BLOCKS, 0, st, d_plan, d_inten, d_stage, d_cta_counts, (int)NMS_PLAIN, (unsigned*)nullptr,
+		          (const unsigned char*)nullptr);
+	}
 }
 
 // ---------------------------------------------------------------- ordered compaction

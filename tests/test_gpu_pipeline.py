@@ -87,6 +87,23 @@ def test_surf_configs(bs, orc):
         bs.FactoryDetectDescribe.surfFast(bad, None, None, np.float32)
 
 
+def test_surf_max_features_per_scale(bs, orc):
+    # ExampleFeatureSurf.java:62 style configuration: ConfigFastHessian(0, 2, 200, 2, 9, 4, 4); here 25 per scale, batch of 3
+    import torch
+    from boofcv_b200.synth import blob_images_torch
+    cfg = bs.ConfigFastHessian(1.0, 2, 25, 1, 9, 4, 4)
+    det = bs.FactoryDetectDescribe.surfFast(cfg, None, None, np.float32)
+    frames = blob_images_torch(400, 300, 3, seed=70, device="cuda")
+    det.setWorkspace(2, 0)
+    det.detectBatch(frames)
+    host = frames.cpu().numpy()
+    for f in range(3):
+        o = orc.surf(host[f], dict(max_features_per_scale=25), orc.ORI_AVERAGE, orc.DESC_SPEED)
+        assert 0 < len(o["x"]) <= 25 * 8
+        _same(det.readFrame(f), o)
+    det.close()
+
+
 def test_surf_device_batch_equals_single_frames(bs, orc):
     import torch
     from boofcv_b200.synth import blob_images_torch

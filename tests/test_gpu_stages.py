@@ -128,6 +128,34 @@ def test_fh_detect_constant_image_has_no_points(st, orc):
     assert len(st.fh_detect(ii)["x"]) == len(orc.fh_detect(ii)["x"]) == 0
 
 
+@pytest.mark.parametrize("n", [1, 5, 40, 300])
+def test_fh_detect_n_best_per_scale(st, orc, n):
+    # SelectNBestFeatures (SelectNBestFeatures.java:51-93) through ConfigFastHessian.maxFeaturesPerScale
+    ii = orc.integral(blob_image(640, 480, 21))
+    cfg = dict(max_features_per_scale=n)
+    g, o = st.fh_detect(ii, cfg), orc.fh_detect(ii, cfg)
+    assert len(o["x"]) > 0
+    _same_detection(g, o)
+    full = orc.fh_detect(ii)
+    if n <= 40:
+        assert len(o["x"]) < len(full["x"])           # the limit really cut something
+
+
+def test_fh_detect_n_best_with_equal_responses(st, orc):
+    # a periodic pattern gives many maxima with bit-identical responses: the tie rule (earlier block wins) is exercised
+    tile = blob_image(48, 48, 3)
+    ii = orc.integral(np.tile(tile, (6, 8)).astype(np.float32))
+    for n in (3, 17, 60):
+        cfg = dict(max_features_per_scale=n, octaves=2)
+        _same_detection(st.fh_detect(ii, cfg), orc.fh_detect(ii, cfg))
+    u8 = np.tile(np.clip(tile, 0, 255).astype(np.uint8), (6, 8))
+    ii = orc.integral(u8)                              # integer integral: exact ties everywhere
+    for n in (2, 25):
+        cfg = dict(max_features_per_scale=n)
+        g, o = st.fh_detect(ii, cfg), orc.fh_detect(ii, cfg)
+        _same_detection(g, o)
+
+
 # ------------------------------------------------------------------ orientation / descriptor
 def _points(orc, img):
     ii = orc.integral(img)
