@@ -167,64 +167,30 @@ def run_gpu(args, rank, world, local_rank):
                 timing=timing, total_features=total_features, B=B)
 
 
-def run_e2e(g, steps, sub=32):
-    """Same metric with HOST frames in and HOST feature lists out: per sub-batch, pinned->device copy of the frames,
-    detect, device->pinned copy of (frame offsets, xy, scale, angle, desc, white).  Returns (frames/s, h2d, d2h bytes/step)."""
+def run_e2e(g, steps):
+    """Same metric through the host-facing call (bs_surf_detect_host_batch): the step's frames live in pinned HOST memory,
+    the feature lists (frame offsets, xy, scale, angle, desc, white) land in pinned HOST memory; the library overlaps the
+    copies of one 32-frame sub-batch with the kernels of the other.  Returns (frames/s, h2d, d2h bytes per step)."""
     torch, det, dev, B = g["torch"], g["det"], g["dev"], g["B"]
-    import ctypes as C
-    sub = min(sub, B)
+    from boofcv_b200 import HostFeatureBuffers
     host = g["frames"].cpu().pin_memory()                       # the step's input lives on the host
-    stage = torch.empty((sub, H, W), dtype=torch.float32, device=dev)
-    cap = int(g["total_features"] * 1.25 / max(B // sub, 1)) + 4096
-    h_desc = torch.empty((cap, 64), dtype=torch.float64).pin_memory()
-    h_misc = torch.empty((cap, 4), dtype=torch.float64).pin_memory()     # x, y, scale, angle
-    h_white = torch.empty(cap, dtype=torch.uint8).pin_memory()
-
-    def view(ptr, n, dtype, shape):
-        nbytes = n * torch.tensor([], dtype=dtype).element_size()
-        buf = (C.c_char * nbytes).from_address(ptr)
-        return torch.frombuffer(buf, dtype=dtype, count=n).view(shape) if n else None
+    cap = int(g["total_features"] * 1.1) + 4096
+    out = HostFeatureBuffers(B, cap, 64, pinned=True)
 
     def one_step():
-        h2d = d2h = 0
-        for f0 in range(0, B, sub):
-            n = min(sub, B - f0)
-            stage[:n].copy_(host[f0:f0 + n], non_blocking=True); h2d += n * H * W * 4
-            det.detectBatch(stage[:n])
-            v = det.deviceView()                              # synchronises this sub-batch; device pointers of the result
-            t = int(v.total)
-            if t > cap:
-                raise RuntimeError("e2e host buffers too small")
-            if t:
-                # device pointers are wrapped without a copy, then copied device->pinned host
-                for (ptr, cols, dst, col0) in ((v.d_xy, 2, h_misc, 0), (v.d_scale, 1, h_misc, 2), (v.d_angle, 1, h_misc, 3)):
-                    src = _wrap(torch, ptr, t * cols, torch.float64, dev).view(t, cols)
-                    dst[:t, col0:col0 + cols].copy_(src, non_blocking=True)
-                h_desc[:t].copy_(_wrap(torch, v.d_desc, t * 64, torch.float64, dev).view(t, 64), non_blocking=True)
-                h_white[:t].copy_(_wrap(torch, v.d_white, t, torch.uint8, dev), non_blocking=True)
-                d2h += t * (64 * 8 + 4 * 8 + 1) + (n + 1) * 4
-            torch.cuda.synchronize(dev)
-        return h2d, d2h
+        det.detectHostBatch(host, out)
+        return B * H * W * 4, out.total * (64 * 8 + 4 * 8 + 1) + (B + 1) * 4
 
-    one_step()                                                  # warm the pinned buffers / allocator
+    one_step()                                                  # warm: worker handles, workspaces
     torch.cuda.synchronize(dev)
     t0 = time.perf_counter()
     for _ in range(steps):
-        h2d, d2h = one_step()
-    torch.cuda.synchronize(dev)
+        h2d, d2h = one_step()                                   # synchronous: returns when the results are on the host
     dt = time.perf_counter() - t0
+    if out.total != g["total_features"]:
+        raise RuntimeError("host path found %d features, device path %d" % (out.total, g["total_features"]))
+    out.close()
     return B * steps / dt, h2d, d2h
-
-
-def _wrap(torch, ptr, count, dtype, dev):
-    """zero-copy torch view of a device pointer owned by libboofsurf (valid until the next detect)."""
-    class _Holder:
-        pass
-    h = _Holder()
-    es = torch.tensor([], dtype=dtype).element_size()
-    h.__cuda_array_interface__ = {"shape": (count,), "typestr": {torch.float64: "<f8", torch.uint8: "|u1"}[dtype],
-                                  "data": (int(ptr), False), "version": 2, "strides": None}
-    return torch.as_tensor(h, device=dev)
 
 
 def main():
@@ -284,6 +250,14 @@ def main():
         achieved = alg_bytes / (hess_ms / max(hess_calls, 1) / 1000.0) / 1e9 if hess_ms > 0 else 0.0
         nfeat = float(feats.item()) / (world * B)
         pipeline_bytes = 3 * 4.0 * W * H + 545.0 * nfeat
+        # DRAM bytes of the dominant kernel from the committed ncu --set full capture (profiles/traffic.json), per launch
+        traffic, kernel_name = None, "hessian_tile_kernel<1,9,6,4,64,16>"
+        try:
+            tj = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "traffic.json")))
+            traffic = float(tj["fast_hessian_dram_bytes_per_frame"]) * chunk_frames
+            kernel_name = tj.get("kernel", kernel_name)
+        except Exception:
+            pass
         out = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -291,8 +265,9 @@ def main():
             "config": {"workload": "surfFast detect+describe, %d x 1920x1080 GrayF32 per GPU per step (BASELINE configs[1])" % B,
                        "batch_per_gpu": B, "features_per_frame": nfeat,
                        "l2": "inputs larger than L2 (%.1f GB batch per step)" % (B * W * H * 4 / 1e9)},
-            "roofline": {"bound": "hbm", "kernel": "hessian_generic_kernel", "achieved": achieved, "peak": pk["hbm_gbs"],
-                         "unit": "GB/s", "frac": achieved / pk["hbm_gbs"], "traffic": None, "peak_kind": pk_kind,
+            "roofline": {"bound": "hbm", "kernel": kernel_name, "achieved": achieved, "peak": pk["hbm_gbs"],
+                         "unit": "GB/s", "frac": achieved / pk["hbm_gbs"], "traffic": traffic, "peak_kind": pk_kind,
+                         "frames_per_launch": chunk_frames, "algorithmic_bytes_per_launch": alg_bytes,
                          "share_of_step": hess_ms / total_stage,
                          "pipeline_achieved_gbs": value / world * pipeline_bytes / 1e9,
                          "pipeline_frac": value / world * pipeline_bytes / 1e9 / pk["hbm_gbs"]},

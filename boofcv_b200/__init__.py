@@ -4,5 +4,6 @@ The package holds only what that path needs: csrc/ (hand-written CUDA kernels + 
 libboofsurf.so), the ctypes binding (_native), the stage-level calls (stages) and the mirror of the reference's factory /
 interface layer (surf, associate).  There is no CPU fallback anywhere in this package."""
 from .surf import (FactoryDetectDescribe, ConfigFastHessian, ConfigAverageIntegral, ConfigSlidingIntegral,  # noqa: F401
-                   ConfigSurfDescribe, BrightFeature, AssociatedIndex, Point2D_F64, DetectDescribeSurf)
+                   ConfigSurfDescribe, BrightFeature, AssociatedIndex, Point2D_F64, DetectDescribeSurf,
+                   HostFeatureBuffers)
 from .associate import FactoryAssociation, ScoreAssociateEuclideanSq_F64, MatchScoreType, AssociateGreedyGPU  # noqa: F401

@@ -57,6 +57,9 @@ SIGNATURES = {
     "bs_surf_set_workspace": (_i, [_vp, _i, _l]),
     "bs_surf_detect": (_i, [_vp, _vp, _i, _i, _i, _i]),
     "bs_surf_detect_device": (_i, [_vp, _vp, _l, _i, _i, _i, _i, _vp]),
+    "bs_surf_detect_host_batch": (_i, [_vp, _vp, _l, _i, _i, _i, _i, _l, _vp, _vp, _vp, _vp, _vp, _vp, C.POINTER(_l)]),
+    "bs_host_register": (_i, [_vp, C.c_size_t]),
+    "bs_host_unregister": (_i, [_vp]),
     "bs_surf_count": (_i, [_vp, _i, _pi]),
     "bs_surf_total": (_i, [_vp, C.POINTER(_l)]),
     "bs_surf_read": (_i, [_vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),

@@ -177,6 +177,8 @@ struct bs_surf {
 		ev_stage.clear();
 	}
 
+	bs_surf* lane[2] = {nullptr, nullptr};     // bs_surf_detect_host_batch: two workers, each with its own stream and workspace
+
 	int group = 0;
 	template <typename TI, typename TII>
 	void run_typed(const void* d_pixels, long frame_stride, int stride, int nbatch, cudaStream_t st);
@@ -194,8 +196,8 @@ void bs_surf::ensure(int w, int h, int nbatch) {
 		h2d_sync(d_plan.p, &plan, sizeof(Plan));
 		W = w; H = h;
 	}
-	// frames per wave: enough to fill the GPU, small enough to keep the intensity workspace L2-friendly
-	int c = chunk_req > 0 ? chunk_req : 4;
+	// frames per wave: measured 2723 / 3389 / 3680 / 3667+ frames/s at 1 / 4 / 8 / 16 (1080p): launches must be big enough to fill 148 SMs
+	int c = chunk_req > 0 ? chunk_req : 16;
 	c = std::min(c, nbatch);
 	chunk = std::max(c, 1);
 	const size_t px = (size_t)W * H;
@@ -329,6 +331,10 @@ int bs_surf_create(int device, const bs_fh_cfg* fh, const bs_ori_cfg* ori, const
 
 int bs_surf_destroy(bs_surf* s) {
 	if (!s) return BS_OK;
+	for (int k = 0; k < 2; k++) {
+		if (s->lane[k]) bs_surf_destroy(s->lane[k]);
+		s->lane[k] = nullptr;
+	}
 	return guarded([&] {
 		DeviceGuard g(s->device);
 		cudaDeviceSynchronize();
@@ -380,6 +386,91 @@ int bs_surf_detect_device(bs_surf* s, const void* d_pixels, long frame_stride, i
 		if (!s || !d_pixels) fail(BS_ERR_ARG, "null argument");
 		DeviceGuard g(s->device);
 		s->run(d_pixels, frame_stride, stride, width, height, batch, stream ? static_cast<cudaStream_t>(stream) : s->stream);
+	});
+}
+
+int bs_host_register(void* p, size_t bytes) {
+	return guarded([&] {
+		if (!p || bytes == 0) fail(BS_ERR_ARG, "null or empty host range");
+		BS_CUDA(cudaHostRegister(p, bytes, cudaHostRegisterPortable));
+	});
+}
+int bs_host_unregister(void* p) {
+	return guarded([&] {
+		if (!p) fail(BS_ERR_ARG, "null pointer");
+		BS_CUDA(cudaHostUnregister(p));
+	});
+}
+
+int bs_surf_detect_host_batch(bs_surf* s, const void* pixels, long frame_stride, int stride, int width, int height, int batch,
+                              long cap, int32_t* frame_offset, double* xy, double* scale, double* angle, double* desc,
+                              uint8_t* white, long* total) {
+	return guarded([&] {
+		if (!s || !pixels || !frame_offset) fail(BS_ERR_ARG, "null argument");
+		if (width <= 0 || height <= 0) fail(BS_ERR_ARG, "image width and height must be positive");
+		if (batch < 0 || cap < 0 || stride < width) fail(BS_ERR_ARG, "bad batch/cap/stride");
+		if (frame_stride < (long)stride * (height - 1) + width) fail(BS_ERR_ARG, "frames overlap");
+		DeviceGuard g(s->device);
+		s->finish();
+		for (int k = 0; k < 2; k++)
+			if (!s->lane[k]) {
+				bs_surf* h = nullptr;
+				if (bs_surf_create(s->device, &s->fh, &s->ori, &s->desc, s->pixel_type, &h) != BS_OK) fail(BS_ERR_CUDA, last_error_cstr());
+				s->lane[k] = h;
+			}
+		const size_t es = elem_size(s->pixel_type);
+		const int dof = s->ds.p.dof;
+		const int sub = 32;                        // frames per lane turn = one integral group
+		frame_offset[0] = 0;
+		long base = 0;                             // features of the frames drained so far
+		struct Turn { int first = 0, n = 0; bool busy = false; } turn[2];
+		auto drain = [&](int k) {
+			Turn& t = turn[k];
+			if (!t.busy) return;
+			bs_surf* h = s->lane[k];
+			h->finish();                           // waits for this lane only; the other lane keeps the GPU busy
+			const int* fo = h->h_frame_offset.data();
+			const long found = fo[t.n];
+			if (found > h->pool.view.cap) fail(BS_ERR_CAPACITY, "feature pool overflow inside a sub-batch (bs_surf_set_workspace pool_features)");
+			for (int i = 0; i < t.n; i++) frame_offset[t.first + i + 1] = (int32_t)(base + fo[i + 1]);
+			const long room = std::max<long>(0, std::min<long>(found, cap - base));
+			if (room > 0) {
+				const Pool& p = h->pool.view;
+				cudaStream_t st = h->stream;   // ordered before this lane's next turn, concurrent with the other lane
+				if (xy) BS_CUDA(cudaMemcpyAsync(xy + 2 * base, p.xy, (size_t)room * 16, cudaMemcpyDeviceToHost, st));
+				if (scale) BS_CUDA(cudaMemcpyAsync(scale + base, p.scale, (size_t)room * 8, cudaMemcpyDeviceToHost, st));
+				if (angle) BS_CUDA(cudaMemcpyAsync(angle + base, p.angle, (size_t)room * 8, cudaMemcpyDeviceToHost, st));
+				if (desc) BS_CUDA(cudaMemcpyAsync(desc + (size_t)dof * base, p.desc, (size_t)room * dof * 8, cudaMemcpyDeviceToHost, st));
+				if (white) BS_CUDA(cudaMemcpyAsync(white + base, p.white, (size_t)room, cudaMemcpyDeviceToHost, st));
+			}
+			base += found;
+			t.busy = false;
+		};
+		int k = 0;
+		for (int f0 = 0; f0 < batch; f0 += sub, k ^= 1) {
+			drain(k);                              // normally a no-op: this lane was drained right after the other one started
+			bs_surf* h = s->lane[k];
+			h->chunk_req = s->chunk_req; h->pool_req = s->pool_req;
+			const int n = std::min(sub, batch - f0);
+			const size_t dense = (size_t)width * height * es;
+			h->d_in.reserve(dense * sub);
+			const char* src = static_cast<const char*>(pixels) + (size_t)f0 * frame_stride * es;
+			if (stride == width && frame_stride == (long)width * height) {
+				BS_CUDA(cudaMemcpyAsync(h->d_in.p, src, dense * n, cudaMemcpyHostToDevice, h->stream));
+			} else {
+				for (int i = 0; i < n; i++)
+					BS_CUDA(cudaMemcpy2DAsync(static_cast<char*>(h->d_in.p) + dense * i, (size_t)width * es, src + (size_t)i * frame_stride * es,
+					                          (size_t)stride * es, (size_t)width * es, height, cudaMemcpyHostToDevice, h->stream));
+			}
+			h->run(h->d_in.p, (long)width * height, width, width, height, n, h->stream);
+			turn[k].first = f0; turn[k].n = n; turn[k].busy = true;
+			drain(k ^ 1);                          // results of the previous turn go home while this one computes
+		}
+		drain(k); drain(k ^ 1);                    // k: the lane started before the last one (or nothing), then the last one
+		for (int j = 0; j < 2; j++) BS_CUDA(cudaStreamSynchronize(s->lane[j]->stream));
+		if (total) *total = base;
+		s->batch = 0; s->pending = false;
+		if (base > cap) fail(BS_ERR_CAPACITY, "more features than the host buffers hold");
 	});
 }
 

@@ -109,6 +109,38 @@ def _p(a):
 
 
 # ------------------------------------------------------------------------------------------------ DetectDescribePoint
+class HostFeatureBuffers:
+    """Host-side result arrays of detectHostBatch, page-locked through the library (bs_host_register) so that the
+    device->host copies run asynchronously.  frame f owns rows frame_offset[f]:frame_offset[f+1] of every array."""
+
+    def __init__(self, batch, cap, dof=64, pinned=True):
+        self.cap = int(cap); self.dof = int(dof); self.total = 0; self.batch = 0
+        self.frame_offset = np.zeros(batch + 1, np.int32)
+        self.xy = np.zeros((self.cap, 2)); self.scale = np.zeros(self.cap); self.angle = np.zeros(self.cap)
+        self.desc = np.zeros((self.cap, self.dof)); self.white = np.zeros(self.cap, np.uint8)
+        self._pinned = []
+        if pinned:
+            for a in (self.xy, self.scale, self.angle, self.desc, self.white):
+                if a.nbytes:
+                    N.check(N.lib().bs_host_register(C.c_void_p(a.ctypes.data), a.nbytes))
+                    self._pinned.append(a)
+
+    def ptr(self, name):
+        return C.c_void_p(getattr(self, name).ctypes.data)
+
+    def frame(self, f):
+        b, e = int(self.frame_offset[f]), int(self.frame_offset[f + 1])
+        return dict(xy=self.xy[b:e], x=self.xy[b:e, 0], y=self.xy[b:e, 1], scale=self.scale[b:e], angle=self.angle[b:e],
+                    desc=self.desc[b:e], white=self.white[b:e].astype(bool))
+
+    def close(self):
+        for a in self._pinned:
+            N.lib().bs_host_unregister(C.c_void_p(a.ctypes.data))
+        self._pinned = []
+
+    __del__ = close
+
+
 class DetectDescribeSurf:
     """WrapDetectDescribeSurf over a bs_surf handle.  Not thread safe, like the reference (recycled storage)."""
 
@@ -156,6 +188,33 @@ class DetectDescribeSurf:
                                               w, h, b, C.c_void_p(st)))
         self._batch = b
         self._res = None
+
+    # --- batched, HOST frames in / HOST feature lists out (bs_surf_detect_host_batch): copies overlap compute inside the
+    # library.  frames: numpy [B,H,W] or a CPU torch tensor (pinned memory makes the copies asynchronous); out: a
+    # HostFeatureBuffers sized for at least the expected number of features.
+    def detectHostBatch(self, frames, out):
+        if hasattr(frames, "data_ptr"):
+            b, h, w = frames.shape
+            ptr, fs, rs = frames.data_ptr(), frames.stride(0), frames.stride(1)
+            if frames.stride(2) != 1 or frames.is_cuda:
+                raise ValueError("frames must be a CPU tensor [batch, height, width] with unit column stride")
+            import torch
+            code = {torch.float32: N.PIXEL_F32, torch.uint8: N.PIXEL_U8, torch.int32: N.PIXEL_S32}.get(frames.dtype)
+        else:
+            frames = np.ascontiguousarray(frames)
+            b, h, w = frames.shape
+            ptr, fs, rs = frames.ctypes.data, h * w, w
+            code = {np.dtype(np.float32): N.PIXEL_F32, np.dtype(np.uint8): N.PIXEL_U8, np.dtype(np.int32): N.PIXEL_S32}.get(frames.dtype)
+        if code != self._pixel:
+            raise ValueError("Unknown input type")
+        if out.dof != self._dof or len(out.frame_offset) < b + 1:
+            raise ValueError("host buffers do not fit this detector / batch")
+        total = C.c_long(0)
+        N.check(N.lib().bs_surf_detect_host_batch(self._h, C.c_void_p(ptr), fs, rs, w, h, b, out.cap, out.ptr("frame_offset"), out.ptr("xy"),
+                                                  out.ptr("scale"), out.ptr("angle"), out.ptr("desc"), out.ptr("white"), C.byref(total)))
+        out.total = total.value; out.batch = b
+        self._batch = 0; self._res = None
+        return out
 
     def totalFeatures(self):
         n = C.c_long(0)

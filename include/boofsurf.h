@@ -20,6 +20,7 @@
 #ifndef BOOFSURF_H
 #define BOOFSURF_H
 
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -109,6 +110,23 @@ int bs_surf_detect(bs_surf* s, const void* pixels, int start_index, int stride, 
  * elements apart.  Asynchronous on `stream`; the first accessor call synchronises. */
 int bs_surf_detect_device(bs_surf* s, const void* d_pixels, long frame_stride, int stride, int width, int height,
                           int batch, void* stream);
+
+/* Batched detect+describe with HOST frames in and HOST feature lists out — what a JVM caller with a list of images uses.
+ * Each image is what DetectDescribePoint.detect (DetectDescribePoint.java:32-46, WrapDetectDescribeSurf.java:75-96) would
+ * receive; the results are what getLocation/getRadius(scale)/getOrientation/getDescription would return, frame after frame.
+ * The batch is cut into sub-batches of 32 frames that alternate between two internal workers, each with its own stream:
+ * the host->device copy and the device->host copy of one sub-batch overlap the kernels of the other.  Pinned host memory
+ * (bs_host_register) makes those copies truly asynchronous; pageable memory works but serialises.
+ *   pixels: frame f starts at element f*frame_stride, rows are `stride` elements apart.
+ *   frame_offset[batch+1]: features of frame f are [frame_offset[f], frame_offset[f+1]).
+ *   xy[cap][2], scale[cap], angle[cap], desc[cap][dof], white[cap]: any of them may be NULL (not copied).
+ *   *total: features found.  BS_ERR_CAPACITY if total > cap (the first cap entries are valid). */
+int bs_surf_detect_host_batch(bs_surf* s, const void* pixels, long frame_stride, int stride, int width, int height,
+                              int batch, long cap, int32_t* frame_offset, double* xy, double* scale, double* angle,
+                              double* desc, uint8_t* white, long* total);
+/* cudaHostRegister / cudaHostUnregister for callers without a CUDA binding of their own (JNI direct buffers) */
+int bs_host_register(void* p, size_t bytes);
+int bs_host_unregister(void* p);
 
 /* getNumberOfFeatures() :112-114 for one frame of the last detect; bs_surf_total = sum over frames (and the number the
  * pool would have needed when BS_ERR_CAPACITY was returned). */

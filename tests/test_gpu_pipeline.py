@@ -232,3 +232,62 @@ def test_config1_shifted_pair_end_to_end(bs, orc):
     good = (np.abs(dx - 7) < 1.0) & (np.abs(dy - 3) < 1.0)
     assert len(ms) > 100 and good.mean() > 0.8
     det.close()
+
+
+def test_sharded_association_device_steps(bs, orc):
+    # the three C-ABI steps of a row-sharded association, three shards simulated on one GPU: forward per
+    # shard with global row offsets, merge of the stacked column partials, validation per shard == single-process result
+    import torch
+    from boofcv_b200 import parallel
+    rng = np.random.default_rng(77)
+    n, m, dof = 301, 257, 64
+    dst = rng.normal(size=(m, dof)); src = rng.normal(size=(n, dof))
+    src[:100] = dst[rng.permutation(m)[:100]] + 0.01 * rng.normal(size=(100, dof))
+    src[7] = src[3]; dst[11] = dst[10]
+    op, of = orc.associate(src, dst, 40.0, True)
+    assoc = bs.FactoryAssociation.greedy(bs.ScoreAssociateEuclideanSq_F64(), 40.0, True)
+    be = parallel.GpuAssocBackend(assoc)
+    d_dst = torch.from_numpy(dst).cuda()
+    spans = [parallel.shard_range(n, r, 3) for r in range(3)]
+    fwd = [be.forward(torch.from_numpy(src[b:e].copy()).cuda(), b, d_dst) for b, e in spans]
+    cmin, cfirst, clast = be.merge(torch.stack([f[2] for f in fwd]), torch.stack([f[3] for f in fwd]), torch.stack([f[4] for f in fwd]))
+    pairs, fit = [], []
+    for (b, e), f in zip(spans, fwd):
+        p, q = be.validate(f[0], f[1], b, cmin, cfirst, clast)
+        pairs.append(p.cpu().numpy()); fit.append(q.cpu().numpy())
+    torch.cuda.synchronize()
+    assert np.array_equal(np.concatenate(pairs), op) and np.array_equal(np.concatenate(fit), of)
+    # world size 1 through the orchestrator
+    sa = parallel.ShardedAssociate(be, True)
+    p, q = sa.associate(torch.from_numpy(src).cuda(), d_dst)
+    assert np.array_equal(p.cpu().numpy(), op) and np.array_equal(q.cpu().numpy(), of)
+    assoc.close()
+
+
+def test_surf_host_batch_equals_single_frames(bs, orc):
+    # bs_surf_detect_host_batch: 70 host frames (two full sub-batches of 32 and a ragged one) through the two-lane copy/compute
+    # pipeline; every frame's list must equal the single-image result, in order
+    import torch
+    frames = np.stack([blob_image(160, 120, 500 + (f % 5)) for f in range(70)])
+    ref = [orc.surf_fast(frames[f]) for f in range(5)]
+    det = bs.FactoryDetectDescribe.surfFast(None, None, None, np.float32)
+    cap = sum(len(ref[f % 5]["x"]) for f in range(70))
+    out = bs.HostFeatureBuffers(70, cap + 10, 64, pinned=True)
+    det.detectHostBatch(torch.from_numpy(frames).pin_memory(), out)
+    assert out.total == cap
+    for f in range(70):
+        r, o = out.frame(f), ref[f % 5]
+        for k in ("x", "y", "scale", "angle", "desc", "white"):
+            assert np.array_equal(r[k], o[k]), (f, k)
+    # pageable numpy input, strided rows (sub-image), second call on the same handle
+    wide = np.zeros((3, 120, 200), np.float32); wide[:, :, 20:180] = frames[:3]
+    t = torch.from_numpy(wide)[:, :, 20:180]
+    out2 = bs.HostFeatureBuffers(3, cap, 64, pinned=False)
+    det.detectHostBatch(t, out2)
+    for f in range(3):
+        assert np.array_equal(out2.frame(f)["desc"], ref[f]["desc"])
+    # capacity error is loud
+    small = bs.HostFeatureBuffers(70, 5, 64, pinned=False)
+    with pytest.raises(Exception):
+        det.detectHostBatch(frames, small)
+    out.close(); det.close()
