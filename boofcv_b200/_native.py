@@ -76,6 +76,7 @@ SIGNATURES = {
     "bs_assoc_destroy": (_i, [_vp]),
     "bs_assoc_set_max_fit_error": (_i, [_vp, _d]),
     "bs_assoc_set_mode": (_i, [_vp, _i]),
+    "bs_assoc_filter_scores": (_i, [_vp, _vp, _i, _vp, _i, _i, _vp, _vp, _vp]),
     "bs_assoc_run": (_i, [_vp, _vp, _i, _vp, _i, _i, _vp, _vp]),
     "bs_assoc_run_device": (_i, [_vp, _vp, _i, _vp, _i, _i, _vp, _vp, _vp]),
     "bs_assoc_forward_device": (_i, [_vp, _vp, _i, _i, _vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp]),

@@ -112,6 +112,17 @@ class AssociateGreedyGPU:
     def setMode(self, mode):
         N.check(N.lib().bs_assoc_set_mode(self._h, int(mode)))
 
+    def filterScores(self, src, dst, want_scores=True):
+        """Diagnostic (bs_assoc_filter_scores): the tensor-core filter's fp32 distance estimates [n][m], the number of
+        candidates per source row, and (tensor-core runs, exact fallbacks) of this handle."""
+        src = _as_matrix(src); dst = _as_matrix(dst)
+        n, m = len(src), len(dst)
+        scores = np.zeros((n, m), np.float32) if want_scores else None
+        cnt = np.zeros(n, np.int32); stats = np.zeros(2, np.int64)
+        N.check(N.lib().bs_assoc_filter_scores(self._h, _p(src), n, _p(dst), m, src.shape[1], _p(scores) if want_scores else None, _p(cnt),
+                                               _p(stats)))
+        return scores, cnt, (int(stats[0]), int(stats[1]))
+
     def getScoreType(self):
         return self._score.getScoreType()
 

@@ -755,6 +755,9 @@ struct bs_assoc {
 	DevBuf p_min, p_first, p_last;            // split partials
 	DevBuf col_min, col_first, col_last;      // column statistics
 	DevBuf d_src, d_dst, d_pairs, d_fit;      // staging for the host entry point
+	// tensor-core filter workspace: split operands, norms, candidate lists
+	DevBuf op_src, op_dst, norm_src, norm_dst, tc_scalars /* maxnorm src, maxnorm dst, overflow */, cand_count, cand;
+	long tc_runs = 0, tc_fallbacks = 0;
 
 	RowminScratch scratch(long entries) {
 		p_min.reserve(entries * 8); p_first.reserve(entries * 4); p_last.reserve(entries * 4);
@@ -785,12 +788,54 @@ struct bs_assoc {
 			BS_CUDA(cudaStreamSynchronize(st));
 			return;
 		}
+		const bool want_tc = mode == 1 || (mode == -1 && tc_supported(dof) && (long)n * m >= (1L << 22));
+		if (want_tc) {
+			if (!tc_supported(dof)) fail(BS_ERR_ARG, "the tensor-core filter is built for 64-element descriptors (SURF-64)");
+			if (run_tc(src, n, dst, m, pairs, fit, st)) return;
+			tc_fallbacks++;                    // a row had more candidates than the list holds: redo everything exactly
+		}
+		run_exact(src, n, dst, m, dof, pairs, fit, st);
+	}
+	void run_exact(const double* src, int n, const double* dst, int m, int dof, int32_t* pairs, double* fit, cudaStream_t st) {
 		forward(src, n, dst, m, dof, pairs, fit, st);
 		if (backwards) {
 			col_min.reserve((size_t)m * 8); col_first.reserve((size_t)m * 4); col_last.reserve((size_t)m * 4);
 			columns(src, n, 0, dst, m, dof, col_min.as<double>(), col_first.as<int32_t>(), col_last.as<int32_t>(), st);
 			launch_validate(n, 0, pairs, fit, col_min.as<double>(), col_first.as<int32_t>(), col_last.as<int32_t>(), st);
 		}
+	}
+	void tc_prepare(const double* src, int n, const double* dst, int m, cudaStream_t st) {
+		op_src.reserve(tc_operand_bytes(n)); op_dst.reserve(tc_operand_bytes(m));
+		norm_src.reserve((size_t)tc_pad_rows(n) * 4); norm_dst.reserve((size_t)tc_pad_rows(m) * 4);
+		tc_scalars.reserve(16);
+		const size_t rows = (size_t)std::max(n, m);
+		cand_count.reserve(rows * 4); cand.reserve(rows * tc_cand_cap() * 4);
+		unsigned* sc = tc_scalars.as<unsigned>();
+		launch_tc_split(src, n, 0, op_src.p, norm_src.as<float>(), sc + 0, st);
+		launch_tc_split(dst, m, 1, op_dst.p, norm_dst.as<float>(), sc + 1, st);
+		BS_CUDA(cudaMemsetAsync(sc + 2, 0, 4, st));
+	}
+	// tensor-core filter + exact re-score; false if a candidate list overflowed (results then invalid).  Synchronises `st`.
+	bool run_tc(const double* src, int n, const double* dst, int m, int32_t* pairs, double* fit, cudaStream_t st) {
+		tc_prepare(src, n, dst, m, st);
+		unsigned* sc = tc_scalars.as<unsigned>();
+		int* overflow = reinterpret_cast<int*>(sc + 2);
+		launch_tc_filter(op_src.p, norm_src.as<float>(), n, op_dst.p, norm_dst.as<float>(), sc + 1, m, cand_count.as<int>(), cand.as<int>(),
+		                 nullptr, sm_count, st);
+		launch_tc_rescore(src, n, dst, cand_count.as<int>(), cand.as<int>(), 0, max_fit, 0, pairs, fit, nullptr, nullptr, nullptr, overflow, st);
+		if (backwards) {
+			col_min.reserve((size_t)m * 8); col_first.reserve((size_t)m * 4); col_last.reserve((size_t)m * 4);
+			launch_tc_filter(op_dst.p, norm_dst.as<float>(), m, op_src.p, norm_src.as<float>(), sc + 0, n, cand_count.as<int>(), cand.as<int>(),
+			                 nullptr, sm_count, st);
+			launch_tc_rescore(dst, m, src, cand_count.as<int>(), cand.as<int>(), 1, 0.0, 0, nullptr, nullptr, col_min.as<double>(),
+			                  col_first.as<int32_t>(), col_last.as<int32_t>(), overflow, st);
+			launch_validate(n, 0, pairs, fit, col_min.as<double>(), col_first.as<int32_t>(), col_last.as<int32_t>(), st);
+		}
+		int h_overflow = 0;
+		BS_CUDA(cudaMemcpyAsync(&h_overflow, overflow, 4, cudaMemcpyDeviceToHost, st));
+		BS_CUDA(cudaStreamSynchronize(st));
+		tc_runs++;
+		return h_overflow == 0;
 	}
 };
 
@@ -818,6 +863,8 @@ int bs_assoc_destroy(bs_assoc* a) {
 		a->p_min.release(); a->p_first.release(); a->p_last.release();
 		a->col_min.release(); a->col_first.release(); a->col_last.release();
 		a->d_src.release(); a->d_dst.release(); a->d_pairs.release(); a->d_fit.release();
+		a->op_src.release(); a->op_dst.release(); a->norm_src.release(); a->norm_dst.release(); a->tc_scalars.release();
+		a->cand_count.release(); a->cand.release();
 		if (a->stream) cudaStreamDestroy(a->stream);
 		delete a;
 	});
@@ -831,8 +878,32 @@ int bs_assoc_set_mode(bs_assoc* a, int mode) {
 	return guarded([&] {
 		if (!a) fail(BS_ERR_ARG, "handle is null");
 		if (mode < -1 || mode > 1) fail(BS_ERR_ARG, "mode must be -1 (auto), 0 (exact) or 1 (tensor-core filter)");
-		if (mode == 1) fail(BS_ERR_ARG, "tensor-core filter mode is not built in this version");
 		a->mode = mode;
+	});
+}
+
+int bs_assoc_filter_scores(bs_assoc* a, const double* src, int n, const double* dst, int m, int dof, float* scores,
+                           int32_t* cand_count, long* stats) {
+	return guarded([&] {
+		if (!a || !src || !dst) fail(BS_ERR_ARG, "null argument");
+		if (n <= 0 || m <= 0) fail(BS_ERR_ARG, "bad sizes");
+		if (!tc_supported(dof)) fail(BS_ERR_ARG, "the tensor-core filter is built for 64-element descriptors (SURF-64)");
+		DeviceGuard g(a->device);
+		cudaStream_t st = a->stream;
+		DevBuf d_scores;
+		a->d_src.reserve((size_t)n * dof * 8); a->d_dst.reserve((size_t)m * dof * 8);
+		BS_CUDA(cudaMemcpyAsync(a->d_src.p, src, (size_t)n * dof * 8, cudaMemcpyHostToDevice, st));
+		BS_CUDA(cudaMemcpyAsync(a->d_dst.p, dst, (size_t)m * dof * 8, cudaMemcpyHostToDevice, st));
+		if (scores) { d_scores.reserve((size_t)n * m * 4); BS_CUDA(cudaMemsetAsync(d_scores.p, 0xff, (size_t)n * m * 4, st)); }
+		a->tc_prepare(a->d_src.as<double>(), n, a->d_dst.as<double>(), m, st);
+		unsigned* sc = a->tc_scalars.as<unsigned>();
+		launch_tc_filter(a->op_src.p, a->norm_src.as<float>(), n, a->op_dst.p, a->norm_dst.as<float>(), sc + 1, m, a->cand_count.as<int>(),
+		                 a->cand.as<int>(), scores ? d_scores.as<float>() : nullptr, a->sm_count, st);
+		if (scores) BS_CUDA(cudaMemcpyAsync(scores, d_scores.p, (size_t)n * m * 4, cudaMemcpyDeviceToHost, st));
+		if (cand_count) BS_CUDA(cudaMemcpyAsync(cand_count, a->cand_count.p, (size_t)n * 4, cudaMemcpyDeviceToHost, st));
+		BS_CUDA(cudaStreamSynchronize(st));
+		d_scores.release();
+		if (stats) { stats[0] = a->tc_runs; stats[1] = a->tc_fallbacks; }
 	});
 }
 

@@ -159,6 +159,18 @@ void launch_describe(const T* d_ii, int W, int H, const DescribeParams& p, const
 
 // ---------------------------------------------------------------- exact association (bs_assoc_exact.cu)
 struct RowminScratch { double* p_min; int* p_first; int* p_last; long cap; };
+// tensor-core candidate filter (bs_assoc_tc.cu)
+bool tc_supported(int dof);
+int tc_pad_rows(int n);
+size_t tc_operand_bytes(int n);
+int tc_cand_cap();
+void launch_tc_split(const double* d_x, int n, int arrangement, void* d_operand, float* d_norm, unsigned* d_max_norm_bits, cudaStream_t st);
+void launch_tc_filter(const void* d_opA, const float* d_normA, int nA, const void* d_opB, const float* d_normB,
+                      const unsigned* d_max_norm_b_bits, int nB, int* d_cand_count, int* d_cand, float* d_dbg, int sm_count,
+                      cudaStream_t st);
+void launch_tc_rescore(const double* d_A, int nA, const double* d_B, const int* d_cand_count, const int* d_cand, int mode, double max_fit,
+                       int index_offset, int32_t* pairs, double* fit, double* o_min, int32_t* o_first, int32_t* o_last, int* d_overflow,
+                       cudaStream_t st);
 int rowmin_splits(int nA, int nB, int sm_count);
 void launch_rowmin(const double* A, int nA, const double* B, int nB, int dof, int splits, const RowminScratch& s, cudaStream_t st);
 void launch_rowmin_finalize(const RowminScratch& s, int nA, int splits, int mode, double max_fit, int index_offset, int32_t* pairs,

@@ -207,9 +207,18 @@ int bs_assoc_destroy(bs_assoc* a);
 int bs_assoc_set_max_fit_error(bs_assoc* a, double max_fit_error); /* Associate.setMaxScoreThreshold */
 
 /* Filter mode: 0 = exact fp64 distances for every pair; 1 = tensor-core candidate filter (tcgen05 bf16 hi/lo split)
- * followed by an exact fp64 re-score of the candidates (same pairs/fit, much faster for large N*M).  Default = auto:
- * mode 1 when n*m >= 2^22 and dof is a multiple of 16, else mode 0. */
+ * followed by an exact fp64 re-score of the candidates (same pairs/fit, much faster for large N*M).  Default -1 = auto:
+ * mode 1 when n*m >= 2^22 and dof == 64 (SURF-64), else mode 0.  Mode 1 synchronises the stream once per call (it has to
+ * learn whether a candidate list overflowed, in which case the call is redone with the exact kernel). */
 int bs_assoc_set_mode(bs_assoc* a, int mode);
+
+/* Diagnostic for the tensor-core filter (mode 1): runs only the bf16 hi/lo split and the tcgen05 pass for src against dst
+ * and returns what the exact re-score would start from.  scores[n][m] (host, may be NULL) = the filter's fp32 estimate of
+ * every squared distance; cand_count[n] (host, may be NULL) = candidates emitted per source row; stats[2] (may be NULL) =
+ * {runs of the tensor-core path, runs that fell back to the exact kernel because a candidate list overflowed}.
+ * Used by the tests to measure the estimate's real error against the bound the filter assumes. */
+int bs_assoc_filter_scores(bs_assoc* a, const double* src, int n, const double* dst, int m, int dof, float* scores,
+                           int32_t* cand_count, long* stats);
 
 /* AssociateGreedy.associate: src[n][dof], dst[m][dof] row-major doubles (the TupleDesc_F64.value arrays back to back).
  * pairs[n] = index into dst or -1 (AssociateGreedyBase.getPairs), fit[n] = score of the match
