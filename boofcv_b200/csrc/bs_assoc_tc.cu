@@ -14,8 +14,8 @@
 //      the candidates (the bound and its margin are stated at tolerance_of()).
 //   3. rescore_kernel: exact fp64 distance of every candidate, sequential over k without FMA like the reference; minimum,
 //      first and last index of the minimum -> pairs/fit (forward) or the column statistics used by backward validation.
-// Roles inside the filter CTA (192 threads): warp 0 = TMA producer, warp 1 = MMA issuer (one thread), warps 2-5 =
-// epilogue (one TMEM lane = one row per thread).  A (2 x 128 rows) stays resident per work item, B tiles stream through a
+// Roles inside the filter CTA (320 threads): warp 0 = TMA producer, warp 1 = MMA issuer (one thread), warps 2-9 =
+// epilogue (one TMEM lane = one row per thread, one warp set per resident A tile).  A (2 x 128 rows) stays resident per work item, B tiles stream through a
 // 2-stage ring; two accumulator buffers in TMEM let the epilogue of tile t overlap the MMAs of tile t+1.
 #include "bs_common.cuh"
 #include "bs_sm100.cuh"
@@ -37,7 +37,8 @@ constexpr int TC_MROWS = 2 * TC_BM;        // rows per work item (two resident A
 constexpr int TC_STAGES = 2;
 constexpr int TC_ATOM_BYTES = TC_BM * 128; // 16 KB: 128 rows x 128 B
 constexpr int TC_TILE_BYTES = TC_ATOMS * TC_ATOM_BYTES;   // 48 KB
-constexpr int TC_THREADS = 192;
+constexpr int TC_EPI_WARPS = 8;           // two per TMEM lane quarter: one per resident A tile
+constexpr int TC_THREADS = 64 + 32 * TC_EPI_WARPS;
 constexpr int TC_CAND_CAP = 64;            // candidates kept per row; more -> the caller falls back to the exact kernel
 constexpr int TC_TMEM_COLS = 512;
 
@@ -114,7 +115,7 @@ filter_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ C
 	if (threadIdx.x == 0) {
 		mbar_init(&bar->a_full, 1); mbar_init(&bar->a_empty, 1);
 		for (int s = 0; s < TC_STAGES; s++) { mbar_init(&bar->b_full[s], 1); mbar_init(&bar->b_empty[s], 1); }
-		for (int s = 0; s < 2; s++) { mbar_init(&bar->acc_full[s], 1); mbar_init(&bar->acc_empty[s], 4); }
+		for (int s = 0; s < 2; s++) { mbar_init(&bar->acc_full[s], 1); mbar_init(&bar->acc_empty[s], TC_EPI_WARPS); }
 		mbar_fence_init();
 	}
 	__syncwarp();
@@ -182,62 +183,69 @@ filter_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ C
 			}
 		}
 	} else {
-		// ===== epilogue: warps 2..5, TMEM lane quarter = warp % 4 =====
+		// ===== epilogue: warps 2..9.  TMEM lane quarter = warp % 4 (hardware rule); warps 2-5 take A tile 0, 6-9 A tile 1 =====
 		const int q = warp & 3;
-		const int e = (warp - 2) * 32 + lane;                        // 0..127 among the epilogue threads
-		const int L = q * 32 + lane;                                 // TMEM lane = row inside a 128-row tile
+		const int h = (warp - 2) >> 2;
+		const int e = (warp - 2) * 32 + lane;                        // 0..255 among the epilogue threads
+		const int L = q * 32 + lane;                                 // TMEM lane = row inside the 128-row tile
 		const float nb_max = __uint_as_float(*P.max_norm_b_bits);
 		uint32_t n_tile = 0;
 		for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
 			const int rp = item / P.chunks, ch = item - rp * P.chunks;
 			const int t0 = ch * P.tiles_per_chunk, t1 = min(t0 + P.tiles_per_chunk, P.b_tiles);
-			int row[2]; float run[2], tol[2], na[2];
-			for (int h = 0; h < 2; h++) {
-				row[h] = rp * TC_MROWS + h * TC_BM + L;
-				na[h] = row[h] < P.nA ? P.norm_a[row[h]] : 0.0f;
-				tol[h] = tolerance_of(na[h], nb_max);
-				run[h] = INFINITY;
-			}
+			const int row = rp * TC_MROWS + h * TC_BM + L;
+			const bool live = row < P.nA;
+			const float na = live ? P.norm_a[row] : 0.0f;
+			const float tol = tolerance_of(na, nb_max);
+			float run = INFINITY;
 			for (int t = t0; t < t1; t++, n_tile++) {
 				const int as = n_tile & 1;
 				const uint32_t acc_use = n_tile >> 1;
 				const int col0 = t * TC_BN;
-				s_nb[as * TC_BN + e] = P.norm_b[col0 + e];
-				asm volatile("bar.sync 1, 128;" ::: "memory");        // the 128 epilogue threads only
+				if (e < TC_BN) s_nb[as * TC_BN + e] = P.norm_b[col0 + e];
+				asm volatile("bar.sync 1, 256;" ::: "memory");        // the 256 epilogue threads only
 				mbar_wait(&bar->acc_full[as], acc_use & 1);
 				tc_fence_after();
-				for (int h = 0; h < 2; h++) {
-#pragma unroll 1
-					for (int c = 0; c < TC_BN / 32; c++) {
-						float v[32];
-						tmem_ld32(tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * 2 * TC_BN + h * TC_BN + c * 32), v);
-						const float* nb = s_nb + as * TC_BN + c * 32;
-						float cmin = INFINITY;
+				const uint32_t tbase = tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * 2 * TC_BN + h * TC_BN);
+				uint32_t ra[32], rb[32];
+				// chunk c+1 is in flight while chunk c is reduced
+				auto reduce = [&](uint32_t (&r)[32], int c) {
+					const float* nb = s_nb + as * TC_BN + c * 32;
+					float v[32];
+					float cmin = INFINITY;
 #pragma unroll
-						for (int k = 0; k < 32; k++) {
-							v[k] = fmaf(-2.0f, v[k], nb[k]);
-							cmin = fminf(cmin, v[k]);
-						}
-						if (P.dbg && row[h] < P.nA) {
+					for (int k = 0; k < 32; k++) {
+						v[k] = fmaf(-2.0f, __uint_as_float(r[k]), nb[k]);
+						cmin = fminf(cmin, v[k]);
+					}
+					if (P.dbg && live) {
 #pragma unroll
-							for (int k = 0; k < 32; k++)
-								if (col0 + c * 32 + k < P.nB) P.dbg[(size_t)row[h] * P.nB + col0 + c * 32 + k] = v[k] + na[h];
-						}
-						if (cmin <= run[h] + tol[h] && cmin < INFINITY && row[h] < P.nA) {
-							run[h] = fminf(run[h], cmin);
-							const float thr = run[h] + tol[h];
+						for (int k = 0; k < 32; k++)
+							if (col0 + c * 32 + k < P.nB) P.dbg[(size_t)row * P.nB + col0 + c * 32 + k] = v[k] + na;
+					}
+					if (cmin <= run + tol && cmin < INFINITY && live) {
+						run = fminf(run, cmin);
+						const float thr = run + tol;
+						unsigned hits = 0;
 #pragma unroll
-							for (int k = 0; k < 32; k++)
-								if (v[k] <= thr) {
-									const int slot = atomicAdd(P.cand_count + row[h], 1);
-									if (slot < TC_CAND_CAP) P.cand[(size_t)row[h] * TC_CAND_CAP + slot] = col0 + c * 32 + k;
-								}
+						for (int k = 0; k < 32; k++) hits |= (v[k] <= thr ? 1u : 0u) << k;
+						while (hits) {
+							const int k = __ffs(hits) - 1;
+							hits &= hits - 1;
+							const int slot = atomicAdd(P.cand_count + row, 1);
+							if (slot < TC_CAND_CAP) P.cand[(size_t)row * TC_CAND_CAP + slot] = col0 + c * 32 + k;
 						}
 					}
-				}
+				};
+				tmem_ld32_issue(tbase, ra);
+				tmem_ld_wait(ra); tmem_ld32_issue(tbase + 32, rb); reduce(ra, 0);
+				tmem_ld_wait(rb); tmem_ld32_issue(tbase + 64, ra); reduce(rb, 1);
+				tmem_ld_wait(ra); tmem_ld32_issue(tbase + 96, rb); reduce(ra, 2);
+				tmem_ld_wait(rb);
 				tc_fence_before();
 				__syncwarp();
-				if (lane == 0) mbar_arrive(&bar->acc_empty[as]);
+				if (lane == 0) mbar_arrive(&bar->acc_empty[as]);     // TMEM buffer free: the last chunk lives in registers now
+				reduce(rb, 3);
 			}
 		}
 	}
@@ -348,8 +356,9 @@ void launch_tc_filter(const void* d_opA, const float* d_normA, int nA, const voi
 	P.nA = nA; P.nB = nB;
 	P.a_tiles256 = tc_pad_rows(nA) / TC_MROWS;
 	P.b_tiles = tc_pad_rows(nB) / TC_BN;
-	// column chunks: enough work items to balance the SMs (about 8 per SM), at least 8 B tiles per item to amortise A
-	int chunks = div_up(8 * sm_count, P.a_tiles256);
+	// column chunks only when there are fewer 256-row items than SMs: a row's running minimum (and with it the number of
+	// candidates it emits, ~ln(columns/32)) is per item; at least 8 B tiles per item to amortise loading A
+	int chunks = div_up(sm_count, P.a_tiles256);
 	chunks = std::max(1, std::min(chunks, P.b_tiles / 8 > 0 ? P.b_tiles / 8 : 1));
 	P.tiles_per_chunk = div_up(P.b_tiles, chunks);
 	P.chunks = div_up(P.b_tiles, P.tiles_per_chunk);

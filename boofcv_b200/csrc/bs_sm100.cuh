@@ -24,7 +24,7 @@ __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
 // Bounded wait: a protocol bug must not hang the GPU (the box is shared), it traps instead.
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
 	const uint32_t addr = smem_u32(bar);
-	for (uint32_t spin = 0; spin < (1u << 28); spin++) {
+	for (uint32_t spin = 0; spin < (1u << 26); spin++) {
 		uint32_t done;
 		asm volatile(
 		    "{\n\t.reg .pred p;\n\t"
@@ -34,6 +34,7 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
 		    : "r"(addr), "r"(parity)
 		    : "memory");
 		if (done) return;
+		if (spin > 64) __nanosleep(32);        // keep the issue slots for the warps that do the work
 	}
 	__trap();
 }
@@ -76,22 +77,26 @@ __device__ __forceinline__ void umma_bf16(uint32_t d_tmem, uint64_t a_desc, uint
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
 	asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
-// 32 lanes x 32 consecutive columns: thread l of warp w reads TMEM lane 32*(w%4)+l, columns [col, col+32)
-__device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
-	uint32_t r[32];
+// 32 lanes x 32 consecutive columns: thread l of warp w reads TMEM lane 32*(w%4)+l, columns [col, col+32).
+// tmem_ld32_issue starts the load; the registers are valid only after tmem_ld_wait on the same array (the wait takes the
+// registers as in/out operands so that the compiler cannot move their consumers above it).
+#define BS_R32(m) m(0), m(1), m(2), m(3), m(4), m(5), m(6), m(7), m(8), m(9), m(10), m(11), m(12), m(13), m(14), m(15), m(16), m(17), \
+	m(18), m(19), m(20), m(21), m(22), m(23), m(24), m(25), m(26), m(27), m(28), m(29), m(30), m(31)
+__device__ __forceinline__ void tmem_ld32_issue(uint32_t taddr, uint32_t (&r)[32]) {
+#define BS_OUT(k) "=r"(r[k])
 	asm volatile(
 	    "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
 	    "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
 	    "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
-	    : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]),
-	      "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]), "=r"(r[17]), "=r"(r[18]),
-	      "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]),
-	      "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+	    : BS_R32(BS_OUT)
 	    : "r"(taddr)
 	    : "memory");
-	asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-#pragma unroll
-	for (int k = 0; k < 32; k++) v[k] = __uint_as_float(r[k]);
+#undef BS_OUT
+}
+__device__ __forceinline__ void tmem_ld_wait(uint32_t (&r)[32]) {
+#define BS_INOUT(k) "+r"(r[k])
+	asm volatile("tcgen05.wait::ld.sync.aligned;" : BS_R32(BS_INOUT)::"memory");
+#undef BS_INOUT
 }
 
 // ---------------------------------------------------------------- UMMA descriptors
