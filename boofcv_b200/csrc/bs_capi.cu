@@ -815,6 +815,25 @@ struct bs_assoc {
 		launch_tc_split(dst, m, 1, op_dst.p, norm_dst.as<float>(), sc + 1, st);
 		BS_CUDA(cudaMemsetAsync(sc + 2, 0, 4, st));
 	}
+	// sharded step 1 on the tensor cores: forward pass of the local rows and the column statistics over them (global row
+	// numbering); false if a candidate list overflowed.  Synchronises `st`.
+	bool forward_tc(const double* src, int n, int row_offset, const double* dst, int m, int32_t* pairs, double* fit, double* cmin,
+	                int32_t* cfirst, int32_t* clast, cudaStream_t st) {
+		tc_prepare(src, n, dst, m, st);
+		unsigned* sc = tc_scalars.as<unsigned>();
+		int* overflow = reinterpret_cast<int*>(sc + 2);
+		launch_tc_filter(op_src.p, norm_src.as<float>(), n, op_dst.p, norm_dst.as<float>(), sc + 1, m, cand_count.as<int>(), cand.as<int>(),
+		                 nullptr, sm_count, st);
+		launch_tc_rescore(src, n, dst, cand_count.as<int>(), cand.as<int>(), 0, max_fit, 0, pairs, fit, nullptr, nullptr, nullptr, overflow, st);
+		launch_tc_filter(op_dst.p, norm_dst.as<float>(), m, op_src.p, norm_src.as<float>(), sc + 0, n, cand_count.as<int>(), cand.as<int>(),
+		                 nullptr, sm_count, st);
+		launch_tc_rescore(dst, m, src, cand_count.as<int>(), cand.as<int>(), 1, 0.0, row_offset, nullptr, nullptr, cmin, cfirst, clast, overflow, st);
+		int h_overflow = 0;
+		BS_CUDA(cudaMemcpyAsync(&h_overflow, overflow, 4, cudaMemcpyDeviceToHost, st));
+		BS_CUDA(cudaStreamSynchronize(st));
+		tc_runs++;
+		return h_overflow == 0;
+	}
 	// tensor-core filter + exact re-score; false if a candidate list overflowed (results then invalid).  Synchronises `st`.
 	bool run_tc(const double* src, int n, const double* dst, int m, int32_t* pairs, double* fit, cudaStream_t st) {
 		tc_prepare(src, n, dst, m, st);
@@ -946,6 +965,12 @@ int bs_assoc_forward_device(bs_assoc* a, const double* d_src, int n, int row_off
 		if (!d_src || !d_dst || !d_pairs || !d_fit || !d_col_min || !d_col_first || !d_col_last) fail(BS_ERR_ARG, "null argument");
 		DeviceGuard g(a->device);
 		cudaStream_t st = stream ? static_cast<cudaStream_t>(stream) : a->stream;
+		const bool want_tc = a->mode == 1 || (a->mode == -1 && tc_supported(dof) && (long)n * m >= (1L << 22));
+		if (want_tc) {
+			if (!tc_supported(dof)) fail(BS_ERR_ARG, "the tensor-core filter is built for 64-element descriptors (SURF-64)");
+			if (a->forward_tc(d_src, n, row_offset, d_dst, m, d_pairs, d_fit, d_col_min, d_col_first, d_col_last, st)) return;
+			a->tc_fallbacks++;
+		}
 		a->forward(d_src, n, d_dst, m, dof, d_pairs, d_fit, st);
 		a->columns(d_src, n, row_offset, d_dst, m, dof, d_col_min, d_col_first, d_col_last, st);
 	});

@@ -234,7 +234,8 @@ def test_config1_shifted_pair_end_to_end(bs, orc):
     det.close()
 
 
-def test_sharded_association_device_steps(bs, orc):
+@pytest.mark.parametrize("mode", [0, 1])
+def test_sharded_association_device_steps(bs, orc, mode):
     # the three C-ABI steps of a row-sharded association, three shards simulated on one GPU: forward per
     # shard with global row offsets, merge of the stacked column partials, validation per shard == single-process result
     import torch
@@ -246,6 +247,7 @@ def test_sharded_association_device_steps(bs, orc):
     src[7] = src[3]; dst[11] = dst[10]
     op, of = orc.associate(src, dst, 40.0, True)
     assoc = bs.FactoryAssociation.greedy(bs.ScoreAssociateEuclideanSq_F64(), 40.0, True)
+    assoc.setMode(mode)                               # 0: exact fp64 kernels, 1: tensor-core filter + exact re-score
     be = parallel.GpuAssocBackend(assoc)
     d_dst = torch.from_numpy(dst).cuda()
     spans = [parallel.shard_range(n, r, 3) for r in range(3)]
