@@ -10,6 +10,7 @@
 // Border samples (`inner == false`) follow convolveSparse: ret = 0; ret += box*weight — the same values for float, a
 // different int/float conversion point for S32 integrals, so both forms are kept.
 #include "bs_common.cuh"
+#include <cstdlib>
 #include "bs_box.cuh"
 
 namespace bs {
@@ -166,8 +167,17 @@ bool try_tiled<float>(const float* d_ii, const Plan& plan, int first, int ns, fl
 	const int step = plan.layers[first + 1].size - L0.size;
 	for (int i = 1; i < ns; i++)
 		if (plan.layers[first + i].size != L0.size + i * step) return false;
-	if (L0.skip == 1 && L0.size == 9 && step == 6) { launch_hessian_tile<1, 9, 6, 4, 64, 16>(d_ii, plan, first, d_inten, batch, st); return true; }
-	if (L0.skip == 2 && L0.size == 15 && step == 12) { launch_hessian_tile<2, 15, 12, 4, 32, 16>(d_ii, plan, first, d_inten, batch, st); return true; }
+	static const int tma_mask = getenv("BS_HESSIAN_NO_TMA") ? 0 : (getenv("BS_HESSIAN_TMA_MASK") ? atoi(getenv("BS_HESSIAN_TMA_MASK")) : 3);
+	if (L0.skip == 1 && L0.size == 9 && step == 6) {
+		if (!((tma_mask & 1) && launch_hessian_tma<1, 9, 6, 4, 64, 16>(d_ii, plan, first, d_inten, batch, st)))
+			launch_hessian_tile<1, 9, 6, 4, 64, 16>(d_ii, plan, first, d_inten, batch, st);
+		return true;
+	}
+	if (L0.skip == 2 && L0.size == 15 && step == 12) {
+		if (!((tma_mask & 2) && launch_hessian_tma<2, 15, 12, 4, 32, 16>(d_ii, plan, first, d_inten, batch, st)))
+			launch_hessian_tile<2, 15, 12, 4, 32, 16>(d_ii, plan, first, d_inten, batch, st);
+		return true;
+	}
 	return false;
 }
 

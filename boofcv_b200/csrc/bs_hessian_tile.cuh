@@ -10,6 +10,8 @@
 //   - samples in the reference's border ring (computeHessian / block_zero semantics) take the generic path per thread.
 // Arithmetic order is exactly hessianInner's (see bs_hessian.cu).
 #pragma once
+#include "bs_sm100.cuh"
+#include <algorithm>
 
 namespace bs {
 
@@ -69,9 +71,14 @@ template <int SIZE, int SKIP> struct InnerBorder {
 	static constexpr int value = (rf + 1 + (SKIP - (rf + 1) % SKIP)) / SKIP;
 };
 
-template <int SKIP, int S0, int STEP, int NS, int TX, int TY, int I>
+// the border ring is rare: keep ONE out-of-line copy of its (large) code instead of one per unrolled layer and row — the
+// fully inlined kernels were 140-154 KB and ncu showed the warps starving on instruction fetch (stall_no_instruction 5.2)
+static __device__ __noinline__ float tile_border_response(const float* __restrict__ ii, int W, int H, const Layer* __restrict__ L, int px, int py) {
+	return response_border(ii, W, H, *L, px, py);
+}
+
+template <typename G, int SKIP, int S0, int STEP, int NS, int I>
 struct TileLayers {
-	typedef TileGeo<SKIP, S0, STEP, NS, TX, TY> G;
 	static __device__ __forceinline__ void run(const float* __restrict__ base, const float* __restrict__ ii, int W, int H,
 	                                           const Layer* __restrict__ layers, float* __restrict__ inten, int x, int y) {
 		constexpr int SIZE = S0 + I * STEP;
@@ -80,13 +87,13 @@ struct TileLayers {
 		const bool inner = x >= border && x < L.w - border && y >= border && y < L.h - border;
 		float v;
 		if (inner) v = tile_response<SIZE, G>(base);
-		else v = response_border(ii, W, H, L, x * SKIP, y * SKIP);
+		else v = tile_border_response(ii, W, H, &L, x * SKIP, y * SKIP);
 		inten[L.offset + (long)y * L.w + x] = v;
-		TileLayers<SKIP, S0, STEP, NS, TX, TY, I + 1>::run(base, ii, W, H, layers, inten, x, y);
+		TileLayers<G, SKIP, S0, STEP, NS, I + 1>::run(base, ii, W, H, layers, inten, x, y);
 	}
 };
-template <int SKIP, int S0, int STEP, int NS, int TX, int TY>
-struct TileLayers<SKIP, S0, STEP, NS, TX, TY, NS> {
+template <typename G, int SKIP, int S0, int STEP, int NS>
+struct TileLayers<G, SKIP, S0, STEP, NS, NS> {
 	static __device__ __forceinline__ void run(const float*, const float*, int, int, const Layer*, float*, int, int) {}
 };
 
@@ -121,12 +128,12 @@ hessian_tile_kernel(const float* __restrict__ ii_all, int W, int H, OctaveLayers
 	const int tx = threadIdx.x % TX, ty0 = threadIdx.x / TX;
 	const int x = X0 + tx;
 	if (x >= w) return;
-#pragma unroll
+#pragma unroll 1
 	for (int ty = ty0; ty < TY; ty += ROWS_PER_PASS) {
 		const int y = Y0 + ty;
 		if (y < h) {
 			const float* base = tile + ty * SKIP * G::PITCH + tx;
-			TileLayers<SKIP, S0, STEP, NS, TX, TY, 0>::run(base, ii, W, H, oct.l, inten, x, y);
+			TileLayers<G, SKIP, S0, STEP, NS, 0>::run(base, ii, W, H, oct.l, inten, x, y);
 		}
 	}
 }
@@ -139,6 +146,153 @@ void launch_hessian_tile(const float* d_ii, const Plan& plan, int first_layer, f
 	if (tiles_x * tiles_y == 0) return;
 	BS_LAUNCH((hessian_tile_kernel<SKIP, S0, STEP, NS, TX, TY>), dim3(tiles_x * tiles_y, batch), TILE_THREADS, 0, st, d_ii, plan.W,
 	          plan.H, oct, tiles_x, plan.inten_per_frame, d_inten);
+}
+
+
+// ---------------------------------------------------------------- TMA-staged variant
+// ncu on the kernel above (profiles/r1_ncu_full_batch8_chunk8_tiled_hessian.txt, source page): 25 % (skip 1) and 60 % (skip 2)
+// of the executed instructions are the staging loop (index division, bounds tests, de-interleaving stores), and nothing
+// hides its L2 latency inside a CTA.  Here one thread issues cp.async.bulk.tensor for the tile of the NEXT work item while
+// the CTA computes the current one; out-of-image pixels are zero-filled by the TMA unit.
+//   skip 1: two TMA buffers, the responses are computed straight out of the one that has landed;
+//   skip 2: one TMA buffer + one buffer of de-interleaved column planes (a short LDS.64 / 2 x STS pass), the next tile's TMA
+//           is issued as soon as that pass has emptied the TMA buffer.
+// Measured constraint (tools/probe/tma_probe.cu): the box must start at a multiple of 4 pixels (16 bytes), so the left halo
+// is rounded up to 4 and the tensor map's element stride cannot be used to fetch the odd column plane.
+// Needs W % 4 == 0 (row pitch multiple of 16 bytes); other widths use the kernel above.
+template <int SKIP, int S0, int STEP, int NS, int TX, int TY> struct TmaGeo {
+	static_assert(SKIP == 1 || SKIP == 2, "TMA variant is written for sample spacing 1 and 2");
+	static_assert((TX * SKIP) % 4 == 0, "tiles must start at a multiple of 4 pixels");
+	static constexpr int SMAX = S0 + (NS - 1) * STEP;
+	static constexpr int HALO = SMAX / 2 + 1;
+	static constexpr int HALO_X = (HALO + 3) & ~3;                                    // left halo, 16-byte aligned box start
+	static constexpr int BOXW = (HALO_X + (TX - 1) * SKIP + HALO + 3) & ~3;           // box width in pixels
+	static constexpr int TH = (TY - 1) * SKIP + 2 * HALO;
+	static constexpr int BOX_WORDS = BOXW * TH;
+	static constexpr int BUF = (BOX_WORDS + 31) & ~31;                                // 128-byte aligned buffers
+	static constexpr int PW = BOXW / SKIP;                                            // plane row pitch (skip 2)
+	static constexpr int PLANE = PW * TH;
+	// word offset of pixel (px+dc, py+dr) relative to the thread's base (= sample (tx,ty) of the tile)
+	static __host__ __device__ constexpr int off(int dr, int dc) {
+		return SKIP == 1 ? (HALO + dr) * BOXW + (HALO_X + dc) : (HALO + dr) * PW + ((HALO_X + dc) % SKIP) * PLANE + (HALO_X + dc) / SKIP;
+	}
+};
+
+template <int SKIP, int S0, int STEP, int NS, int TX, int TY>
+__global__ void __launch_bounds__(TILE_THREADS)
+hessian_tma_kernel(const __grid_constant__ CUtensorMap tm, const float* __restrict__ ii_all, int W, int H, OctaveLayers oct, int tiles_x,
+                   int tiles_y, int frames, long inten_per_frame, float* __restrict__ inten_all) {
+	typedef TmaGeo<SKIP, S0, STEP, NS, TX, TY> G;
+	extern __shared__ unsigned char tma_smem_raw[];
+	float* buf = reinterpret_cast<float*>((reinterpret_cast<uintptr_t>(tma_smem_raw) + 127) & ~(uintptr_t)127);
+	uint64_t* full = reinterpret_cast<uint64_t*>(buf + 2 * G::BUF);            // [2]
+	const CUtensorMap* tmap = &tm;                 // address of the kernel parameter itself (a copy is not a valid descriptor)
+	const int per_frame = tiles_x * tiles_y;
+	const long total = (long)per_frame * frames;
+	if (threadIdx.x == 0) {
+		sm100::mbar_init(&full[0], 1); sm100::mbar_init(&full[1], 1);
+		sm100::mbar_fence_init();
+	}
+	__syncthreads();
+	auto issue = [=](long item, int b) {           // thread 0 only: TMA of work item `item` into TMA buffer b
+		const int frame = (int)(item / per_frame), t = (int)(item - (long)frame * per_frame);
+		const int tyi = t / tiles_x, txi = t - tyi * tiles_x;
+		sm100::mbar_expect_tx(&full[b], G::BOX_WORDS * 4);
+		sm100::tma_load_3d(buf + b * G::BUF, tmap, txi * TX * SKIP - G::HALO_X, tyi * TY * SKIP - G::HALO, frame, &full[b]);
+	};
+	if (threadIdx.x == 0 && (long)blockIdx.x < total) issue(blockIdx.x, 0);
+	const int w = oct.l[0].w, h = oct.l[0].h;
+	constexpr int ROWS_PER_PASS = TILE_THREADS / TX;
+	const int tx = threadIdx.x % TX, ty0 = threadIdx.x / TX;
+	uint32_t n = 0;
+	for (long item = blockIdx.x; item < total; item += gridDim.x, n++) {
+		const float* tile;
+		if (SKIP == 1) {
+			const int b = n & 1;
+			// buffer b^1 was last read in the previous iteration, which ended with __syncthreads
+			if (threadIdx.x == 0 && item + gridDim.x < total) issue(item + gridDim.x, b ^ 1);
+			sm100::mbar_wait(&full[b], (n >> 1) & 1);
+			tile = buf + b * G::BUF;
+		} else {
+			// TMA buffer = buf, planes = buf + BUF
+			sm100::mbar_wait(&full[0], n & 1);
+			float* planes = buf + G::BUF;
+			const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+			for (int r = warp; r < G::TH; r += TILE_THREADS / 32) {
+				const float2* src = reinterpret_cast<const float2*>(buf + r * G::BOXW);
+				for (int j = lane; j < G::PW; j += 32) {
+					const float2 v = src[j];
+					planes[r * G::PW + j] = v.x;
+					planes[G::PLANE + r * G::PW + j] = v.y;
+				}
+			}
+			__syncthreads();                       // TMA buffer drained, planes complete
+			if (threadIdx.x == 0 && item + gridDim.x < total) issue(item + gridDim.x, 0);
+			tile = planes;
+		}
+		const int frame = (int)(item / per_frame), t = (int)(item - (long)frame * per_frame);
+		const int tyi = t / tiles_x, txi = t - tyi * tiles_x;
+		const float* ii = ii_all + (long)frame * W * H;
+		float* inten = inten_all + (long)frame * inten_per_frame;
+		const int x = txi * TX + tx;
+		if (x < w) {
+#pragma unroll 1
+			for (int ty = ty0; ty < TY; ty += ROWS_PER_PASS) {
+				const int y = tyi * TY + ty;
+				if (y < h) TileLayers<G, SKIP, S0, STEP, NS, 0>::run(tile + ty * SKIP * (SKIP == 1 ? G::BOXW : G::PW) + tx, ii, W, H, oct.l, inten, x, y);
+			}
+		}
+		__syncthreads();
+	}
+}
+
+typedef CUresult (*HessianEncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                         const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                         CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+template <int SKIP, int S0, int STEP, int NS, int TX, int TY>
+bool launch_hessian_tma(const float* d_ii, const Plan& plan, int first_layer, float* d_inten, int batch, cudaStream_t st) {
+	typedef TmaGeo<SKIP, S0, STEP, NS, TX, TY> G;
+	if ((plan.W & 3) != 0 || (reinterpret_cast<uintptr_t>(d_ii) & 15) != 0) return false;
+	static HessianEncodeTiledFn encode = nullptr;
+	if (!encode) {
+		void* p = nullptr;
+		cudaDriverEntryPointQueryResult q;
+		if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess || !p || q != cudaDriverEntryPointSuccess) {
+			cudaGetLastError();
+			return false;
+		}
+		encode = reinterpret_cast<HessianEncodeTiledFn>(p);
+	}
+	OctaveLayers oct{};
+	for (int i = 0; i < NS; i++) oct.l[i] = plan.layers[first_layer + i];
+	const int tiles_x = div_up(oct.l[0].w, TX), tiles_y = div_up(oct.l[0].h, TY);
+	if (tiles_x * tiles_y == 0) return true;
+	CUtensorMap tm;
+	const cuuint64_t dims[3] = {(cuuint64_t)plan.W, (cuuint64_t)plan.H, (cuuint64_t)batch};
+	const cuuint64_t strides[2] = {(cuuint64_t)plan.W * 4, (cuuint64_t)plan.W * plan.H * 4};
+	const cuuint32_t box[3] = {(cuuint32_t)G::BOXW, (cuuint32_t)G::TH, 1};
+	const cuuint32_t estr[3] = {1, 1, 1};
+	if (encode(&tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<float*>(d_ii), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+	           CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+		return false;
+	static int sm_count = 0;
+	static bool attr = false;
+	constexpr int smem = 2 * G::BUF * 4 + 16 + 128;
+	auto kern = hessian_tma_kernel<SKIP, S0, STEP, NS, TX, TY>;
+	if (!attr) {
+		int dev = 0;
+		BS_CUDA(cudaGetDevice(&dev));
+		BS_CUDA(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev));
+		BS_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+		attr = true;
+	}
+	int per_sm = (200 * 1024) / (smem + 1024);
+	per_sm = per_sm > 4 ? 4 : (per_sm < 1 ? 1 : per_sm);
+	const long total = (long)tiles_x * tiles_y * batch;
+	const int grid = (int)std::min<long>(total, (long)sm_count * per_sm);
+	BS_LAUNCH(kern, grid, TILE_THREADS, smem, st, tm, d_ii, plan.W, plan.H, oct, tiles_x, tiles_y, batch, plan.inten_per_frame, d_inten);
+	return true;
 }
 
 }  // namespace bs

@@ -50,6 +50,14 @@ __device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* m, int
 	             : "memory");
 }
 
+// 3-D tiled load (x, y, frame); out-of-range coordinates are filled with zeros
+__device__ __forceinline__ void tma_load_3d(void* dst, const CUtensorMap* m, int c0, int c1, int c2, uint64_t* bar) {
+	asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];" ::"r"(
+	                 smem_u32(dst)),
+	             "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2)
+	             : "memory");
+}
+
 // ---------------------------------------------------------------- tcgen05 / TMEM
 // all 32 lanes of ONE warp; the TMEM base address is written to *slot (shared memory)
 template <int COLS>
