@@ -68,12 +68,30 @@ nms_kernel(const Plan* __restrict__ plan, const float* __restrict__ inten_all, R
 		const int x0 = V.border + bx * step, y0 = V.border + by * step;
 		const int x1 = min(x0 + step, endX), y1 = min(y0 + step, endY);
 		// searchBlock: first strict maximum in raster order
-		for (int y = y0; y < y1; y++)
-			for (int x = x0; x < x1; x++) {
-				const float v = __ldg(mid + (long)y * w + x);
-				if (v > peak) { peak = v; peakX = x; peakY = y; }
-			}
+		if (step == 3 && x1 - x0 == 3 && y1 - y0 == 3) {
+			// the common case (radius 2, full block): nine loads in flight at once instead of a dependent loop
+			const float* p = mid + (long)y0 * w + x0;
+			float v[9];
+#pragma unroll
+			for (int k = 0; k < 9; k++) v[k] = __ldg(p + (k / 3) * w + (k % 3));
+#pragma unroll
+			for (int k = 0; k < 9; k++)
+				if (v[k] > peak) { peak = v[k]; peakX = x0 + k % 3; peakY = y0 + k / 3; }
+		} else {
+			for (int y = y0; y < y1; y++)
+				for (int x = x0; x < x1; x++) {
+					const float v = __ldg(mid + (long)y * w + x);
+					if (v > peak) { peak = v; peakX = x; peakY = y; }
+				}
+		}
 		ok = peak >= plan->threshold && peak != FLT_MAX;
+		if (ok && mode == NMS_PLAIN) {
+			// Every test below must pass for a point to be emitted, so their order is free: try the two cheapest reads of
+			// checkMax first (the same pixel in the neighbouring layers, FastHessianFeatureDetector.java:304-313).  Not in the
+			// n-best modes, where the extractor's own output is needed.
+			const long c = (long)peakY * w + peakX;
+			if (__ldg(inten + plan->layers[V.lower].offset + c) >= peak || __ldg(inten + plan->layers[V.upper].offset + c) >= peak) ok = false;
+		}
 		if (ok) {
 			// checkLocalMax: strictly greater than everything else in the (2r+1)^2 window clamped to the image
 			const int wx0 = max(peakX - radius, 0), wx1 = min(peakX + radius, w - 1);

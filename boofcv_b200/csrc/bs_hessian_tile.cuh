@@ -12,6 +12,7 @@
 #pragma once
 #include "bs_sm100.cuh"
 #include <algorithm>
+#include <cstdlib>
 
 namespace bs {
 
@@ -288,7 +289,8 @@ bool launch_hessian_tma(const float* d_ii, const Plan& plan, int first_layer, fl
 		attr = true;
 	}
 	int per_sm = (200 * 1024) / (smem + 1024);
-	per_sm = per_sm > 4 ? 4 : (per_sm < 1 ? 1 : per_sm);
+	static const int per_sm_cap = getenv("BS_HT_PER_SM") ? atoi(getenv("BS_HT_PER_SM")) : 4;
+	per_sm = per_sm > per_sm_cap ? per_sm_cap : (per_sm < 1 ? 1 : per_sm);
 	const long total = (long)tiles_x * tiles_y * batch;
 	const int grid = (int)std::min<long>(total, (long)sm_count * per_sm);
 	BS_LAUNCH(kern, grid, TILE_THREADS, smem, st, tm, d_ii, plan.W, plan.H, oct, tiles_x, tiles_y, batch, plan.inten_per_frame, d_inten);
