@@ -92,15 +92,29 @@ nms_kernel(const Plan* __restrict__ plan, const float* __restrict__ inten_all, R
 			const long c = (long)peakY * w + peakX;
 			if (__ldg(inten + plan->layers[V.lower].offset + c) >= peak || __ldg(inten + plan->layers[V.upper].offset + c) >= peak) ok = false;
 		}
-		if (ok) {
-			// checkLocalMax: strictly greater than everything else in the (2r+1)^2 window clamped to the image
-			const int wx0 = max(peakX - radius, 0), wx1 = min(peakX + radius, w - 1);
-			const int wy0 = max(peakY - radius, 0), wy1 = min(peakY + radius, h - 1);
-			for (int y = wy0; y <= wy1 && ok; y++)
-				for (int x = wx0; x <= wx1; x++) {
-					const float v = __ldg(mid + (long)y * w + x);
-					if (v >= peak && !(x == peakX && y == peakY)) { ok = false; break; }
-				}
+	}
+	// From here on the warp works on one candidate at a time, all 32 lanes together: ncu showed the per-thread version at 12
+	// active lanes per instruction, i.e. every warp paid the 25-pixel window, the 18 scale neighbours and the refinement of its
+	// few candidates serially.
+	const int lane = threadIdx.x & 31;
+	{
+		// checkLocalMax: strictly greater than everything else in the (2r+1)^2 window clamped to the image
+		unsigned todo = __ballot_sync(0xffffffffu, ok);
+		while (todo) {
+			const int src = __ffs(todo) - 1;
+			todo &= todo - 1;
+			const int cx = __shfl_sync(0xffffffffu, peakX, src), cy = __shfl_sync(0xffffffffu, peakY, src);
+			const float val = __shfl_sync(0xffffffffu, peak, src);
+			const int wx0 = max(cx - radius, 0), wx1 = min(cx + radius, w - 1);
+			const int wy0 = max(cy - radius, 0), wy1 = min(cy + radius, h - 1);
+			const int ww = wx1 - wx0 + 1, n = ww * (wy1 - wy0 + 1);
+			bool bad = false;
+			for (int k = lane; k < n; k += 32) {
+				const int y = wy0 + k / ww, x = wx0 + k % ww;
+				const float v = __ldg(mid + (long)y * w + x);
+				bad = bad || (v >= val && !(x == cx && y == cy));
+			}
+			if (__any_sync(0xffffffffu, bad) && lane == src) ok = false;
 		}
 	}
 	if (mode != NMS_PLAIN) {
@@ -114,30 +128,46 @@ nms_kernel(const Plan* __restrict__ plan, const float* __restrict__ inten_all, R
 		const int ir = V.border + radius;
 		if (peakX < ir || peakX >= w - ir || peakY < ir || peakY >= h - ir) ok = false;
 	}
-	if (ok) {
+	{
 		const float* lower = inten + plan->layers[V.lower].offset;
 		const float* upper = inten + plan->layers[V.upper].offset;
-		const float val = __ldg(mid + (long)peakY * w + peakX);
-		if (scale_neighbour_ok(lower, w, h, val, peakX, peakY) && scale_neighbour_ok(upper, w, h, val, peakX, peakY)) {
-			const long c = (long)peakY * w + peakX;
-			const float peakXf = poly_peak(__ldg(mid + c - 1), val, __ldg(mid + c + 1));
-			const float peakYf = poly_peak(__ldg(mid + c - w), val, __ldg(mid + c + w));
-			const float peakS = poly_peak(__ldg(lower + c), val, __ldg(upper + c));
-			const float interpX = ((float)peakX + peakXf) * (float)M.skip;
-			const float interpY = ((float)peakY + peakYf) * (float)M.skip;
-			const float interpS = (float)V.level_size + peakS * (float)V.level_step;
-			pt.x = (double)interpX; pt.y = (double)interpY;
-			pt.scale = 1.2 * (double)interpS / 9.0;
-			pt.response = val;
-			pt.px = (int16_t)peakX; pt.py = (int16_t)peakY;
-			pt.octave = (int16_t)V.octave; pt.level = (int16_t)V.level;
-			pt.pad = 0;
-			found = true;
+		unsigned todo = __ballot_sync(0xffffffffu, ok);
+		while (todo) {
+			const int src = __ffs(todo) - 1;
+			todo &= todo - 1;
+			const int cx = __shfl_sync(0xffffffffu, peakX, src), cy = __shfl_sync(0xffffffffu, peakY, src);
+			const float val = __shfl_sync(0xffffffffu, peak, src);
+			// checkMax :304-313 in both neighbouring layers: lanes 0-8 the lower one, 9-17 the upper one; out-of-image reads are 0
+			bool bad = false;
+			if (lane < 18) {
+				const int k = lane < 9 ? lane : lane - 9;
+				const int x = cx - 1 + k % 3, y = cy - 1 + k / 3;
+				const float* img = lane < 9 ? lower : upper;
+				const float v = (x >= 0 && y >= 0 && x < w && y < h) ? __ldg(img + (long)y * w + x) : 0.0f;
+				bad = v >= val;
+			}
+			if (__any_sync(0xffffffffu, bad)) continue;
+			if (lane == src) {
+				const long c = (long)cy * w + cx;
+				const float peakXf = poly_peak(__ldg(mid + c - 1), val, __ldg(mid + c + 1));
+				const float peakYf = poly_peak(__ldg(mid + c - w), val, __ldg(mid + c + w));
+				const float peakS = poly_peak(__ldg(lower + c), val, __ldg(upper + c));
+				const float interpX = ((float)cx + peakXf) * (float)M.skip;
+				const float interpY = ((float)cy + peakYf) * (float)M.skip;
+				const float interpS = (float)V.level_size + peakS * (float)V.level_step;
+				pt.x = (double)interpX; pt.y = (double)interpY;
+				pt.scale = 1.2 * (double)interpS / 9.0;
+				pt.response = val;
+				pt.px = (int16_t)cx; pt.py = (int16_t)cy;
+				pt.octave = (int16_t)V.octave; pt.level = (int16_t)V.level;
+				pt.pad = 0;
+				found = true;
+			}
 		}
 	}
 	// rank inside the CTA in thread (= block-raster) order
 	const unsigned ballot = __ballot_sync(0xffffffffu, found);
-	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+	const int warp = threadIdx.x >> 5;
 	if (lane == 0) warp_counts[warp] = __popc(ballot);
 	__syncthreads();
 	int base = 0, total = 0;
