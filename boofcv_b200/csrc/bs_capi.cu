@@ -218,7 +218,7 @@ void bs_surf::ensure(int w, int h, int nbatch) {
 	const size_t nctas = (size_t)std::max(plan.ctas_per_frame, 1) * chunk;
 	d_stage.reserve(nctas * NMS_CTA_BLOCKS * sizeof(RawPoint));
 	d_counts.reserve(nctas * sizeof(int));
-	d_offsets.reserve(nctas * sizeof(int));
+	d_offsets.reserve((nctas + chunk) * sizeof(int));      // + one frame total per frame of the chunk
 	if (plan.max_per_level > 0) {          // SelectNBestFeatures scratch: one key and one flag per NMS block
 		d_keys.reserve(nctas * NMS_CTA_BLOCKS * sizeof(unsigned));
 		d_keep.reserve(nctas * NMS_CTA_BLOCKS);
@@ -693,7 +693,7 @@ int bs_fh_detect(int device, int ii_type, const void* ii, int width, int height,
 		d_inten.reserve((size_t)std::max<long>(plan.inten_per_frame, 1) * 4);
 		const size_t nctas = std::max(plan.ctas_per_frame, 1);
 		d_stage.reserve(nctas * NMS_CTA_BLOCKS * sizeof(RawPoint));
-		d_counts.reserve(nctas * 4); d_offsets.reserve(nctas * 4); d_fo.reserve(8);
+		d_counts.reserve(nctas * 4); d_offsets.reserve((nctas + 1) * 4); d_fo.reserve(8);
 		if (plan.max_per_level > 0) { d_keys.reserve(nctas * NMS_CTA_BLOCKS * 4); d_keep.reserve(nctas * NMS_CTA_BLOCKS); }
 		BS_CUDA(cudaMemset(d_fo.p, 0, 8));
 		BS_CUDA(cudaDeviceSynchronize());

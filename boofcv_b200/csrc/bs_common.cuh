@@ -143,6 +143,7 @@ void launch_nms(const Plan& plan, const Plan* d_plan, const float* d_inten, int 
 // Exclusive scan of the per-CTA counts of the chunk's frames (frame0 .. frame0+batch), continuing from
 // d_frame_offset[frame0]; writes d_frame_offset[frame0+1 .. frame0+batch] and the per-CTA pool offsets, then gathers the
 // staged points into the pool in (frame, octave, level, block-row, block-column) order.
+// d_cta_offsets needs batch * ctas_per_frame + batch ints (the frame totals live behind the per-CTA offsets).
 void launch_compact(const Plan& plan, int batch, int frame0, const RawPoint* d_stage, const int* d_cta_counts, int* d_cta_offsets,
                     int* d_frame_offset, const Pool& pool, cudaStream_t st);
 

@@ -290,51 +290,66 @@ void launch_nms(const Plan& plan, const Plan* d_plan, const float* d_inten, int 
 // ---------------------------------------------------------------- ordered compaction
 constexpr int SCAN_THREADS = 1024;
 
-// one CTA: running exclusive scan over [batch][ctas] counts
+// one CTA per frame: exclusive scan of the frame's per-CTA counts (relative offsets) and the frame total
 __global__ void __launch_bounds__(SCAN_THREADS)
-scan_counts_kernel(const int* __restrict__ counts, int ctas, int batch, int frame0, int* __restrict__ offsets,
-                   int* __restrict__ frame_offset) {
+scan_counts_kernel(const int* __restrict__ counts, int ctas, int* __restrict__ offsets, int* __restrict__ frame_total) {
 	__shared__ int warp_sums[SCAN_THREADS / 32];
 	__shared__ int carry;
 	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-	if (threadIdx.x == 0) carry = frame_offset[frame0];
+	const int f = blockIdx.x;
+	if (threadIdx.x == 0) carry = 0;
 	__syncthreads();
-	for (int f = 0; f < batch; f++) {
-		for (int c0 = 0; c0 < ctas; c0 += SCAN_THREADS) {
-			const int c = c0 + threadIdx.x;
-			const int v = c < ctas ? counts[(long)f * ctas + c] : 0;
-			int incl = v;
+	for (int c0 = 0; c0 < ctas; c0 += SCAN_THREADS) {
+		const int c = c0 + threadIdx.x;
+		const int v = c < ctas ? counts[(long)f * ctas + c] : 0;
+		int incl = v;
 #pragma unroll
-			for (int d = 1; d < 32; d <<= 1) {
-				const int t = __shfl_up_sync(0xffffffffu, incl, d);
-				if (lane >= d) incl += t;
-			}
-			if (lane == 31) warp_sums[warp] = incl;
-			__syncthreads();
-			int wbase = 0, chunk_total = 0;
-			for (int k = 0; k < SCAN_THREADS / 32; k++) {
-				const int s = warp_sums[k];
-				if (k < warp) wbase += s;
-				chunk_total += s;
-			}
-			const int base = carry;
-			if (c < ctas) offsets[(long)f * ctas + c] = base + wbase + incl - v;
-			__syncthreads();
-			if (threadIdx.x == 0) carry = base + chunk_total;
-			__syncthreads();
+		for (int d = 1; d < 32; d <<= 1) {
+			const int t = __shfl_up_sync(0xffffffffu, incl, d);
+			if (lane >= d) incl += t;
 		}
-		if (threadIdx.x == 0) frame_offset[frame0 + f + 1] = carry;
+		if (lane == 31) warp_sums[warp] = incl;
 		__syncthreads();
+		int wbase = 0, chunk_total = 0;
+		for (int k = 0; k < SCAN_THREADS / 32; k++) {
+			const int s = warp_sums[k];
+			if (k < warp) wbase += s;
+			chunk_total += s;
+		}
+		const int base = carry;
+		if (c < ctas) offsets[(long)f * ctas + c] = base + wbase + incl - v;
+		__syncthreads();
+		if (threadIdx.x == 0) carry = base + chunk_total;
+		__syncthreads();
+	}
+	if (threadIdx.x == 0) frame_total[f] = carry;
+}
+
+// frame_offset[frame0 + f + 1] = frame_offset[frame0] + sum of the totals of frames 0..f of the chunk (one warp)
+__global__ void frame_offsets_kernel(const int* __restrict__ frame_total, int batch, int frame0, int* __restrict__ frame_offset) {
+	const int lane = threadIdx.x;
+	int carry = frame_offset[frame0];
+	for (int f0 = 0; f0 < batch; f0 += 32) {
+		const int f = f0 + lane;
+		const int v = f < batch ? frame_total[f] : 0;
+		int incl = v;
+#pragma unroll
+		for (int d = 1; d < 32; d <<= 1) {
+			const int t = __shfl_up_sync(0xffffffffu, incl, d);
+			if (lane >= d) incl += t;
+		}
+		if (f < batch) frame_offset[frame0 + f + 1] = carry + incl;
+		carry += __shfl_sync(0xffffffffu, incl, 31);
 	}
 }
 
 __global__ void __launch_bounds__(NMS_CTA_BLOCKS)
 gather_points_kernel(const RawPoint* __restrict__ stage, const int* __restrict__ counts, const int* __restrict__ offsets,
-                     int ctas, int frame0, Pool pool) {
+                     const int* __restrict__ frame_offset, int ctas, int frame0, Pool pool) {
 	const long idx = (long)blockIdx.y * ctas + blockIdx.x;
 	const int n = counts[idx];
 	if ((int)threadIdx.x >= n) return;
-	const long dst = (long)offsets[idx] + threadIdx.x;
+	const long dst = (long)frame_offset[frame0 + blockIdx.y] + offsets[idx] + threadIdx.x;
 	if (dst >= pool.cap) return;      // counted, not stored: the host reports BS_ERR_CAPACITY
 	const RawPoint p = stage[idx * NMS_CTA_BLOCKS + threadIdx.x];
 	pool.xy[2 * dst] = p.x; pool.xy[2 * dst + 1] = p.y;
@@ -347,11 +362,13 @@ gather_points_kernel(const RawPoint* __restrict__ stage, const int* __restrict__
 void launch_compact(const Plan& plan, int batch, int frame0, const RawPoint* d_stage, const int* d_cta_counts, int* d_cta_offsets,
                     int* d_frame_offset, const Pool& pool, cudaStream_t st) {
 	if (batch <= 0) return;
-	BS_LAUNCH(scan_counts_kernel, 1, SCAN_THREADS, 0, st, d_cta_counts, plan.ctas_per_frame, batch, frame0, d_cta_offsets,
-	          d_frame_offset);
+	// the per-CTA offset array has one spare int per frame at its end: the frame totals
+	int* d_frame_total = d_cta_offsets + (long)batch * plan.ctas_per_frame;
+	BS_LAUNCH(scan_counts_kernel, batch, SCAN_THREADS, 0, st, d_cta_counts, plan.ctas_per_frame, d_cta_offsets, d_frame_total);
+	BS_LAUNCH(frame_offsets_kernel, 1, 32, 0, st, (const int*)d_frame_total, batch, frame0, d_frame_offset);
 	if (plan.ctas_per_frame == 0) return;
-	BS_LAUNCH(gather_points_kernel, dim3(plan.ctas_per_frame, batch), NMS_CTA_BLOCKS, 0, st, d_stage, d_cta_counts, d_cta_offsets,
-	          plan.ctas_per_frame, frame0, pool);
+	BS_LAUNCH(gather_points_kernel, dim3(plan.ctas_per_frame, batch), NMS_CTA_BLOCKS, 0, st, d_stage, d_cta_counts, (const int*)d_cta_offsets,
+	          (const int*)d_frame_offset, plan.ctas_per_frame, frame0, pool);
 }
 
 }  // namespace bs
