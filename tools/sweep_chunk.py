@@ -5,7 +5,7 @@ import sys
 
 batch = sys.argv[1] if len(sys.argv) > 1 else "256"
 for c in sys.argv[2:] or ["1", "2", "4", "8"]:
-    out = subprocess.run([sys.executable, "bench.py", "--batch", batch, "--steps", "2", "--chunk", c, "--no-cpu", "--no-e2e"],
+    out = subprocess.run([sys.executable, "bench.py", "--batch", batch, "--steps", "2", "--chunk", c, "--no-cpu", "--no-e2e", "--no-assoc"],
                          capture_output=True, text=True)
     try:
         d = json.loads(out.stdout.strip().splitlines()[-1])

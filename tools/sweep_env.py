@@ -14,7 +14,7 @@ var, vals = args[0], args[1:]
 for v in vals:
     env = dict(os.environ)
     env[var] = v
-    out = subprocess.run([sys.executable, "bench.py", "--batch", "256", "--steps", "2", "--chunk", "8", "--no-cpu", "--no-e2e"] + extra,
+    out = subprocess.run([sys.executable, "bench.py", "--batch", "256", "--steps", "2", "--chunk", "8", "--no-cpu", "--no-e2e", "--no-assoc"] + extra,
                          capture_output=True, text=True, env=env)
     try:
         d = json.loads(out.stdout.strip().splitlines()[-1])
