@@ -22,7 +22,13 @@
 
 namespace bs {
 
-constexpr int DESC_WARPS = 8;
+#ifndef BS_DESC_WARPS
+#define BS_DESC_WARPS 4
+#endif
+// features per CTA round (<= 16: the batched orientation sums use two lanes per feature).  Measured per 256 frames (1080p):
+// 4 warps x 8 CTAs/SM 24.0 ms, 8 x 4 24.8 ms, 16 x 2 34.0 ms, 2 x 16 26.4 ms; fewer registers for more resident warps (48
+// registers, 40 warps) 43 ms: the kernel is bound by the L1 data pipe and more warps only thrash it.
+constexpr int DESC_WARPS = BS_DESC_WARPS;
 
 // SurfDescribeOps.isInside (:119-159,183-204) only selects between the reference's unchecked gradient operator and its
 // bounds-checked wrapper (which yields (0,0) outside).  Whenever isInside holds every sample passes the bounds check, so
@@ -295,8 +301,11 @@ static DescribeSmem describe_smem(const DescribeParams& p) {
 	return s;
 }
 
+#ifndef BS_DESC_MIN_BLOCKS
+#define BS_DESC_MIN_BLOCKS 8
+#endif
 template <typename T>
-__global__ void __launch_bounds__(DESC_WARPS * 32)
+__global__ void __launch_bounds__(DESC_WARPS * 32, BS_DESC_MIN_BLOCKS)
 describe_kernel(const T* __restrict__ ii_all, int W, int H, DescribeParams P, DescribeTables tabs, DescribeSmem S, Pool pool,
                 const int* __restrict__ d_begin, const int* __restrict__ d_end, int frame0, int do_orientation, int do_describe) {
 	extern __shared__ __align__(16) unsigned char smem[];
@@ -405,7 +414,10 @@ void launch_describe(const T* d_ii, int W, int H, const DescribeParams& p, const
 	if (S.total > 220 * 1024) fail(BS_ERR_ARG, "orientation/descriptor configuration needs too much shared memory");
 	BS_CUDA(cudaFuncSetAttribute(describe_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, S.total));
 	int ctas_per_sm = (224 * 1024) / (S.total + 1024);
-	ctas_per_sm = ctas_per_sm > 4 ? 4 : (ctas_per_sm < 1 ? 1 : ctas_per_sm);
+	const int cap = BS_DESC_MIN_BLOCKS > 1 ? BS_DESC_MIN_BLOCKS : 32 / DESC_WARPS;   // resident CTAs per SM the register budget allows
+	static const int env_cap = getenv("BS_DESC_CTAS") ? atoi(getenv("BS_DESC_CTAS")) : 0;
+	ctas_per_sm = ctas_per_sm > cap ? cap : (ctas_per_sm < 1 ? 1 : ctas_per_sm);
+	if (env_cap > 0 && env_cap < ctas_per_sm) ctas_per_sm = env_cap;
 	BS_LAUNCH((describe_kernel<T>), sm_count * ctas_per_sm, DESC_WARPS * 32, S.total, st, d_ii, W, H, p, t, S, pool, d_begin, d_end, frame0,
 	          do_orientation ? 1 : 0, do_describe ? 1 : 0);
 }

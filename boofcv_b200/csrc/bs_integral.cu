@@ -15,7 +15,7 @@ namespace bs {
 
 constexpr int ROWS_WARPS = 2;        // warps per CTA in the row pass (32 rows each)
 constexpr int COL_THREADS = 64;      // threads per CTA in the column pass
-constexpr int COL_UNROLL = 8;        // rows prefetched per step in the column pass
+constexpr int COL_UNROLL = 16;       // rows per step in the column pass (one step ahead is in flight)
 
 template <typename TI, typename TO, typename ACC>
 __global__ void __launch_bounds__(ROWS_WARPS * 32)
@@ -29,15 +29,25 @@ integral_rows_kernel(const TI* __restrict__ in, long in_frame_stride, int in_str
 	ACC(*t)[33] = tile[warp];
 	const int rows = min(32, H - y0);
 	ACC total = 0;
+	// the tile after the current one is already in flight (registers) while the current one is scanned: with only
+	// rows x frames / 32 warps in the grid nothing else hides the load latency
+	ACC nxt[32];
+	auto fetch = [&](int x0) {
+		const int x = x0 + lane;
+#pragma unroll
+		for (int r = 0; r < 32; r++) {
+			ACC v = 0;
+			if (x < W && r < rows) v = (ACC)src[(long)(y0 + r) * in_stride + x];
+			nxt[r] = v;
+		}
+	};
+	fetch(0);
 	for (int x0 = 0; x0 < W; x0 += 32) {
 		const int x = x0 + lane;
 		const bool xin = x < W;
 #pragma unroll
-		for (int r = 0; r < 32; r++) {
-			ACC v = 0;
-			if (xin && r < rows) v = (ACC)src[(long)(y0 + r) * in_stride + x];
-			t[r][lane] = v;
-		}
+		for (int r = 0; r < 32; r++) t[r][lane] = nxt[r];
+		if (x0 + 32 < W) fetch(x0 + 32);
 		__syncwarp();
 		// lane = row: the reference's serial `total += in[x]`
 #pragma unroll
@@ -61,14 +71,26 @@ integral_cols_kernel(TO* __restrict__ out, int W, int H) {
 	TO* p = out + (long)blockIdx.y * W * H + x;
 	ACC acc = (ACC)p[0];      // first row is the plain running sum
 	int y = 1;
-	for (; y + COL_UNROLL <= H; y += COL_UNROLL) {
-		ACC v[COL_UNROLL];
+	// software pipeline: the next COL_UNROLL rows are loaded while the current ones are accumulated and stored
+	ACC cur[COL_UNROLL], nxt[COL_UNROLL];
+	if (y + COL_UNROLL <= H) {
 #pragma unroll
-		for (int k = 0; k < COL_UNROLL; k++) v[k] = (ACC)p[(long)(y + k) * W];
+		for (int k = 0; k < COL_UNROLL; k++) cur[k] = (ACC)p[(long)(y + k) * W];
+	}
+	for (; y + COL_UNROLL <= H; y += COL_UNROLL) {
+		const bool more = y + 2 * COL_UNROLL <= H;
+		if (more) {
+#pragma unroll
+			for (int k = 0; k < COL_UNROLL; k++) nxt[k] = (ACC)p[(long)(y + COL_UNROLL + k) * W];
+		}
 #pragma unroll
 		for (int k = 0; k < COL_UNROLL; k++) {
-			acc = (ACC)(acc + v[k]);      // out[y-1][x] + total
+			acc = (ACC)(acc + cur[k]);      // out[y-1][x] + total
 			p[(long)(y + k) * W] = (TO)acc;
+		}
+		if (more) {
+#pragma unroll
+			for (int k = 0; k < COL_UNROLL; k++) cur[k] = nxt[k];
 		}
 	}
 	for (; y < H; y++) {
