@@ -85,6 +85,14 @@ nms_kernel(const Plan* __restrict__ plan, const float* __restrict__ inten_all, R
 				}
 		}
 		ok = peak >= plan->threshold && peak != FLT_MAX;
+		if (ok) {
+			// part of checkLocalMax, done per thread before the warp-wide window test: the four direct neighbours (most block
+			// maxima that are not window maxima lose against one of them)
+			const long c = (long)peakY * w + peakX;
+			if ((peakX > 0 && __ldg(mid + c - 1) >= peak) || (peakX + 1 < w && __ldg(mid + c + 1) >= peak) ||
+			    (peakY > 0 && __ldg(mid + c - w) >= peak) || (peakY + 1 < h && __ldg(mid + c + w) >= peak))
+				ok = false;
+		}
 		if (ok && mode == NMS_PLAIN) {
 			// Every test below must pass for a point to be emitted, so their order is free: try the two cheapest reads of
 			// checkMax first (the same pixel in the neighbouring layers, FastHessianFeatureDetector.java:304-313).  Not in the

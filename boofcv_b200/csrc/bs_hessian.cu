@@ -174,7 +174,7 @@ bool try_tiled<float>(const float* d_ii, const Plan& plan, int first, int ns, fl
 		return true;
 	}
 	if (L0.skip == 2 && L0.size == 15 && step == 12) {
-		if (!((tma_mask & 2) && launch_hessian_tma<2, 15, 12, 4, 32, 16>(d_ii, plan, first, d_inten, batch, st)))
+		if (!((tma_mask & 2) && launch_hessian_tma<2, 15, 12, 4, 32, 16, 512>(d_ii, plan, first, d_inten, batch, st)))
 			launch_hessian_tile<2, 15, 12, 4, 32, 16>(d_ii, plan, first, d_inten, batch, st);
 		return true;
 	}

@@ -179,8 +179,8 @@ template <int SKIP, int S0, int STEP, int NS, int TX, int TY> struct TmaGeo {
 	}
 };
 
-template <int SKIP, int S0, int STEP, int NS, int TX, int TY>
-__global__ void __launch_bounds__(TILE_THREADS)
+template <int SKIP, int S0, int STEP, int NS, int TX, int TY, int THREADS>
+__global__ void __launch_bounds__(THREADS)
 hessian_tma_kernel(const __grid_constant__ CUtensorMap tm, const float* __restrict__ ii_all, int W, int H, OctaveLayers oct, int tiles_x,
                    int tiles_y, int frames, long inten_per_frame, float* __restrict__ inten_all) {
 	typedef TmaGeo<SKIP, S0, STEP, NS, TX, TY> G;
@@ -203,7 +203,7 @@ hessian_tma_kernel(const __grid_constant__ CUtensorMap tm, const float* __restri
 	};
 	if (threadIdx.x == 0 && (long)blockIdx.x < total) issue(blockIdx.x, 0);
 	const int w = oct.l[0].w, h = oct.l[0].h;
-	constexpr int ROWS_PER_PASS = TILE_THREADS / TX;
+	constexpr int ROWS_PER_PASS = THREADS / TX;
 	const int tx = threadIdx.x % TX, ty0 = threadIdx.x / TX;
 	uint32_t n = 0;
 	for (long item = blockIdx.x; item < total; item += gridDim.x, n++) {
@@ -219,7 +219,7 @@ hessian_tma_kernel(const __grid_constant__ CUtensorMap tm, const float* __restri
 			sm100::mbar_wait(&full[0], n & 1);
 			float* planes = buf + G::BUF;
 			const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-			for (int r = warp; r < G::TH; r += TILE_THREADS / 32) {
+			for (int r = warp; r < G::TH; r += THREADS / 32) {
 				const float2* src = reinterpret_cast<const float2*>(buf + r * G::BOXW);
 				for (int j = lane; j < G::PW; j += 32) {
 					const float2 v = src[j];
@@ -251,7 +251,7 @@ typedef CUresult (*HessianEncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuui
                                          const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
                                          CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 
-template <int SKIP, int S0, int STEP, int NS, int TX, int TY>
+template <int SKIP, int S0, int STEP, int NS, int TX, int TY, int THREADS = TILE_THREADS>
 bool launch_hessian_tma(const float* d_ii, const Plan& plan, int first_layer, float* d_inten, int batch, cudaStream_t st) {
 	typedef TmaGeo<SKIP, S0, STEP, NS, TX, TY> G;
 	if ((plan.W & 3) != 0 || (reinterpret_cast<uintptr_t>(d_ii) & 15) != 0) return false;
@@ -280,7 +280,7 @@ bool launch_hessian_tma(const float* d_ii, const Plan& plan, int first_layer, fl
 	static int sm_count = 0;
 	static bool attr = false;
 	constexpr int smem = 2 * G::BUF * 4 + 16 + 128;
-	auto kern = hessian_tma_kernel<SKIP, S0, STEP, NS, TX, TY>;
+	auto kern = hessian_tma_kernel<SKIP, S0, STEP, NS, TX, TY, THREADS>;
 	if (!attr) {
 		int dev = 0;
 		BS_CUDA(cudaGetDevice(&dev));
@@ -293,7 +293,7 @@ bool launch_hessian_tma(const float* d_ii, const Plan& plan, int first_layer, fl
 	per_sm = per_sm > per_sm_cap ? per_sm_cap : (per_sm < 1 ? 1 : per_sm);
 	const long total = (long)tiles_x * tiles_y * batch;
 	const int grid = (int)std::min<long>(total, (long)sm_count * per_sm);
-	BS_LAUNCH(kern, grid, TILE_THREADS, smem, st, tm, d_ii, plan.W, plan.H, oct, tiles_x, tiles_y, batch, plan.inten_per_frame, d_inten);
+	BS_LAUNCH(kern, grid, THREADS, smem, st, tm, d_ii, plan.W, plan.H, oct, tiles_x, tiles_y, batch, plan.inten_per_frame, d_inten);
 	return true;
 }
 
