@@ -61,8 +61,26 @@ void h2d_sync(void* dst, const void* src, size_t bytes) {
 struct DescribeSetup {
 	DescribeParams p{};
 	std::vector<double> ori_w, w, wgrid;
-	DevBuf d_ori_w, d_w, d_wgrid;
+	std::vector<uint16_t> perm;
+	DevBuf d_ori_w, d_w, d_wgrid, d_perm;
 	DescribeTables tables{};
+
+	// visiting order of the G x G sample grid per orientation bin (see DescribeTables::d_perm)
+	void build_perm(int G) {
+		const int n = G * G, R = G / 2;
+		perm.assign((size_t)DESC_PERM_BINS * n, 0);
+		std::vector<std::pair<std::pair<long, double>, int>> key(n);
+		for (int b = 0; b < DESC_PERM_BINS; b++) {
+			const double th = (b + 0.5) * (3.14159265358979323846 / DESC_PERM_BINS), c = std::cos(th), s = std::sin(th);
+			for (int k = 0; k < n; k++) {
+				const int gy = k / G - R, gx = k % G - R;
+				const double y = s * gx + c * gy, x = c * gx - s * gy;
+				key[k] = {{(long)std::floor(y * 4.0 + 1e-9), x}, k};     // bands a quarter of a sample spacing high
+			}
+			std::sort(key.begin(), key.end());
+			for (int k = 0; k < n; k++) perm[(size_t)b * n + k] = (uint16_t)key[k].second;
+		}
+	}
 
 	void build(const bs_ori_cfg& o, const bs_desc_cfg& d) {
 		p.ori_variant = o.variant; p.ori_radius = o.radius; p.ori_sample_width = o.sample_width;
@@ -77,6 +95,8 @@ struct DescribeSetup {
 		p.dof = d.width_large_grid * d.width_large_grid * 4;
 		const int region = d.width_large_grid * d.width_sub_region;
 		p.radius_descriptor = region / 2 + p.overlap;
+		if (region + 2 * p.overlap > 255) fail(BS_ERR_ARG, "descriptor sample grid too large");
+		build_perm(region + 2 * p.overlap);
 		if (d.variant == 0) {
 			// weight = gaussianWidth(weightSigma, radius*2) / weight.get(radius, radius)
 			const int radius = region / 2, width = radius * 2;
@@ -110,8 +130,11 @@ struct DescribeSetup {
 		tables.d_ori_w = p.ori_weighted ? up(d_ori_w, ori_w) : nullptr;
 		tables.d_w = up(d_w, w);
 		tables.d_wgrid = up(d_wgrid, wgrid);
+		d_perm.reserve(perm.size() * sizeof(uint16_t));
+		h2d_sync(d_perm.p, perm.data(), perm.size() * sizeof(uint16_t));
+		tables.d_perm = d_perm.as<uint16_t>();
 	}
-	void release() { d_ori_w.release(); d_w.release(); d_wgrid.release(); }
+	void release() { d_ori_w.release(); d_w.release(); d_wgrid.release(); d_perm.release(); }
 };
 
 struct PoolBufs {

@@ -151,7 +151,12 @@ struct DescribeTables {
 	const double* d_ori_w;     // (2r+1)^2 or null
 	const double* d_w;         // fast: (grid*sub)^2 ; mod: weight_sub (sub+2*overlap)^2
 	const double* d_wgrid;     // mod: grid^2
+	// [DESC_PERM_BINS][G*G] visiting order of the descriptor's sample grid for features whose orientation falls into the
+	// bin (angle mod pi): samples sorted into thin bands of equal image row, left to right, so that the 32 lanes of a
+	// warp read a few cache lines instead of one each.  The order only decides which lane fetches which sample.
+	const uint16_t* d_perm;
 };
+constexpr int DESC_PERM_BINS = 32;
 // Orientation + descriptor for pool entries [*d_begin, *d_end) (device-side range, persistent warps loop over it).
 // ii of frame f is at d_ii + (f - frame0) * W * H.  !do_orientation: use the angles already in pool.angle.
 template <typename T>

@@ -272,6 +272,7 @@ struct Slot {                      // one feature of the round (shared memory)
 	double x, y, scale, angle, c, s;
 	long f;                        // pool index, -1: none
 	int frame;                     // frame index relative to the first frame of the launch
+	int bin;                       // orientation bin of the descriptor's sample visiting order
 	OriGeo og;
 	DescGeo dg;
 };
@@ -382,11 +383,17 @@ describe_kernel(const T* __restrict__ ii_all, int W, int H, DescribeParams P, De
 		}
 		if (do_describe) {
 			// cos/sin of all slots by the first lanes of warp 0
-			if (warp == 0 && lane < DESC_WARPS && slots[lane].f >= 0) { slots[lane].c = sm_cos(slots[lane].angle); slots[lane].s = sm_sin(slots[lane].angle); }
+			if (warp == 0 && lane < DESC_WARPS && slots[lane].f >= 0) {
+				const double a = slots[lane].angle;
+				slots[lane].c = sm_cos(a); slots[lane].s = sm_sin(a);
+				int bin = (int)((a < 0.0 ? a + 3.14159265358979323846 : a) * (DESC_PERM_BINS / 3.14159265358979323846));
+				slots[lane].bin = bin < 0 ? 0 : (bin >= DESC_PERM_BINS ? DESC_PERM_BINS - 1 : bin);   // also catches NaN
+			}
 			__syncthreads();                   // every slot has cos/sin; the orientation scratch is free
 			for (int idx = tid; idx < live * S.desc_g2; idx += NT) {
-				const int j = (int)(((float)idx + 0.5f) * inv_desc), k = idx - j * S.desc_g2;
+				const int j = (int)(((float)idx + 0.5f) * inv_desc);
 				const Slot& sj = slots[j];
+				const int k = __ldg(tabs.d_perm + sj.bin * S.desc_g2 + (idx - j * S.desc_g2));
 				T* gx = reinterpret_cast<T*>(scratch + (size_t)j * S.per_warp + (size_t)P.dof * 8);
 				describe_sample(ii_all + sj.frame * frame_words, W, H, sj.dg, sj.c, sj.s, sj.scale, k, gx, gx + S.desc_g2);
 			}
