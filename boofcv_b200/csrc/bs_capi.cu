@@ -207,7 +207,12 @@ struct bs_surf {
 		ev_stage.clear();
 	}
 
-	bs_surf* lane[2] = {nullptr, nullptr};     // bs_surf_detect_host_batch: two workers, each with its own stream and workspace
+	// bs_surf_detect_host_batch: workers, each with its own stream and workspace.  A lane's turn is upload -> kernels ->
+	// download in stream order; with three lanes the GPU always has the kernels of another turn queued while one lane
+	// uploads and one downloads (two lanes leave it idle for the difference between copy and kernel time).
+	static constexpr int MAX_LANES = 4;
+	bs_surf* lane[MAX_LANES] = {nullptr, nullptr, nullptr, nullptr};
+	int n_lanes = 3;
 
 	int group = 0;
 	template <typename TI, typename TII>
@@ -372,6 +377,7 @@ int bs_surf_create(int device, const bs_fh_cfg* fh, const bs_ori_cfg* ori, const
 		BS_CUDA(cudaEventCreateWithFlags(&s->ev_group[1], cudaEventDisableTiming));
 		BS_CUDA(cudaEventCreateWithFlags(&s->ev_side, cudaEventDisableTiming));
 		s->overlap = getenv("BS_OVERLAP") != nullptr;
+		if (const char* e = getenv("BS_LANES")) s->n_lanes = std::min(std::max(atoi(e), 2), (int)bs_surf::MAX_LANES);
 		s->ds.build(o, d);
 		s->ds.upload();
 		*out = s.release();
@@ -380,7 +386,7 @@ int bs_surf_create(int device, const bs_fh_cfg* fh, const bs_ori_cfg* ori, const
 
 int bs_surf_destroy(bs_surf* s) {
 	if (!s) return BS_OK;
-	for (int k = 0; k < 2; k++) {
+	for (int k = 0; k < bs_surf::MAX_LANES; k++) {
 		if (s->lane[k]) bs_surf_destroy(s->lane[k]);
 		s->lane[k] = nullptr;
 	}
@@ -466,7 +472,8 @@ int bs_surf_detect_host_batch(bs_surf* s, const void* pixels, long frame_stride,
 		if (frame_stride < (long)stride * (height - 1) + width) fail(BS_ERR_ARG, "frames overlap");
 		DeviceGuard g(s->device);
 		s->finish();
-		for (int k = 0; k < 2; k++)
+		const int NL = s->n_lanes;
+		for (int k = 0; k < NL; k++)
 			if (!s->lane[k]) {
 				bs_surf* h = nullptr;
 				if (bs_surf_create(s->device, &s->fh, &s->ori, &s->desc, s->pixel_type, &h) != BS_OK) fail(BS_ERR_CUDA, last_error_cstr());
@@ -477,7 +484,7 @@ int bs_surf_detect_host_batch(bs_surf* s, const void* pixels, long frame_stride,
 		const int sub = 32;                        // frames per lane turn = one integral group
 		frame_offset[0] = 0;
 		long base = 0;                             // features of the frames drained so far
-		struct Turn { int first = 0, n = 0; bool busy = false; } turn[2];
+		struct Turn { int first = 0, n = 0; bool busy = false; } turn[bs_surf::MAX_LANES];
 		auto drain = [&](int k) {
 			Turn& t = turn[k];
 			if (!t.busy) return;
@@ -500,9 +507,9 @@ int bs_surf_detect_host_batch(bs_surf* s, const void* pixels, long frame_stride,
 			base += found;
 			t.busy = false;
 		};
-		int k = 0;
-		for (int f0 = 0; f0 < batch; f0 += sub, k ^= 1) {
-			drain(k);                              // normally a no-op: this lane was drained right after the other one started
+		int k = 0, last = 0;
+		for (int f0 = 0; f0 < batch; f0 += sub, k = (k + 1) % NL) {
+			drain(k);                              // normally a no-op: this lane was drained right after the previous one started
 			bs_surf* h = s->lane[k];
 			h->chunk_req = s->chunk_req; h->pool_req = s->pool_req;
 			const int n = std::min(sub, batch - f0);
@@ -518,10 +525,11 @@ int bs_surf_detect_host_batch(bs_surf* s, const void* pixels, long frame_stride,
 			}
 			h->run(h->d_in.p, (long)width * height, width, width, height, n, h->stream);
 			turn[k].first = f0; turn[k].n = n; turn[k].busy = true;
-			drain(k ^ 1);                          // results of the previous turn go home while this one computes
+			last = k;
+			drain((k + 1) % NL);                   // results of the oldest turn go home while the younger ones upload and compute
 		}
-		drain(k); drain(k ^ 1);                    // k: the lane started before the last one (or nothing), then the last one
-		for (int j = 0; j < 2; j++) BS_CUDA(cudaStreamSynchronize(s->lane[j]->stream));
+		for (int j = 1; j <= NL; j++) drain((last + j) % NL);      // the remaining turns, oldest first
+		for (int j = 0; j < NL; j++) BS_CUDA(cudaStreamSynchronize(s->lane[j]->stream));
 		if (total) *total = base;
 		s->batch = 0; s->pending = false;
 		if (base > cap) fail(BS_ERR_CAPACITY, "more features than the host buffers hold");
