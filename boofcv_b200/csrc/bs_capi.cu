@@ -208,11 +208,11 @@ struct bs_surf {
 	}
 
 	// bs_surf_detect_host_batch: workers, each with its own stream and workspace.  A lane's turn is upload -> kernels ->
-	// download in stream order; with three lanes the GPU always has the kernels of another turn queued while one lane
+	// download in stream order; with three or more lanes the GPU always has the kernels of another turn queued while one lane
 	// uploads and one downloads (two lanes leave it idle for the difference between copy and kernel time).
 	static constexpr int MAX_LANES = 4;
 	bs_surf* lane[MAX_LANES] = {nullptr, nullptr, nullptr, nullptr};
-	int n_lanes = 3;
+	int n_lanes = 4;
 
 	int group = 0;
 	template <typename TI, typename TII>
@@ -231,8 +231,9 @@ void bs_surf::ensure(int w, int h, int nbatch) {
 		h2d_sync(d_plan.p, &plan, sizeof(Plan));
 		W = w; H = h;
 	}
-	// frames per wave: measured 2723 / 3389 / 3680 / 3667+ frames/s at 1 / 4 / 8 / 16 (1080p): launches must be big enough to fill 148 SMs
-	int c = chunk_req > 0 ? chunk_req : 16;
+	// frames per wave: measured 5001 / 5209 / 5317 frames/s at 8 / 16 / 32 (1080p): launches must be big enough to fill 148 SMs
+	// and amortise the tails of the persistent kernels; capped so that the intensity layers stay around 1.5 GB
+	int c = chunk_req > 0 ? chunk_req : (int)std::max<long>(1, std::min<long>(32, (3L << 29) / std::max<long>(plan.inten_per_frame * 4, 1)));
 	c = std::min(c, nbatch);
 	chunk = std::max(c, 1);
 	const size_t px = (size_t)W * H;
