@@ -6,4 +6,5 @@ interface layer (surf, associate).  There is no CPU fallback anywhere in this pa
 from .surf import (FactoryDetectDescribe, ConfigFastHessian, ConfigAverageIntegral, ConfigSlidingIntegral,  # noqa: F401
                    ConfigSurfDescribe, BrightFeature, AssociatedIndex, Point2D_F64, DetectDescribeSurf,
                    HostFeatureBuffers)
-from .associate import FactoryAssociation, ScoreAssociateEuclideanSq_F64, MatchScoreType, AssociateGreedyGPU  # noqa: F401
+from .associate import (FactoryAssociation, ScoreAssociateEuclideanSq_F64, MatchScoreType, AssociateGreedyGPU,  # noqa: F401
+                        AssociateSurfBasic, WrapAssociateSurfBasic)

@@ -143,6 +143,136 @@ class AssociateGreedyGPU:
         return pairs, fit
 
 
+def _as_bright(features):
+    """FastQueue<BrightFeature> -> ([n][dof] float64, white uint8[n]).  Accepts (desc, white) arrays, a dict with "desc"/"white"
+    (DetectDescribeSurf.readFrame) or a sequence of objects with `.value` and `.white`."""
+    if features is None:
+        return None, None
+    if isinstance(features, dict):
+        features = (features["desc"], features["white"])
+    if isinstance(features, tuple) and len(features) == 2 and isinstance(features[0], np.ndarray):
+        d = _as_matrix(features[0]); w = np.ascontiguousarray(np.asarray(features[1]) != 0, np.uint8)
+    else:
+        features = list(features)
+        d = _as_matrix(features)
+        w = np.ascontiguousarray([1 if f.white else 0 for f in features], np.uint8)
+    if len(w) != len(d):
+        raise ValueError("descriptor and laplacian-sign lists differ in length")
+    return d, w
+
+
+class AssociateSurfBasic:
+    """AssociateSurfBasic (F/alg/feature/associate/AssociateSurfBasic.java:36-160): features are split by the sign of the
+    Laplacian (BrightFeature.white), the two classes are associated independently by `assoc` (FactoryAssociation.greedy)
+    and reported with the indices of the input lists.  Runs on the handle of `assoc` (bs_assoc_surf_run)."""
+    def __init__(self, assoc):
+        if not isinstance(assoc, AssociateGreedyGPU):
+            raise ValueError("AssociateSurfBasic needs the GPU greedy associator (FactoryAssociation.greedy)")
+        self.assoc = assoc
+        self._src = (None, None); self._dst = (None, None)
+        self._matches = []; self.unassociatedSrc = np.zeros(0, np.int32); self._unassoc_dst = np.zeros(0, np.int32)
+        self._pairs = None; self._fit = None
+
+    def setSrc(self, src):
+        self._src = _as_bright(src)
+
+    def setDst(self, dst):
+        self._dst = _as_bright(dst)
+
+    def swapLists(self):
+        self._src, self._dst = self._dst, self._src
+
+    def associate(self):
+        (src, sw), (dst, dw) = self._src, self._dst
+        if src is None:
+            raise ValueError("source features not specified")
+        if dst is None:
+            raise ValueError("destination features not specified")
+        n, m = len(src), len(dst)
+        dof = max(src.shape[1] if n else 0, dst.shape[1] if m else 0, 1)
+        if (n and src.shape[1] != dof) or (m and dst.shape[1] != dof):
+            raise ValueError("source and destination descriptors differ in length")
+        L = N.lib()
+        self._pairs = np.full(n, -1, np.int32); self._fit = np.zeros(n, np.float64)
+        if n:
+            N.check(L.bs_assoc_surf_run(self.assoc._h, _p(src), _p(sw), n, _p(dst) if m else None, _p(dw) if m else None, m, dof,
+                                        _p(self._pairs), _p(self._fit)))
+        ms = np.zeros(n, np.int32); md = np.zeros(n, np.int32); sc = np.zeros(n, np.float64)
+        us = np.zeros(n, np.int32); ud = np.zeros(m, np.int32)
+        nm, nus, nud = C.c_int(0), C.c_int(0), C.c_int(0)
+        N.check(L.bs_assoc_surf_matches(_p(self._pairs), _p(self._fit), _p(sw) if n else None, n, m, _p(ms), _p(md), _p(sc), C.byref(nm),
+                                        _p(us), C.byref(nus), _p(ud), C.byref(nud)))
+        self._matches = [AssociatedIndex(int(ms[k]), int(md[k]), float(sc[k])) for k in range(nm.value)]
+        self.unassociatedSrc = us[:nus.value].copy()
+        self._unassoc_dst = ud[:nud.value].copy()
+
+    def getMatches(self):
+        return self._matches
+
+    def totalDestination(self):
+        return 0 if self._dst[0] is None else len(self._dst[0])
+
+    def getUnassociatedSrc(self):
+        return self.unassociatedSrc
+
+    def getAssoc(self):
+        return self.assoc
+
+    def getPairs(self):
+        return self._pairs
+
+    def getFitQuality(self):
+        return self._fit
+
+    # device-resident variant: torch tensors desc [n,dof] float64 + white [n] uint8 on both sides
+    def associateDevice(self, src, src_white, dst, dst_white, stream=None):
+        import torch
+        n, dof = src.shape; m = dst.shape[0]
+        pairs = torch.empty(n, dtype=torch.int32, device=src.device); fit = torch.empty(n, dtype=torch.float64, device=src.device)
+        st = (stream if stream is not None else torch.cuda.current_stream(src.device).cuda_stream) or 1
+        N.check(N.lib().bs_assoc_surf_run_device(self.assoc._h, C.c_void_p(src.data_ptr()), C.c_void_p(src_white.data_ptr()), n,
+                                                 C.c_void_p(dst.data_ptr()), C.c_void_p(dst_white.data_ptr()), m, dof,
+                                                 C.c_void_p(pairs.data_ptr()), C.c_void_p(fit.data_ptr()), C.c_void_p(st)))
+        return pairs, fit
+
+
+class WrapAssociateSurfBasic:
+    """AssociateDescription<BrightFeature> around AssociateSurfBasic
+    (F/abst/feature/associate/WrapAssociateSurfBasic.java:35-90)."""
+    def __init__(self, alg):
+        self.alg = alg
+
+    def setSource(self, listSrc):
+        self.alg.setSrc(listSrc)
+
+    def setDestination(self, listDst):
+        self.alg.setDst(listDst)
+
+    def associate(self):
+        self.alg.associate()
+
+    def getMatches(self):
+        return self.alg.getMatches()
+
+    def getUnassociatedSource(self):
+        return self.alg.getUnassociatedSrc()
+
+    def getUnassociatedDestination(self):
+        return self.alg._unassoc_dst
+
+    def setMaxScoreThreshold(self, score):
+        self.alg.getAssoc().setMaxScoreThreshold(score)
+
+    def getScoreType(self):
+        return self.alg.getAssoc().getScoreType()
+
+    def uniqueSource(self):
+        return self.alg.getAssoc().uniqueSource()
+
+    def uniqueDestination(self):
+        return self.alg.getAssoc().uniqueDestination()
+
+
 class FactoryAssociation:
     @staticmethod
     def greedy(score, maxError, backwardsValidation, device=0):

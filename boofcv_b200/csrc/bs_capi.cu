@@ -821,6 +821,36 @@ struct bs_assoc {
 	// tensor-core filter workspace: split operands, norms, candidate lists
 	DevBuf op_src, op_dst, norm_src, norm_dst, tc_scalars /* maxnorm src, maxnorm dst, overflow */, cand_count, cand;
 	long tc_runs = 0, tc_fallbacks = 0;
+	// AssociateSurfBasic workspace: class index lists, class matrices, class results, staged Laplacian signs
+	DevBuf sb_idx_src, sb_idx_dst, sb_counts, sb_src, sb_dst, sb_pairs, sb_fit, sb_white_src, sb_white_dst;
+
+	// AssociateSurfBasic.associate (F/alg/feature/associate/AssociateSurfBasic.java:83-122) on device arrays: pairs[n] = index
+	// into dst (global) or -1, fit[n].  Synchronises `st` (the class sizes decide the launches).
+	void run_surf_basic(const double* src, const uint8_t* white_src, int n, const double* dst, const uint8_t* white_dst, int m, int dof,
+	                    int32_t* pairs, double* fit, cudaStream_t st) {
+		if (n < 0 || m < 0 || dof < 1) fail(BS_ERR_ARG, "bad sizes");
+		if (n == 0) return;
+		sb_idx_src.reserve((size_t)n * 4); sb_idx_dst.reserve((size_t)std::max(m, 1) * 4); sb_counts.reserve(8);
+		sb_src.reserve((size_t)n * dof * 8); sb_dst.reserve((size_t)std::max(m, 1) * dof * 8);
+		sb_pairs.reserve((size_t)n * 4); sb_fit.reserve((size_t)n * 8);
+		int32_t* cnt = sb_counts.as<int32_t>();
+		launch_partition_white(white_src, n, sb_idx_src.as<int32_t>(), cnt + 0, st);
+		launch_partition_white(white_dst, m, sb_idx_dst.as<int32_t>(), cnt + 1, st);
+		launch_gather_rows(src, sb_idx_src.as<int32_t>(), n, dof, sb_src.as<double>(), st);
+		launch_gather_rows(dst, sb_idx_dst.as<int32_t>(), m, dof, sb_dst.as<double>(), st);
+		int32_t h_cnt[2] = {0, 0};
+		BS_CUDA(cudaMemcpyAsync(h_cnt, cnt, 8, cudaMemcpyDeviceToHost, st));
+		BS_CUDA(cudaStreamSynchronize(st));
+		const int ns[2] = {h_cnt[0], n - h_cnt[0]}, ms[2] = {h_cnt[1], m - h_cnt[1]};
+		const int so[2] = {0, h_cnt[0]}, mo[2] = {0, h_cnt[1]};
+		for (int c = 0; c < 2; c++) {            // positive (white) lists first, then negative (:94-121)
+			if (ns[c] == 0) continue;
+			run(sb_src.as<double>() + (size_t)so[c] * dof, ns[c], sb_dst.as<double>() + (size_t)mo[c] * dof, ms[c], dof,
+			    sb_pairs.as<int32_t>() + so[c], sb_fit.as<double>() + so[c], st);
+			launch_scatter_pairs(sb_pairs.as<int32_t>() + so[c], sb_fit.as<double>() + so[c], ns[c], sb_idx_src.as<int32_t>() + so[c],
+			                     sb_idx_dst.as<int32_t>() + mo[c], pairs, fit, st);
+		}
+	}
 
 	RowminScratch scratch(long entries) {
 		p_min.reserve(entries * 8); p_first.reserve(entries * 4); p_last.reserve(entries * 4);
@@ -947,6 +977,8 @@ int bs_assoc_destroy(bs_assoc* a) {
 		a->d_src.release(); a->d_dst.release(); a->d_pairs.release(); a->d_fit.release();
 		a->op_src.release(); a->op_dst.release(); a->norm_src.release(); a->norm_dst.release(); a->tc_scalars.release();
 		a->cand_count.release(); a->cand.release();
+		a->sb_idx_src.release(); a->sb_idx_dst.release(); a->sb_counts.release(); a->sb_src.release(); a->sb_dst.release();
+		a->sb_pairs.release(); a->sb_fit.release(); a->sb_white_src.release(); a->sb_white_dst.release();
 		if (a->stream) cudaStreamDestroy(a->stream);
 		delete a;
 	});
@@ -1016,6 +1048,81 @@ int bs_assoc_run(bs_assoc* a, const double* src, int n, const double* dst, int m
 		BS_CUDA(cudaMemcpyAsync(pairs, a->d_pairs.p, (size_t)n * 4, cudaMemcpyDeviceToHost, a->stream));
 		BS_CUDA(cudaMemcpyAsync(fit, a->d_fit.p, (size_t)n * 8, cudaMemcpyDeviceToHost, a->stream));
 		BS_CUDA(cudaStreamSynchronize(a->stream));
+	});
+}
+
+int bs_assoc_surf_run_device(bs_assoc* a, const double* d_src, const uint8_t* d_src_white, int n, const double* d_dst,
+                             const uint8_t* d_dst_white, int m, int dof, int32_t* d_pairs, double* d_fit, void* stream) {
+	return guarded([&] {
+		if (!a) fail(BS_ERR_ARG, "handle is null");
+		if ((n > 0 && (!d_src || !d_src_white || !d_pairs || !d_fit)) || (m > 0 && (!d_dst || !d_dst_white))) fail(BS_ERR_ARG, "null argument");
+		DeviceGuard g(a->device);
+		a->run_surf_basic(d_src, d_src_white, n, d_dst, d_dst_white, m, dof, d_pairs, d_fit,
+		                  stream ? static_cast<cudaStream_t>(stream) : a->stream);
+	});
+}
+
+int bs_assoc_surf_run(bs_assoc* a, const double* src, const uint8_t* src_white, int n, const double* dst, const uint8_t* dst_white, int m,
+                      int dof, int32_t* pairs, double* fit) {
+	return guarded([&] {
+		if (!a) fail(BS_ERR_ARG, "handle is null");
+		if ((!src || !src_white) && n > 0) fail(BS_ERR_STATE, "source features not specified");
+		if ((!dst || !dst_white) && m > 0) fail(BS_ERR_STATE, "destination features not specified");
+		if (n < 0 || m < 0 || dof < 1) fail(BS_ERR_ARG, "bad sizes");
+		if (n == 0) return;
+		if (!pairs || !fit) fail(BS_ERR_ARG, "null argument");
+		DeviceGuard g(a->device);
+		cudaStream_t st = a->stream;
+		a->d_src.reserve((size_t)n * dof * 8); a->d_dst.reserve((size_t)std::max(m, 1) * dof * 8);
+		a->d_pairs.reserve((size_t)n * 4); a->d_fit.reserve((size_t)n * 8);
+		a->sb_white_src.reserve((size_t)n); a->sb_white_dst.reserve((size_t)std::max(m, 1));
+		BS_CUDA(cudaMemcpyAsync(a->d_src.p, src, (size_t)n * dof * 8, cudaMemcpyHostToDevice, st));
+		BS_CUDA(cudaMemcpyAsync(a->sb_white_src.p, src_white, (size_t)n, cudaMemcpyHostToDevice, st));
+		if (m > 0) {
+			BS_CUDA(cudaMemcpyAsync(a->d_dst.p, dst, (size_t)m * dof * 8, cudaMemcpyHostToDevice, st));
+			BS_CUDA(cudaMemcpyAsync(a->sb_white_dst.p, dst_white, (size_t)m, cudaMemcpyHostToDevice, st));
+		}
+		a->run_surf_basic(a->d_src.as<double>(), a->sb_white_src.as<uint8_t>(), n, a->d_dst.as<double>(), a->sb_white_dst.as<uint8_t>(), m,
+		                  dof, a->d_pairs.as<int32_t>(), a->d_fit.as<double>(), st);
+		BS_CUDA(cudaMemcpyAsync(pairs, a->d_pairs.p, (size_t)n * 4, cudaMemcpyDeviceToHost, st));
+		BS_CUDA(cudaMemcpyAsync(fit, a->d_fit.p, (size_t)n * 8, cudaMemcpyDeviceToHost, st));
+		BS_CUDA(cudaStreamSynchronize(st));
+	});
+}
+
+// AssociateSurfBasic.associate :83-122 — match list and unassociated sources in the reference's order: the white class in
+// ascending source index, then the other class; nothing at all when either list is empty (:89-92)
+int bs_assoc_surf_matches(const int32_t* pairs, const double* fit, const uint8_t* src_white, int n, int m, int32_t* match_src,
+                          int32_t* match_dst, double* match_score, int* n_matches, int32_t* unassoc_src, int* n_unassoc_src,
+                          int32_t* unassoc_dst, int* n_unassoc_dst) {
+	return guarded([&] {
+		if (n < 0 || m < 0 || (n > 0 && (!pairs || !fit || !src_white))) fail(BS_ERR_ARG, "bad arguments");
+		std::vector<char> hit((size_t)std::max(m, 1), 0);
+		int nm = 0, nus = 0, nud = 0;
+		if (n > 0 && m > 0) {
+			for (int cls = 1; cls >= 0; cls--)
+				for (int i = 0; i < n; i++) {
+					if ((src_white[i] != 0) != (cls == 1)) continue;
+					const int d = pairs[i];
+					if (d >= 0) {
+						if (d >= m) fail(BS_ERR_ARG, "pair index out of range");
+						if (match_src) match_src[nm] = i;
+						if (match_dst) match_dst[nm] = d;
+						if (match_score) match_score[nm] = fit[i];
+						nm++; hit[d] = 1;
+					}
+				}
+			// the unassociated sources of a class are listed after that class's matches, class by class (:104-107,118-121)
+			for (int cls = 1; cls >= 0; cls--)
+				for (int i = 0; i < n; i++)
+					if ((src_white[i] != 0) == (cls == 1) && pairs[i] < 0) { if (unassoc_src) unassoc_src[nus] = i; nus++; }
+		}
+		// WrapAssociateSurfBasic.getUnassociatedDestination: FindUnassociated.checkDestination over totalDestination()
+		for (int j = 0; j < m; j++)
+			if (!hit[j]) { if (unassoc_dst) unassoc_dst[nud] = j; nud++; }
+		if (n_matches) *n_matches = nm;
+		if (n_unassoc_src) *n_unassoc_src = nus;
+		if (n_unassoc_dst) *n_unassoc_dst = nud;
 	});
 }
 

@@ -186,6 +186,12 @@ void launch_validate(int n, int row_offset, int32_t* pairs, double* fit, const d
 void launch_merge_columns(int ranks, int m, const double* a_min, const int32_t* a_first, const int32_t* a_last, double* o_min,
                           int32_t* o_first, int32_t* o_last, cudaStream_t st);
 
+// AssociateSurfBasic helpers (bs_assoc_surf.cu)
+void launch_partition_white(const uint8_t* d_white, int n, int32_t* d_idx, int32_t* d_count, cudaStream_t st);
+void launch_gather_rows(const double* d_in, const int32_t* d_idx, int n, int dof, double* d_out, cudaStream_t st);
+void launch_scatter_pairs(const int32_t* d_pairs_c, const double* d_fit_c, int n_c, const int32_t* d_src_idx, const int32_t* d_dst_idx,
+                          int32_t* d_pairs, double* d_fit, cudaStream_t st);
+
 const char* last_error_cstr();
 long launch_count();
 Layer make_layer(int size, int skip, int W, int H);

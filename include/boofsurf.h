@@ -252,6 +252,23 @@ int bs_assoc_matches(const int32_t* pairs, const double* fit, int n, int m, int3
                      double* match_score, int* n_matches, int32_t* unassoc_src, int* n_unassoc_src,
                      int32_t* unassoc_dst, int* n_unassoc_dst);
 
+/* AssociateSurfBasic (F/alg/feature/associate/AssociateSurfBasic.java:83-143) behind WrapAssociateSurfBasic
+ * (F/abst/feature/associate/WrapAssociateSurfBasic.java:35-90), the associator FactoryPointTracker.dda_FH_SURF_Fast/Stable
+ * build around FactoryAssociation.greedy: BrightFeature lists are split by `white` (sign of the Laplacian), each class is
+ * associated with the handle's greedy settings, indices refer to the callers' lists.
+ * src_white[n] / dst_white[m] = BrightFeature.white (0/1).  pairs[n] = index into dst or -1, fit[n] as bs_assoc_run. */
+int bs_assoc_surf_run(bs_assoc* a, const double* src, const uint8_t* src_white, int n, const double* dst,
+                      const uint8_t* dst_white, int m, int dof, int32_t* pairs, double* fit);
+/* Same on device pointers (e.g. straight from bs_surf_view); synchronises `stream` once (class sizes). */
+int bs_assoc_surf_run_device(bs_assoc* a, const double* d_src, const uint8_t* d_src_white, int n, const double* d_dst,
+                             const uint8_t* d_dst_white, int m, int dof, int32_t* d_pairs, double* d_fit, void* stream);
+/* Match list in AssociateSurfBasic's order (white class in ascending source index, then the other class), its
+ * unassociated-source list (same class order; empty when either input list is empty, :89-92) and
+ * FindUnassociated.checkDestination over all m destinations.  Host-side index bookkeeping; outputs sized n,n,n,n,m. */
+int bs_assoc_surf_matches(const int32_t* pairs, const double* fit, const uint8_t* src_white, int n, int m,
+                          int32_t* match_src, int32_t* match_dst, double* match_score, int* n_matches,
+                          int32_t* unassoc_src, int* n_unassoc_src, int32_t* unassoc_dst, int* n_unassoc_dst);
+
 /* kernel launch counter (all kernels this library launched on the calling process since load) — bench.py's
  * gpu_launches */
 long bs_launch_count(void);

@@ -286,3 +286,29 @@ def matches_from_pairs(pairs, fit, n_dst):
     unassoc_src = np.nonzero(pairs < 0)[0].astype(np.int32)
     hit = np.zeros(n_dst, bool); hit[pairs[src_idx]] = True
     return matches, unassoc_src, np.nonzero(~hit)[0].astype(np.int32)
+
+
+def associate_surf_basic(src, src_white, dst, dst_white, max_fit_error=np.finfo(np.float64).max, backwards=False):
+    """AssociateSurfBasic.sort + associate (F/alg/feature/associate/AssociateSurfBasic.java:83-143) around the greedy
+    oracle, WrapAssociateSurfBasic.getUnassociatedDestination (F/abst/feature/associate/WrapAssociateSurfBasic.java:71-73).
+    Returns (matches [(src, dst, score)], unassociated_src, unassociated_dst) in the reference's order."""
+    src = np.ascontiguousarray(src, np.float64); dst = np.ascontiguousarray(dst, np.float64)
+    sw = np.asarray(src_white) != 0; dw = np.asarray(dst_white) != 0
+    matches, unassoc = [], []
+    if len(src) and len(dst):                                   # :89-92
+        for cls in (True, False):                               # positive lists first (:94-107), then negative (:108-121)
+            si = np.nonzero(sw == cls)[0]; di = np.nonzero(dw == cls)[0]
+            # WrapAssociateGreedy.associate accepts empty lists: every source is then unassociated
+            if len(si) == 0:
+                continue
+            if len(di) == 0:
+                unassoc += [int(i) for i in si]
+                continue
+            pairs, fit = associate(src[si], dst[di], max_fit_error, backwards)
+            m, us, _ = matches_from_pairs(pairs, fit, len(di))
+            matches += [(int(si[a]), int(di[b]), f) for a, b, f in m]
+            unassoc += [int(si[i]) for i in us]
+    hit = np.zeros(len(dst), bool)
+    for _, b, _ in matches:
+        hit[b] = True
+    return matches, np.asarray(unassoc, np.int32), np.nonzero(~hit)[0].astype(np.int32)

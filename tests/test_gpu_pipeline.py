@@ -293,3 +293,61 @@ def test_surf_host_batch_equals_single_frames(bs, orc):
     with pytest.raises(Exception):
         det.detectHostBatch(frames, small)
     out.close(); det.close()
+
+
+# ------------------------------------------------------------------ AssociateSurfBasic (split by Laplacian sign)
+def _desc1(vals):
+    d = np.zeros((len(vals), 64)); d[:, 0] = vals
+    return d
+
+
+def _surf_basic(bs, src, sw, dst, dw, max_err, backwards):
+    alg = bs.AssociateSurfBasic(bs.FactoryAssociation.greedy(bs.ScoreAssociateEuclideanSq_F64(), max_err, backwards))
+    w = bs.WrapAssociateSurfBasic(alg)
+    w.setSource((src, np.asarray(sw, np.uint8))); w.setDestination((dst, np.asarray(dw, np.uint8))); w.associate()
+    return w
+
+
+def test_assoc_surf_basic_known_answers(bs):
+    # TestAssociateSurfBasic.java:44-162 (threshold squared: the GPU score is Euclidean^2)
+    w = _surf_basic(bs, _desc1([10]), [1], _desc1([0, 10]), [1, 0], 400.0, True)
+    assert [(m.src, m.dst) for m in w.getMatches()] == [(0, 0)]
+    w = _surf_basic(bs, _desc1([10, 12, 5, 2344, 1000]), [1, 1, 0, 0, 0], _desc1([0, 10.1, 13, 0.1, 7]), [1, 1, 1, 0, 0], 400.0, True)
+    assert [(m.src, m.dst) for m in w.getMatches()] == [(0, 1), (1, 2), (2, 4)] and all(m.fitScore != 0 for m in w.getMatches())
+    assert sorted(w.getUnassociatedSource().tolist()) == [3, 4]
+    w = _surf_basic(bs, _desc1([10, 12, 5]), [1, 1, 0], _desc1([0, 10.1, 13, 0.1, 7]), [1, 1, 1, 0, 0], 400.0, True)
+    assert len(w.getMatches()) == 3 and len(w.getUnassociatedSource()) == 0 and w.getUnassociatedDestination().tolist() == [0, 3]
+    assert w.uniqueSource() and w.uniqueDestination() and w.getScoreType() == bs.MatchScoreType.NORM_ERROR
+
+
+@pytest.mark.parametrize("n,m", [(300, 280), (3000, 2500), (1, 5), (40, 0)])
+@pytest.mark.parametrize("backwards", [False, True])
+def test_assoc_surf_basic_matches_oracle(bs, orc, n, m, backwards):
+    rng = np.random.default_rng(n * 7 + m)
+    src, dst = descriptors(n, seed=11), descriptors(m, seed=12) if m else np.zeros((0, 64))
+    sw, dw = rng.integers(0, 2, n), rng.integers(0, 2, m)
+    w = _surf_basic(bs, src, sw, dst, dw, 1.5, backwards)
+    matches, us, ud = orc.associate_surf_basic(src, sw, dst, dw, 1.5, backwards)
+    assert [(x.src, x.dst, x.fitScore) for x in w.getMatches()] == matches
+    assert np.array_equal(w.getUnassociatedSource(), us) and np.array_equal(w.getUnassociatedDestination(), ud)
+
+
+def test_assoc_surf_basic_one_sided_classes_and_device(bs, orc):
+    import torch
+    src, dst = descriptors(500, seed=21), descriptors(400, seed=22)
+    sw = np.ones(500, np.uint8); dw = np.zeros(400, np.uint8); dw[:7] = 1          # few white destinations, no dark sources
+    w = _surf_basic(bs, src, sw, dst, dw, DMAX, True)
+    matches, us, ud = orc.associate_surf_basic(src, sw, dst, dw, DMAX, True)
+    assert [(x.src, x.dst, x.fitScore) for x in w.getMatches()] == matches and np.array_equal(w.getUnassociatedSource(), us)
+    # device-resident call on real SURF features of a shifted pair: same pairs as the host call
+    a, b = shifted_pair(320, 240)
+    det = bs.FactoryDetectDescribe.surfFast(None, None, None, np.float32)
+    det.detect(a); ra = det.readFrame(0)
+    det.detect(b); rb = det.readFrame(0)
+    alg = bs.AssociateSurfBasic(bs.FactoryAssociation.greedy(bs.ScoreAssociateEuclideanSq_F64(), 0.1, True))
+    alg.setSrc(ra); alg.setDst(rb); alg.associate()
+    matches, us, ud = orc.associate_surf_basic(ra["desc"], ra["white"], rb["desc"], rb["white"], 0.1, True)
+    assert [(x.src, x.dst, x.fitScore) for x in alg.getMatches()] == matches and len(matches) > 10
+    t = lambda x, dt: torch.as_tensor(np.ascontiguousarray(x), dtype=dt, device="cuda")
+    p, f = alg.associateDevice(t(ra["desc"], torch.float64), t(ra["white"], torch.uint8), t(rb["desc"], torch.float64), t(rb["white"], torch.uint8))
+    assert np.array_equal(p.cpu().numpy(), alg.getPairs()) and np.array_equal(f.cpu().numpy(), alg.getFitQuality())
