@@ -5,6 +5,6 @@ libboofsurf.so), the ctypes binding (_native), the stage-level calls (stages) an
 interface layer (surf, associate).  There is no CPU fallback anywhere in this package."""
 from .surf import (FactoryDetectDescribe, ConfigFastHessian, ConfigAverageIntegral, ConfigSlidingIntegral,  # noqa: F401
                    ConfigSurfDescribe, BrightFeature, AssociatedIndex, Point2D_F64, DetectDescribeSurf,
-                   HostFeatureBuffers)
+                   HostFeatureBuffers, ImageType, SurfPlanar_to_DetectDescribePoint)
 from .associate import (FactoryAssociation, ScoreAssociateEuclideanSq_F64, MatchScoreType, AssociateGreedyGPU,  # noqa: F401
                         AssociateSurfBasic, WrapAssociateSurfBasic)

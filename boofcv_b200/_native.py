@@ -56,6 +56,9 @@ SIGNATURES = {
     "bs_surf_destroy": (_i, [_vp]),
     "bs_surf_set_workspace": (_i, [_vp, _i, _l]),
     "bs_surf_detect": (_i, [_vp, _vp, _i, _i, _i, _i]),
+    "bs_surf_create_planar": (_i, [_i, C.POINTER(FhCfg), C.POINTER(OriCfg), C.POINTER(DescCfg), _i, _i, C.POINTER(_vp)]),
+    "bs_surf_detect_planar": (_i, [_vp, C.POINTER(_vp), _i, _i, _i, _i, _i]),
+    "bs_surf_detect_planar_device": (_i, [_vp, _vp, _l, _l, _i, _i, _i, _i, _vp]),
     "bs_surf_detect_device": (_i, [_vp, _vp, _l, _i, _i, _i, _i, _vp]),
     "bs_surf_detect_host_batch": (_i, [_vp, _vp, _l, _i, _i, _i, _i, _l, _vp, _vp, _vp, _vp, _vp, _vp, C.POINTER(_l)]),
     "bs_host_register": (_i, [_vp, C.c_size_t]),

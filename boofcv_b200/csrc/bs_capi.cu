@@ -95,6 +95,8 @@ struct DescribeSetup {
 		p.dof = d.width_large_grid * d.width_large_grid * 4;
 		const int region = d.width_large_grid * d.width_sub_region;
 		p.radius_descriptor = region / 2 + p.overlap;
+		p.ori_object_radius_mult = 2.0;              // BoofDefaults.SURF_SCALE_TO_RADIUS (WrapDetectDescribeSurf.java:103)
+		p.out_stride = p.dof; p.out_offset = 0; p.finish = 1;
 		if (region + 2 * p.overlap > 255) fail(BS_ERR_ARG, "descriptor sample grid too large");
 		build_perm(region + 2 * p.overlap);
 		if (d.variant == 0) {
@@ -161,6 +163,8 @@ struct bs_surf {
 	int device = 0;
 	bs_fh_cfg fh{}; bs_ori_cfg ori{}; bs_desc_cfg desc{};
 	int pixel_type = BS_PIXEL_F32;
+	int bands = 0;                // 0: grey SURF; >= 1: colour SURF over a Planar image of that many bands
+	int out_dof() const { return ds.p.dof * std::max(bands, 1); }
 	cudaStream_t stream = nullptr;
 	cudaEvent_t done = nullptr;
 	// Optional (BS_OVERLAP=1): orientation+descriptor on a second stream, one chunk behind detection.  Measured +1.5 %
@@ -175,6 +179,7 @@ struct bs_surf {
 	int W = 0, H = 0, chunk = 0;
 	Plan plan{};
 	DevBuf d_plan, d_in, d_ii, d_inten, d_stage, d_counts, d_offsets, d_frame_offset, d_keys, d_keep;
+	DevBuf d_gray, d_ii_bands;    // colour SURF: band average (pixel type) and the band integrals [band][group][H][W]
 	PoolBufs pool;
 	void* h_pinned = nullptr; size_t h_pinned_bytes = 0;
 	// last result
@@ -217,8 +222,11 @@ struct bs_surf {
 	int group = 0;
 	template <typename TI, typename TII>
 	void run_typed(const void* d_pixels, long frame_stride, int stride, int nbatch, cudaStream_t st);
+	template <typename TI, typename TII>
+	void run_planar_typed(const void* d_pixels, long frame_stride, long band_stride, int stride, int nbatch, cudaStream_t st);
 	void ensure(int w, int h, int nbatch);
 	void run(const void* d_pixels, long frame_stride, int stride, int w, int h, int nbatch, cudaStream_t st);
+	void run_planar(const void* d_pixels, long frame_stride, long band_stride, int stride, int w, int h, int nbatch, cudaStream_t st);
 	void finish();
 };
 
@@ -254,7 +262,11 @@ void bs_surf::ensure(int w, int h, int nbatch) {
 	}
 	d_frame_offset.reserve((size_t)(nbatch + 1) * sizeof(int));
 	long cap = pool_req > 0 ? pool_req : (long)nbatch * std::max<long>((long)px / 64, 256);
-	pool.reserve(cap, ds.p.dof);
+	pool.reserve(cap, out_dof());
+	if (bands > 0) {
+		d_gray.reserve(px * elem_size(pixel_type) * group);
+		d_ii_bands.reserve(px * 4 * group * bands);
+	}
 }
 
 // the whole pipeline for a device-resident batch, all on `st`.  Two granularities:
@@ -306,7 +318,72 @@ void bs_surf::run_typed(const void* d_pixels, long frame_stride, int stride, int
 	}
 }
 
+// Colour SURF for a device-resident batch of Planar frames (band b of frame f at d_pixels + f*frame_stride + b*band_stride):
+// SurfPlanar_to_DetectDescribePoint.detect (F/abst/feature/detdesc/SurfPlanar_to_DetectDescribePoint.java:58-74: band average,
+// grey integral, one integral per band) -> DetectDescribeSurfPlanar.detect/describe (F/alg/feature/detdesc/
+// DetectDescribeSurfPlanar.java:87-116: detection and orientation on the grey integral, object radius = scale) ->
+// DescribePointSurfPlanar.describe (F/alg/feature/describe/DescribePointSurfPlanar.java:97-111: raw sums per band,
+// one L2 normalisation over all bands, Laplacian sign from the grey integral).
+template <typename TI, typename TII>
+void bs_surf::run_planar_typed(const void* d_pixels, long frame_stride, long band_stride, int stride, int nbatch, cudaStream_t st) {
+	int* fo = d_frame_offset.as<int>();
+	const long px = (long)W * H;
+	const int dof = ds.p.dof, total = dof * bands;
+	for (int g0 = 0; g0 < nbatch; g0 += group) {
+		const int g = std::min(group, nbatch - g0);
+		TII* ii = d_ii.as<TII>();
+		TII* bii = d_ii_bands.as<TII>();
+		const TI* in = static_cast<const TI*>(d_pixels) + (long)g0 * frame_stride;
+		stage_begin(0, st);
+		launch_average_bands<TI>(in, frame_stride, band_stride, stride, bands, d_gray.as<TI>(), W, H, g, st);
+		launch_integral<TI, TII>(d_gray.as<TI>(), px, W, ii, W, H, g, st);
+		for (int b = 0; b < bands; b++) launch_integral<TI, TII>(in + b * band_stride, frame_stride, stride, bii + (long)b * group * px, W, H, g, st);
+		stage_end(st);
+		for (int f0 = g0; f0 < g0 + g; f0 += chunk) {
+			const int c = std::min(chunk, g0 + g - f0);
+			const TII* cii = ii + (long)(f0 - g0) * px;
+			stage_begin(1, st);
+			launch_hessian_plan<TII>(cii, plan, d_plan.as<Plan>(), d_inten.as<float>(), c, st);
+			stage_end(st);
+			stage_begin(2, st);
+			launch_nms(plan, d_plan.as<Plan>(), d_inten.as<float>(), c, d_stage.as<RawPoint>(), d_counts.as<int>(), d_keys.as<unsigned>(),
+			           d_keep.as<unsigned char>(), st);
+			stage_end(st);
+			stage_begin(3, st);
+			launch_compact(plan, c, f0, d_stage.as<RawPoint>(), d_counts.as<int>(), d_offsets.as<int>(), fo, pool.view, st);
+			stage_end(st);
+			stage_begin(4, st);
+			DescribeParams po = ds.p;
+			po.ori_object_radius_mult = 1.0;
+			launch_describe<TII>(cii, W, H, po, ds.tables, pool.view, fo + f0, fo + f0 + c, f0, true, false, st);
+			for (int b = 0; b < bands; b++) {
+				DescribeParams pb = ds.p;
+				pb.out_stride = total; pb.out_offset = b * dof; pb.finish = 0;
+				launch_describe<TII>(bii + (long)b * group * px + (long)(f0 - g0) * px, W, H, pb, ds.tables, pool.view, fo + f0, fo + f0 + c, f0,
+				                     false, true, st);
+			}
+			launch_planar_finish<TII>(cii, W, H, total, pool.view, fo + f0, fo + f0 + c, f0, st);
+			stage_end(st);
+		}
+	}
+}
+
+void bs_surf::run_planar(const void* d_pixels, long frame_stride, long band_stride, int stride, int w, int h, int nbatch, cudaStream_t st) {
+	if (bands <= 0) fail(BS_ERR_STATE, "this handle was created for single-band images (bs_surf_create)");
+	if (nbatch <= 0) fail(BS_ERR_ARG, "batch must be >= 1");
+	if (stride < w) fail(BS_ERR_ARG, "stride must be >= width");
+	ensure(w, h, nbatch);
+	batch = nbatch;
+	BS_CUDA(cudaMemsetAsync(d_frame_offset.p, 0, sizeof(int), st));
+	if (pixel_type == BS_PIXEL_F32) run_planar_typed<float, float>(d_pixels, frame_stride, band_stride, stride, nbatch, st);
+	else if (pixel_type == BS_PIXEL_U8) run_planar_typed<uint8_t, int32_t>(d_pixels, frame_stride, band_stride, stride, nbatch, st);
+	else run_planar_typed<int32_t, int32_t>(d_pixels, frame_stride, band_stride, stride, nbatch, st);
+	BS_CUDA(cudaEventRecord(done, st));
+	pending = true;
+}
+
 void bs_surf::run(const void* d_pixels, long frame_stride, int stride, int w, int h, int nbatch, cudaStream_t st) {
+	if (bands > 0) fail(BS_ERR_STATE, "this handle was created for Planar images (bs_surf_detect_planar)");
 	if (nbatch <= 0) fail(BS_ERR_ARG, "batch must be >= 1");
 	if (stride < w) fail(BS_ERR_ARG, "stride must be >= width");
 	ensure(w, h, nbatch);
@@ -385,6 +462,52 @@ int bs_surf_create(int device, const bs_fh_cfg* fh, const bs_ori_cfg* ori, const
 	});
 }
 
+int bs_surf_create_planar(int device, const bs_fh_cfg* fh, const bs_ori_cfg* ori, const bs_desc_cfg* desc, int pixel_type, int num_bands,
+                          bs_surf** out) {
+	if (num_bands < 1 || num_bands > 16) {
+		set_last_error("number of bands must be in [1,16]");
+		if (out) *out = nullptr;
+		return BS_ERR_ARG;
+	}
+	const int rc = bs_surf_create(device, fh, ori, desc, pixel_type, out);
+	if (rc == BS_OK) (*out)->bands = num_bands;
+	return rc;
+}
+
+int bs_surf_detect_planar_device(bs_surf* s, const void* d_pixels, long frame_stride, long band_stride, int stride, int width, int height,
+                                 int batch, void* stream) {
+	return guarded([&] {
+		if (!s || !d_pixels) fail(BS_ERR_ARG, "null argument");
+		DeviceGuard g(s->device);
+		s->run_planar(d_pixels, frame_stride, band_stride, stride, width, height, batch, stream ? static_cast<cudaStream_t>(stream) : s->stream);
+	});
+}
+
+int bs_surf_detect_planar(bs_surf* s, const void* const* bands, int num_bands, int start_index, int stride, int width, int height) {
+	return guarded([&] {
+		if (!s || !bands) fail(BS_ERR_ARG, "null argument");
+		if (s->bands <= 0) fail(BS_ERR_STATE, "this handle was created for single-band images (bs_surf_create)");
+		// SurfPlanar_to_DetectDescribePoint.detect :59-61
+		if (num_bands != s->bands)
+			fail(BS_ERR_ARG, "Unexpected number of bands. Expected " + std::to_string(s->bands) + " found " + std::to_string(num_bands));
+		if (width <= 0 || height <= 0) fail(BS_ERR_ARG, "image width and height must be positive");
+		if (stride < width || start_index < 0) fail(BS_ERR_ARG, "bad stride/startIndex");
+		DeviceGuard g(s->device);
+		const size_t es = elem_size(s->pixel_type);
+		const size_t dense = (size_t)width * height * es;
+		s->d_in.reserve(dense * num_bands);
+		for (int b = 0; b < num_bands; b++) {
+			if (!bands[b]) fail(BS_ERR_ARG, "null band");
+			const char* src = static_cast<const char*>(bands[b]) + (size_t)start_index * es;
+			BS_CUDA(cudaMemcpy2DAsync(static_cast<char*>(s->d_in.p) + dense * b, (size_t)width * es, src, (size_t)stride * es, (size_t)width * es,
+			                          height, cudaMemcpyHostToDevice, s->stream));
+		}
+		const long px = (long)width * height;
+		s->run_planar(s->d_in.p, px * num_bands, px, width, width, height, 1, s->stream);
+		s->finish();
+	});
+}
+
 int bs_surf_destroy(bs_surf* s) {
 	if (!s) return BS_OK;
 	for (int k = 0; k < bs_surf::MAX_LANES; k++) {
@@ -397,6 +520,7 @@ int bs_surf_destroy(bs_surf* s) {
 		s->ds.release(); s->pool.release();
 		s->d_plan.release(); s->d_in.release(); s->d_ii.release(); s->d_inten.release(); s->d_stage.release();
 		s->d_counts.release(); s->d_offsets.release(); s->d_frame_offset.release(); s->d_keys.release(); s->d_keep.release();
+		s->d_gray.release(); s->d_ii_bands.release();
 		if (s->h_pinned) cudaFreeHost(s->h_pinned);
 		if (s->done) cudaEventDestroy(s->done);
 		if (s->ev_chunk) cudaEventDestroy(s->ev_chunk);
@@ -418,7 +542,7 @@ int bs_surf_set_workspace(bs_surf* s, int chunk_frames, long pool_features) {
 	});
 }
 
-int bs_surf_dof(const bs_surf* s) { return s ? s->ds.p.dof : 0; }
+int bs_surf_dof(const bs_surf* s) { return s ? s->out_dof() : 0; }
 
 int bs_surf_set_timing(bs_surf* s, int on) {
 	return guarded([&] {
@@ -481,7 +605,7 @@ int bs_surf_detect_host_batch(bs_surf* s, const void* pixels, long frame_stride,
 				s->lane[k] = h;
 			}
 		const size_t es = elem_size(s->pixel_type);
-		const int dof = s->ds.p.dof;
+		const int dof = s->out_dof();
 		const int sub = 32;                        // frames per lane turn = one integral group
 		frame_offset[0] = 0;
 		long base = 0;                             // features of the frames drained so far
@@ -591,7 +715,7 @@ int bs_surf_read(bs_surf* s, int frame, double* xy, double* scale, double* angle
 		const size_t n = (size_t)(e - b);
 		if (n == 0) return;
 		const Pool& p = s->pool.view;
-		const int dof = s->ds.p.dof;
+		const int dof = s->out_dof();
 		if (xy) BS_CUDA(cudaMemcpy(xy, p.xy + 2 * b, n * 16, cudaMemcpyDeviceToHost));
 		if (scale) BS_CUDA(cudaMemcpy(scale, p.scale + b, n * 8, cudaMemcpyDeviceToHost));
 		if (angle) BS_CUDA(cudaMemcpy(angle, p.angle + b, n * 8, cudaMemcpyDeviceToHost));
@@ -610,7 +734,7 @@ int bs_surf_view(bs_surf* s, bs_surf_device_view* v) {
 		const Pool& p = s->pool.view;
 		v->d_xy = p.xy; v->d_scale = p.scale; v->d_angle = p.angle; v->d_desc = p.desc; v->d_white = p.white;
 		v->d_frame_offset = s->d_frame_offset.as<int32_t>();
-		v->total = s->h_frame_offset[s->batch]; v->batch = s->batch; v->dof = s->ds.p.dof;
+		v->total = s->h_frame_offset[s->batch]; v->batch = s->batch; v->dof = s->out_dof();
 		if (v->total > p.cap) fail(BS_ERR_CAPACITY, "feature pool too small for this batch");
 	});
 }

@@ -113,6 +113,12 @@ struct DescribeParams {
 	// descriptor
 	int variant, grid, sub, sample_width, overlap, dof;
 	int radius_descriptor;
+	// WrapDetectDescribeSurf sets the orientation's object radius to scale*SURF_SCALE_TO_RADIUS (2.0),
+	// DetectDescribeSurfPlanar (F/alg/feature/detdesc/DetectDescribeSurfPlanar.java:108) to the scale itself (1.0)
+	double ori_object_radius_mult;
+	// where a feature's `dof` values go: pool.desc + f*out_stride + out_offset.  finish = 1: L2-normalise them and compute
+	// the Laplacian sign (grey SURF); 0: raw sums of one band (colour SURF, finished by launch_planar_finish)
+	int out_stride, out_offset, finish;
 };
 
 // ---------------------------------------------------------------- stage launchers (implemented in the .cu files)
@@ -162,6 +168,16 @@ constexpr int DESC_PERM_BINS = 32;
 template <typename T>
 void launch_describe(const T* d_ii, int W, int H, const DescribeParams& p, const DescribeTables& t, const Pool& pool,
                      const int* d_begin, const int* d_end, int frame0, bool do_orientation, bool do_describe, cudaStream_t st);
+
+// Colour SURF (DescribePointSurfPlanar.describe :97-111): L2-normalise the `total_dof` concatenated band sums of every pool
+// entry in [*d_begin, *d_end) and set its Laplacian sign from the grey integral image.
+template <typename T>
+void launch_planar_finish(const T* d_gray_ii, int W, int H, int total_dof, const Pool& pool, const int* d_begin, const int* d_end,
+                          int frame0, cudaStream_t st);
+// ConvertImage.average(Planar, gray): gray[f][y][x] = (sum over bands, left to right) / bands, in the pixel type's arithmetic
+template <typename T>
+void launch_average_bands(const T* d_in, long frame_stride, long band_stride, int stride, int bands, T* d_gray, int W, int H, int batch,
+                          cudaStream_t st);
 
 // ---------------------------------------------------------------- exact association (bs_assoc_exact.cu)
 struct RowminScratch { double* p_min; int* p_first; int* p_last; long cap; };

@@ -56,7 +56,7 @@ __device__ __forceinline__ OriGeo ori_geometry(const DescribeParams& P, double c
 	OriGeo g;
 	g.sw = 2 * P.ori_radius + 1;
 	// setObjectRadius(scale*BoofDefaults.SURF_SCALE_TO_RADIUS): scale = radius*objectRadiusToScale; kernel width = scale*sampleWidth
-	const double sc = (ptScale * 2.0) * P.ori_radius_to_scale;
+	const double sc = (ptScale * P.ori_object_radius_mult) * P.ori_radius_to_scale;
 	g.r = gradient_radius(sc * P.ori_sample_width);
 	g.period = sc * P.ori_period;
 	g.tl_x = c_x - P.ori_radius * g.period;
@@ -254,6 +254,11 @@ __device__ void describe_reduce(const T* __restrict__ ii, int W, int H, const De
 	for (int k = 0; k < P.dof; k++) { const double t = feat[k]; norm += t * t; }
 	const bool scale_it = norm != 0.0;
 	norm = sqrt(norm);
+	if (!P.finish) {                       // one band of a colour descriptor: the raw sums, finished by planar_finish_kernel
+		for (int k = lane; k < P.dof; k += 32) out_desc[k] = feat[k];
+		__syncwarp();
+		return;
+	}
 	for (int k = lane; k < P.dof; k += 32) out_desc[k] = scale_it ? feat[k] / norm : feat[k];
 	if (lane == 0) *out_white = laplace_sign(ii, W, H, (int)(x + 0.5), (int)(y + 0.5), scale) ? 1 : 0;
 	__syncwarp();
@@ -402,7 +407,7 @@ describe_kernel(const T* __restrict__ ii_all, int W, int H, DescribeParams P, De
 				double* feat = reinterpret_cast<double*>(mine);
 				const T* gx = reinterpret_cast<const T*>(feat + P.dof);
 				describe_reduce(ii_all + me.frame * frame_words, W, H, P, t_w, t_wgrid, me.x, me.y, me.c, me.s, me.scale, gx, gx + S.desc_g2, feat,
-				                pool.desc + me.f * P.dof, pool.white + me.f);
+				                pool.desc + me.f * P.out_stride + P.out_offset, pool.white + me.f);
 			}
 		}
 	}
@@ -428,6 +433,76 @@ void launch_describe(const T* d_ii, int W, int H, const DescribeParams& p, const
 	BS_LAUNCH((describe_kernel<T>), sm_count * ctas_per_sm, DESC_WARPS * 32, S.total, st, d_ii, W, H, p, t, S, pool, d_begin, d_end, frame0,
 	          do_orientation ? 1 : 0, do_describe ? 1 : 0);
 }
+// DescribePointSurfPlanar.describe :106-110: UtilFeature.normalizeL2 over all bands, Laplacian sign from the grey integral.
+// One warp per feature (persistent, the range is only known on the device); every lane repeats the serial sum of
+// squares (broadcast loads) so the order is the reference's.
+template <typename T>
+__global__ void __launch_bounds__(256) planar_finish_kernel(const T* __restrict__ gray_ii, int W, int H, int total_dof, Pool pool,
+                                                            const int* __restrict__ d_begin, const int* __restrict__ d_end, int frame0) {
+	const int lane = threadIdx.x & 31;
+	long end = *d_end;
+	if (end > pool.cap) end = pool.cap;
+	const long warps = (long)gridDim.x * (blockDim.x >> 5);
+	for (long f = *d_begin + (long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); f < end; f += warps) {
+		double* d = pool.desc + f * total_dof;
+		double norm = 0.0;
+		for (int k = 0; k < total_dof; k++) { const double t = d[k]; norm += t * t; }
+		__syncwarp();
+		if (norm != 0.0) {
+			norm = sqrt(norm);
+			for (int k = lane; k < total_dof; k += 32) d[k] = d[k] / norm;
+		}
+		if (lane == 0) {
+			const T* ii = gray_ii + (long)(pool.frame[f] - frame0) * W * H;
+			pool.white[f] = laplace_sign(ii, W, H, (int)(pool.xy[2 * f] + 0.5), (int)(pool.xy[2 * f + 1] + 0.5), pool.scale[f]) ? 1 : 0;
+		}
+	}
+}
+
+template <typename T>
+void launch_planar_finish(const T* d_gray_ii, int W, int H, int total_dof, const Pool& pool, const int* d_begin, const int* d_end,
+                          int frame0, cudaStream_t st) {
+	int dev = 0, sm_count = 0;
+	BS_CUDA(cudaGetDevice(&dev));
+	BS_CUDA(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev));
+	BS_LAUNCH((planar_finish_kernel<T>), sm_count * 8, 256, 0, st, d_gray_ii, W, H, total_dof, pool, d_begin, d_end, frame0);
+}
+template void launch_planar_finish<float>(const float*, int, int, int, const Pool&, const int*, const int*, int, cudaStream_t);
+template void launch_planar_finish<int32_t>(const int32_t*, int, int, int, const Pool&, const int*, const int*, int, cudaStream_t);
+
+// ConvertImage.average (core/image/impl/ImplConvertPlanarToGray.java:44-84 U8, :213-253 S32, :296-336 F32): bands summed left to
+// right in the pixel type's arithmetic (float adds, wrapping int adds), then divided by the band count
+template <typename T> struct AvgAcc;
+template <> struct AvgAcc<float> { static __device__ __forceinline__ float run(const float* p, long bs, int nb) {
+	if (nb == 1) return p[0];
+	float sum = nb == 3 ? p[0] : 0.0f;
+	for (int b = nb == 3 ? 1 : 0; b < nb; b++) sum += p[b * bs];
+	return sum / nb; } };
+template <> struct AvgAcc<uint8_t> { static __device__ __forceinline__ uint8_t run(const uint8_t* p, long bs, int nb) {
+	int sum = 0;
+	for (int b = 0; b < nb; b++) sum += p[b * bs];
+	return (uint8_t)(sum / nb); } };
+template <> struct AvgAcc<int32_t> { static __device__ __forceinline__ int32_t run(const int32_t* p, long bs, int nb) {
+	uint32_t sum = 0;
+	for (int b = 0; b < nb; b++) sum += (uint32_t)p[b * bs];
+	return (int32_t)sum / nb; } };
+template <typename T>
+__global__ void average_bands_kernel(const T* __restrict__ in, long frame_stride, long band_stride, int stride, int bands, T* __restrict__ gray,
+                                     int W, int H) {
+	const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y, f = blockIdx.z;
+	if (x >= W) return;
+	gray[((long)f * H + y) * W + x] = AvgAcc<T>::run(in + f * frame_stride + (long)y * stride + x, band_stride, bands);
+}
+template <typename T>
+void launch_average_bands(const T* d_in, long frame_stride, long band_stride, int stride, int bands, T* d_gray, int W, int H, int batch,
+                          cudaStream_t st) {
+	BS_LAUNCH((average_bands_kernel<T>), dim3(div_up(W, 256), H, batch), 256, 0, st, d_in, frame_stride, band_stride, stride, bands, d_gray,
+	          W, H);
+}
+template void launch_average_bands<float>(const float*, long, long, int, int, float*, int, int, int, cudaStream_t);
+template void launch_average_bands<uint8_t>(const uint8_t*, long, long, int, int, uint8_t*, int, int, int, cudaStream_t);
+template void launch_average_bands<int32_t>(const int32_t*, long, long, int, int, int32_t*, int, int, int, cudaStream_t);
+
 template void launch_describe<float>(const float*, int, int, const DescribeParams&, const DescribeTables&, const Pool&, const int*, const int*,
                                      int, bool, bool, cudaStream_t);
 template void launch_describe<int32_t>(const int32_t*, int, int, const DescribeParams&, const DescribeTables&, const Pool&, const int*,

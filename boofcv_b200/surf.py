@@ -144,11 +144,16 @@ class HostFeatureBuffers:
 class DetectDescribeSurf:
     """WrapDetectDescribeSurf over a bs_surf handle.  Not thread safe, like the reference (recycled storage)."""
 
-    def __init__(self, fh, ori, desc, imageType, device=0):
+    def __init__(self, fh, ori, desc, imageType, device=0, numBands=0):
         self._pixel = S.pixel_type(imageType)
         self._dtype = np.dtype(imageType)
         self._h = C.c_void_p()
-        N.check(N.lib().bs_surf_create(device, C.byref(fh), C.byref(ori), C.byref(desc), self._pixel, C.byref(self._h)))
+        self._bands = int(numBands)
+        if self._bands > 0:
+            N.check(N.lib().bs_surf_create_planar(device, C.byref(fh), C.byref(ori), C.byref(desc), self._pixel, self._bands,
+                                                  C.byref(self._h)))
+        else:
+            N.check(N.lib().bs_surf_create(device, C.byref(fh), C.byref(ori), C.byref(desc), self._pixel, C.byref(self._h)))
         self._dof = N.lib().bs_surf_dof(self._h)
         self.device = device
         self._res = None          # results of frame 0 of the last detect (host copies)
@@ -294,7 +299,101 @@ class DetectDescribeSurf:
         return True
 
 
+class ImageType:
+    """boofcv.struct.image.ImageType, as far as the SURF factories look at it: family, band type, band count."""
+    GRAY, PLANAR, INTERLEAVED = "GRAY", "PLANAR", "INTERLEAVED"
+
+    def __init__(self, family, dataType, numBands):
+        self.family = family; self.dataType = dataType; self.numBands = int(numBands)
+
+    @staticmethod
+    def pl(numBands, dataType):
+        return ImageType(ImageType.PLANAR, dataType, numBands)
+
+    @staticmethod
+    def single(dataType):
+        return ImageType(ImageType.GRAY, dataType, 1)
+
+    def getFamily(self):
+        return self.family
+
+    def getNumBands(self):
+        return self.numBands
+
+    def getImageClass(self):
+        return self.dataType
+
+
+class SurfPlanar_to_DetectDescribePoint(DetectDescribeSurf):
+    """DetectDescribePoint<Planar<T>,BrightFeature> for colour images (F/abst/feature/detdesc/
+    SurfPlanar_to_DetectDescribePoint.java:40-118 around DetectDescribeSurfPlanar / DescribePointSurfPlanar): detection and
+    orientation on the band average, descriptor = per-band SURF sums concatenated and normalised once (64*numBands values).
+    Input: array [numBands, height, width] (Planar.bands)."""
+
+    def detect(self, input):
+        a = np.asarray(input)
+        if a.ndim != 3:
+            raise ValueError("expected a Planar image [numBands, height, width]")
+        if a.shape[0] != self._bands:
+            raise ValueError("Unexpected number of bands. Expected %d found %d" % (self._bands, a.shape[0]))
+        if a.dtype != self._dtype:
+            raise ValueError("Unknown input type: expected %s" % self._dtype)
+        planes = [S._strided(a[b]) for b in range(self._bands)]
+        stride = planes[0][1]
+        if any(p[1] != stride for p in planes):
+            planes = [(np.ascontiguousarray(p[0]), p[0].shape[1]) for p in planes]
+            stride = planes[0][1]
+        h, w = planes[0][0].shape
+        ptrs = (C.c_void_p * self._bands)(*[p[0].ctypes.data for p in planes])
+        N.check(N.lib().bs_surf_detect_planar(self._h, ptrs, self._bands, 0, stride, w, h))
+        self._batch = 1
+        self._res = self.readFrame(0)
+
+    def detectBatch(self, frames, stream=None):
+        """Device-resident batch: torch tensor [B, numBands, H, W] on this handle's device."""
+        import torch
+        if frames.dim() != 4 or frames.stride(3) != 1 or frames.shape[1] != self._bands:
+            raise ValueError("frames must be [batch, numBands, height, width] with unit column stride")
+        if {torch.float32: N.PIXEL_F32, torch.uint8: N.PIXEL_U8, torch.int32: N.PIXEL_S32}.get(frames.dtype) != self._pixel:
+            raise ValueError("Unknown input type")
+        b, _, h, w = frames.shape
+        st = (stream if stream is not None else torch.cuda.current_stream(frames.device).cuda_stream) or 1
+        N.check(N.lib().bs_surf_detect_planar_device(self._h, C.c_void_p(frames.data_ptr()), frames.stride(0), frames.stride(1),
+                                                     frames.stride(2), w, h, b, C.c_void_p(st)))
+        self._batch = b
+        self._res = None
+
+    def detectHostBatch(self, frames, out):
+        raise NotImplementedError("host batches are implemented for single-band frames only")
+
+    def getRadius(self, featureIndex):
+        # DetectDescribeSurfPlanar.getRadius (:131-133) returns the scale itself
+        return float(self._need()["scale"][featureIndex])
+
+
 class FactoryDetectDescribe:
+    @staticmethod
+    def _color(fh, ori, desc, imageType, device):
+        if not isinstance(imageType, ImageType) or imageType.getFamily() != ImageType.PLANAR:
+            raise ValueError("Image type not supported")           # FactoryDetectDescribe.java:176, :266
+        return SurfPlanar_to_DetectDescribePoint(fh, ori, desc, imageType.getImageClass(), device, imageType.getNumBands())
+
+    @staticmethod
+    def surfColorFast(configDetector=None, configDesc=None, configOrientation=None, imageType=None, device=0):
+        """FactoryDetectDescribe.surfColorFast (F/factory/feature/detdesc/FactoryDetectDescribe.java:153-178)."""
+        fh = (configDetector or ConfigFastHessian())._c()
+        desc = (configDesc or ConfigSurfDescribe.Speed())._c()
+        ori = (configOrientation or ConfigAverageIntegral())._c()
+        return FactoryDetectDescribe._color(fh, ori, desc, imageType, device)
+
+    @staticmethod
+    def surfColorStable(configDetector=None, configDescribe=None, configOrientation=None, imageType=None, device=0):
+        """FactoryDetectDescribe.surfColorStable (:247-268)."""
+        fh = (configDetector or ConfigFastHessian())._c()
+        desc = (configDescribe or ConfigSurfDescribe.Stability())._c()
+        ori = (configOrientation or ConfigSlidingIntegral())._c()
+        return FactoryDetectDescribe._color(fh, ori, desc, imageType, device)
+
     @staticmethod
     def surfFast(configDetector=None, configDesc=None, configOrientation=None, imageType=np.float32, device=0):
         fh = (configDetector or ConfigFastHessian())._c()

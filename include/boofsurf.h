@@ -94,6 +94,21 @@ typedef struct bs_surf bs_surf;
 /* Constructor.  Validates the configs the way Configuration.checkValidity does (BS_ERR_ARG). */
 int bs_surf_create(int device, const bs_fh_cfg* fh, const bs_ori_cfg* ori, const bs_desc_cfg* desc, int pixel_type,
                    bs_surf** out);
+/* Colour SURF: FactoryDetectDescribe.surfColorFast / surfColorStable (F/factory/feature/detdesc/FactoryDetectDescribe.java:
+ * 153-178, 247-268) = SurfPlanar_to_DetectDescribePoint (F/abst/feature/detdesc/SurfPlanar_to_DetectDescribePoint.java:40-74)
+ * around DetectDescribeSurfPlanar (F/alg/feature/detdesc/DetectDescribeSurfPlanar.java:87-116) and DescribePointSurfPlanar
+ * (F/alg/feature/describe/DescribePointSurfPlanar.java:97-111).  Features are detected and oriented on the band average;
+ * the descriptor is the concatenation of the per-band sums, normalised once: bs_surf_dof() = 64 * num_bands.
+ * pixel_type is the band type (Planar<GrayF32|GrayU8|GrayS32>). */
+int bs_surf_create_planar(int device, const bs_fh_cfg* fh, const bs_ori_cfg* ori, const bs_desc_cfg* desc, int pixel_type,
+                          int num_bands, bs_surf** out);
+/* DetectDescribePoint<Planar<T>>.detect: bands[b] = Planar.bands[b].data (host), all with the same startIndex/stride.
+ * A band count other than the handle's is an error (IllegalArgumentException in the reference, :59-61). */
+int bs_surf_detect_planar(bs_surf* s, const void* const* bands, int num_bands, int start_index, int stride, int width,
+                          int height);
+/* Device-resident batch: band b of frame f starts at d_pixels + f*frame_stride + b*band_stride (elements). */
+int bs_surf_detect_planar_device(bs_surf* s, const void* d_pixels, long frame_stride, long band_stride, int stride,
+                                 int width, int height, int batch, void* stream);
 int bs_surf_destroy(bs_surf* s);
 
 /* Workspace tuning (optional, before the first detect).  chunk_frames = frames processed per kernel wave (bounds the

@@ -47,6 +47,7 @@ def lib():
                           ("orc_block_unsafe_f32", C.c_float), ("orc_block_zero_f32", C.c_float),
                           ("orc_poly_peak", C.c_float), ("orc_euclidean_sq", C.c_double)):
             getattr(_LIB, name).restype = res
+        _LIB.orc_laplace_sign_f32.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_double]
         _LIB.orc_atan2.argtypes = [C.c_double, C.c_double]
         _LIB.orc_sin.argtypes = [C.c_double]
         _LIB.orc_cos.argtypes = [C.c_double]
@@ -312,3 +313,60 @@ def associate_surf_basic(src, src_white, dst, dst_white, max_fit_error=np.finfo(
     for _, b, _ in matches:
         hit[b] = True
     return matches, np.asarray(unassoc, np.int32), np.nonzero(~hit)[0].astype(np.int32)
+
+
+# ------------------------------------------------------------------ colour SURF (surfColorFast / surfColorStable)
+def planar_average(bands):
+    """ConvertImage.average(Planar, gray) (core/image/impl/ImplConvertPlanarToGray.java:44-84 U8, :296-336 F32)."""
+    b = np.ascontiguousarray(bands)
+    nb, h, w = b.shape
+    out = np.zeros((h, w), b.dtype)
+    f = {np.dtype(np.float32): lib().orc_planar_average_f32, np.dtype(np.uint8): lib().orc_planar_average_u8}[b.dtype]
+    f(_p(b), nb, w, h, _p(out))
+    return out
+
+
+def describe_raw(ii, x, y, angle, scale, cfg=None):
+    """DescribePointSurf.describe(x,y,angle,scale,TupleDesc_F64) :195-213: the sums only, not normalised."""
+    a, st = _img(ii, ii.dtype)
+    assert a.dtype == np.float32
+    xys = _xys(x, y, scale)
+    ang = np.ascontiguousarray(angle, np.float64)
+    dv = _desc(cfg)
+    desc = np.zeros((len(xys), int(dv[1]) ** 2 * 4), np.float64)
+    lib().orc_describe_raw_f32(_p(a), st, a.shape[1], a.shape[0], _p(dv), _p(xys), _p(ang), len(xys), _p(desc))
+    return desc
+
+
+def laplace_sign(ii, x, y, scale, cfg=None):
+    a, st = _img(ii, ii.dtype)
+    return bool(lib().orc_laplace_sign_f32(_p(a), st, a.shape[1], a.shape[0], _p(_desc(cfg)), int(x), int(y), float(scale)))
+
+
+def surf_planar(bands, fh=None, ori=None, desc=None, nthreads=1):
+    """SurfPlanar_to_DetectDescribePoint.detect -> DetectDescribeSurfPlanar.detect -> DescribePointSurfPlanar.describe.
+    bands: [nb][h][w] float32 or uint8.  desc rows hold nb*64 doubles."""
+    b = np.ascontiguousarray(bands)
+    nb, h, w = b.shape
+    iv, thr = _fh(fh)
+    dv = _desc(desc)
+    dof = int(dv[1]) ** 2 * 4 * nb
+    cap = max(1024, w * h // 8)
+    while True:
+        xys = np.zeros((cap, 3), np.float64); angle = np.zeros(cap, np.float64)
+        d = np.zeros((cap, dof), np.float64); white = np.zeros(cap, np.uint8)
+        f = {np.dtype(np.float32): lib().orc_surf_planar_f32, np.dtype(np.uint8): lib().orc_surf_planar_u8}[b.dtype]
+        n = f(_p(b), nb, w, h, _p(iv), thr, _p(_ori(ori)), _p(dv), cap, _p(xys), _p(angle), _p(d), _p(white), nthreads)
+        if n <= cap:
+            break
+        cap = n
+    return dict(x=xys[:n, 0].copy(), y=xys[:n, 1].copy(), scale=xys[:n, 2].copy(), angle=angle[:n].copy(),
+                desc=d[:n].copy(), white=white[:n].astype(bool))
+
+
+def surf_color_fast(bands, fh=None, nthreads=1):
+    return surf_planar(bands, fh, ORI_AVERAGE, DESC_SPEED, nthreads)
+
+
+def surf_color_stable(bands, fh=None, nthreads=1):
+    return surf_planar(bands, fh, ORI_SLIDING, DESC_STABILITY, nthreads)

@@ -54,6 +54,21 @@ template <typename TIn, typename TII> int surf_t(const TIn* px, int stride, int 
 	}
 	return n;
 }
+// colour SURF (surfColorFast / surfColorStable): bands = nb dense w x h planes; desc holds nb*dof doubles per feature
+template <typename TIn, typename TII> static int surf_planar_t(const TIn* bands, int nb, int w, int h, const int* iv, float thr, const double* ov,
+                                                               const double* dv, int max_out, double* xys, double* angle, double* desc,
+                                                               uint8_t* white, int nthreads) {
+	SurfResult r;
+	surf_planar_detect_describe<TIn, TII>(bands, nb, w, h, fh_from(iv, thr), oc_from(ov), dc_from(dv), r, nthreads);
+	int n = (int)r.points.size();
+	int dof = n ? (int)(r.desc.size() / n) : 0;
+	for (int i = 0; i < n && i < max_out; i++) {
+		xys[3 * i] = r.points[i].x; xys[3 * i + 1] = r.points[i].y; xys[3 * i + 2] = r.points[i].scale;
+		angle[i] = r.angle[i]; white[i] = r.white[i];
+		std::memcpy(desc + (size_t)i * dof, r.desc.data() + (size_t)i * dof, sizeof(double) * dof);
+	}
+	return n;
+}
 }  // namespace
 
 extern "C" {
@@ -155,6 +170,25 @@ int orc_surf_f32(const float* px, int stride, int w, int h, const int* iv, float
 int orc_surf_u8(const uint8_t* px, int stride, int w, int h, const int* iv, float thr, const double* ov, const double* dv, int max_out,
                 double* xys, double* angle, double* desc, uint8_t* white, int nthreads) {
 	return surf_t<uint8_t, int32_t>(px, stride, w, h, iv, thr, ov, dv, max_out, xys, angle, desc, white, nthreads);
+}
+
+int orc_surf_planar_f32(const float* bands, int nb, int w, int h, const int* iv, float thr, const double* ov, const double* dv, int max_out,
+                        double* xys, double* angle, double* desc, uint8_t* white, int nthreads) {
+	return surf_planar_t<float, float>(bands, nb, w, h, iv, thr, ov, dv, max_out, xys, angle, desc, white, nthreads);
+}
+int orc_surf_planar_u8(const uint8_t* bands, int nb, int w, int h, const int* iv, float thr, const double* ov, const double* dv, int max_out,
+                       double* xys, double* angle, double* desc, uint8_t* white, int nthreads) {
+	return surf_planar_t<uint8_t, int32_t>(bands, nb, w, h, iv, thr, ov, dv, max_out, xys, angle, desc, white, nthreads);
+}
+void orc_planar_average_f32(const float* bands, int nb, int w, int h, float* gray) { planar_average<float>(bands, nb, w, h, gray); }
+void orc_planar_average_u8(const uint8_t* bands, int nb, int w, int h, uint8_t* gray) { planar_average<uint8_t>(bands, nb, w, h, gray); }
+void orc_describe_raw_f32(const float* ii, int stride, int w, int h, const double* dv, const double* xys, const double* angle, int n, double* desc) {
+	Describe<float> d(dc_from(dv)); d.set_image(Img<float>{ii, stride, w, h});
+	for (int i = 0; i < n; i++) d.describe_raw(xys[3 * i], xys[3 * i + 1], angle[i], xys[3 * i + 2], desc + (size_t)i * d.dof);
+}
+int orc_laplace_sign_f32(const float* ii, int stride, int w, int h, const double* dv, int x, int y, double scale) {
+	Describe<float> d(dc_from(dv)); d.set_image(Img<float>{ii, stride, w, h});
+	return d.laplace_sign(x, y, scale) ? 1 : 0;
 }
 
 double orc_euclidean_sq(const double* a, const double* b, int n) { return euclidean_sq(a, b, n); }

@@ -640,13 +640,16 @@ template <typename T> Describe<T>::Describe(const DescribeConfig& c) : cfg(c) {
 }
 
 // DescribePointSurf.describe :169-213
-template <typename T> void Describe<T>::describe(double x, double y, double angle, double scale, double* desc, bool* white) {
+template <typename T> void Describe<T>::describe_raw(double x, double y, double angle, double scale, double* desc) {
 	double c = fd_cos(angle), s = fd_sin(angle);
 	bool isInBounds = is_inside_rotated(ii.width, ii.height, x, y, radius_descriptor, cfg.width_sample, scale, c, s);
 	g.ii = ii;
 	g.set_width(cfg.width_sample * scale);
 	if (cfg.variant == 0) features_fast(x, y, c, s, scale, !isInBounds, desc);
 	else features_mod(x, y, c, s, scale, !isInBounds, desc);
+}
+template <typename T> void Describe<T>::describe(double x, double y, double angle, double scale, double* desc, bool* white) {
+	describe_raw(x, y, angle, scale, desc);
 	normalize_l2(desc, dof);
 	if (white) *white = laplace_sign((int)(x + 0.5), (int)(y + 0.5), scale);
 }
@@ -775,6 +778,77 @@ void surf_detect_describe(Img<TIn> input, const FastHessianConfig& fh, const Ori
 template void surf_detect_describe<float, float>(Img<float>, const FastHessianConfig&, const OrientationConfig&, const DescribeConfig&, SurfResult&, int);
 template void surf_detect_describe<uint8_t, int32_t>(Img<uint8_t>, const FastHessianConfig&, const OrientationConfig&, const DescribeConfig&, SurfResult&, int);
 template void surf_detect_describe<int32_t, int32_t>(Img<int32_t>, const FastHessianConfig&, const OrientationConfig&, const DescribeConfig&, SurfResult&, int);
+
+// ===================================================================== colour SURF
+// ImplConvertPlanarToGray.average: the 3-band and the general loop give the same values (sum left to right, then divide)
+template <> void planar_average<float>(const float* bands, int nb, int w, int h, float* gray) {
+	const size_t px = (size_t)w * h;
+	for (size_t i = 0; i < px; i++) {
+		if (nb == 1) { gray[i] = bands[i]; continue; }
+		float sum = nb == 3 ? bands[i] : 0.0f;
+		for (int b = nb == 3 ? 1 : 0; b < nb; b++) sum += bands[b * px + i];
+		gray[i] = sum / nb;
+	}
+}
+template <> void planar_average<uint8_t>(const uint8_t* bands, int nb, int w, int h, uint8_t* gray) {
+	const size_t px = (size_t)w * h;
+	for (size_t i = 0; i < px; i++) {
+		int sum = 0;
+		for (int b = 0; b < nb; b++) sum += bands[b * px + i] & 0xFF;
+		gray[i] = (uint8_t)(sum / nb);
+	}
+}
+template <> void planar_average<int32_t>(const int32_t* bands, int nb, int w, int h, int32_t* gray) {
+	const size_t px = (size_t)w * h;
+	for (size_t i = 0; i < px; i++) {
+		uint32_t sum = 0;                              // Java int adds wrap
+		for (int b = 0; b < nb; b++) sum += (uint32_t)bands[b * px + i];
+		gray[i] = (int32_t)sum / nb;
+	}
+}
+
+template <typename TIn, typename TII>
+void surf_planar_detect_describe(const TIn* bands, int nb, int w, int h, const FastHessianConfig& fh, const OrientationConfig& oc,
+                                 const DescribeConfig& dc, SurfResult& out, int nthreads) {
+	const size_t px = (size_t)w * h;
+	// SurfPlanar_to_DetectDescribePoint.detect :58-74
+	std::vector<TIn> gray(px);
+	planar_average<TIn>(bands, nb, w, h, gray.data());
+	std::vector<TII> gbuf(px), bbuf(px * nb);
+	do_integral<TIn, TII>(Img<TIn>{gray.data(), w, w, h}, ImgMut<TII>{gbuf.data(), w, w, h});
+	for (int b = 0; b < nb; b++) do_integral<TIn, TII>(Img<TIn>{bands + b * px, w, w, h}, ImgMut<TII>{bbuf.data() + b * px, w, w, h});
+	Img<TII> grayII{gbuf.data(), w, w, h};
+	// DetectDescribeSurfPlanar.detect / describe :87-116
+	fast_hessian_detect(grayII, fh, out.points, nthreads);
+	const int n = (int)out.points.size();
+	Describe<TII> proto(dc);
+	const int dof = proto.dof, total = dof * nb;
+	out.angle.assign(n, 0.0); out.desc.assign((size_t)n * total, 0.0); out.white.assign(n, 0);
+	const int nt = std::max(1, std::min(nthreads, n));
+	auto work = [&](int t) {
+		Orientation<TII> ori(oc); Describe<TII> des(dc);
+		ori.set_image(grayII);
+		int b0 = (int)((long)n * t / nt), b1 = (int)((long)n * (t + 1) / nt);
+		for (int i = b0; i < b1; i++) {
+			const ScalePoint& p = out.points[i];
+			ori.set_object_radius(p.scale);          // :108 — the scale itself, not scale*SURF_SCALE_TO_RADIUS as in WrapDetectDescribeSurf
+			double angle = ori.compute(p.x, p.y);
+			double* d = &out.desc[(size_t)i * total];
+			// DescribePointSurfPlanar.describe :97-111
+			for (int b = 0; b < nb; b++) {
+				des.set_image(Img<TII>{bbuf.data() + b * px, w, w, h});
+				des.describe_raw(p.x, p.y, angle, p.scale, d + b * dof);
+			}
+			normalize_l2(d, total);
+			des.set_image(grayII);
+			out.white[i] = des.laplace_sign((int)(p.x + 0.5), (int)(p.y + 0.5), p.scale) ? 1 : 0;
+			out.angle[i] = angle;
+		}
+	};
+	parallel_for(0, nt, nt, work);
+}
+template void surf_planar_detect_describe<float, float>(const float*, int, int, int, const FastHessianConfig&, const OrientationConfig&, const DescribeConfig&, SurfResult&, int);
+template void surf_planar_detect_describe<uint8_t, int32_t>(const uint8_t*, int, int, int, const FastHessianConfig&, const OrientationConfig&, const DescribeConfig&, SurfResult&, int);
 
 // ===================================================================== association
 // DescriptorDistance.euclideanSq :55-64

@@ -127,6 +127,8 @@ template <typename T> struct Describe {
 	explicit Describe(const DescribeConfig& c);
 	void set_image(Img<T> im) { ii = im; g.ii = im; }
 	void describe(double x, double y, double angle, double scale, double* desc, bool* white);
+	// DescribePointSurf.describe(x,y,angle,scale,TupleDesc_F64) :195-213 — neither normalised nor signed
+	void describe_raw(double x, double y, double angle, double scale, double* desc);
 	void features_fast(double c_x, double c_y, double c, double s, double scale, bool safe, double* f);
 	void features_mod(double c_x, double c_y, double c, double s, double scale, bool safe, double* f);
 	bool laplace_sign(int x, int y, double scale);
@@ -140,6 +142,15 @@ struct SurfResult {
 template <typename TIn, typename TII>
 void surf_detect_describe(Img<TIn> input, const FastHessianConfig& fh, const OrientationConfig& oc, const DescribeConfig& dc,
                           SurfResult& out, int nthreads = 1);
+
+// ---- colour SURF: core/image/impl/ImplConvertPlanarToGray.java:44-84,213-253,296-336 (average),
+//      F/abst/feature/detdesc/SurfPlanar_to_DetectDescribePoint.java:58-74, F/alg/feature/detdesc/DetectDescribeSurfPlanar.java:87-116,
+//      F/alg/feature/describe/DescribePointSurfPlanar.java:97-111 ----
+// bands: nb dense w x h images back to back.  desc: nb*dof doubles per feature.
+template <typename TIn> void planar_average(const TIn* bands, int nb, int w, int h, TIn* gray);
+template <typename TIn, typename TII>
+void surf_planar_detect_describe(const TIn* bands, int nb, int w, int h, const FastHessianConfig& fh, const OrientationConfig& oc,
+                                 const DescribeConfig& dc, SurfResult& out, int nthreads = 1);
 
 // ---- F/alg/descriptor/DescriptorDistance.java:55-64, F/alg/feature/associate/AssociateGreedy.java:65-118 ----
 double euclidean_sq(const double* a, const double* b, int n);

@@ -351,3 +351,46 @@ def test_assoc_surf_basic_one_sided_classes_and_device(bs, orc):
     t = lambda x, dt: torch.as_tensor(np.ascontiguousarray(x), dtype=dt, device="cuda")
     p, f = alg.associateDevice(t(ra["desc"], torch.float64), t(ra["white"], torch.uint8), t(rb["desc"], torch.float64), t(rb["white"], torch.uint8))
     assert np.array_equal(p.cpu().numpy(), alg.getPairs()) and np.array_equal(f.cpu().numpy(), alg.getFitQuality())
+
+
+# ------------------------------------------------------------------ colour SURF (surfColorFast / surfColorStable)
+def _planar(w, h, nb=3, seed=234):
+    return np.stack([blob_image(w, h, seed + 17 * b) for b in range(nb)])
+
+
+@pytest.mark.parametrize("which", ["fast", "stable"])
+@pytest.mark.parametrize("nb,shape", [(3, (320, 240)), (2, (400, 300)), (1, (200, 160))])
+def test_surf_color_matches_oracle_bit_exact(bs, orc, which, nb, shape):
+    bands = _planar(shape[0], shape[1], nb)
+    it = bs.ImageType.pl(nb, np.float32)
+    det = (bs.FactoryDetectDescribe.surfColorFast if which == "fast" else bs.FactoryDetectDescribe.surfColorStable)(None, None, None, it)
+    det.detect(bands)
+    o = (orc.surf_color_fast if which == "fast" else orc.surf_color_stable)(bands)
+    r = det.readFrame(0)
+    assert len(o["x"]) > 30 and r["desc"].shape[1] == 64 * nb
+    _same(r, o)
+    assert det.getRadius(0) == o["scale"][0] and det.createDescription().size() == 64 * nb
+    assert det.getDescription(1).white == bool(o["white"][1])
+
+
+def test_surf_color_u8_and_errors(bs, orc):
+    bands = np.clip(_planar(320, 240, 3, seed=5), 0, 255).astype(np.uint8)
+    det = bs.FactoryDetectDescribe.surfColorFast(None, None, None, bs.ImageType.pl(3, np.uint8))
+    det.detect(bands)
+    _same(det.readFrame(0), orc.surf_color_fast(bands))
+    with pytest.raises(ValueError):
+        det.detect(bands[:2])                                    # SurfPlanar_to_DetectDescribePoint.java:59-61
+    with pytest.raises(ValueError):
+        bs.FactoryDetectDescribe.surfColorFast(None, None, None, bs.ImageType.single(np.float32))   # "Image type not supported"
+    grey = bs.FactoryDetectDescribe.surfFast(None, None, None, np.uint8)
+    grey.detect(bands[0])                                        # the grey handle is unaffected by the colour one
+
+
+def test_surf_color_device_batch(bs, orc):
+    import torch
+    frames = np.stack([_planar(320, 240, 3, seed=s) for s in (1, 2, 3, 4, 5)])
+    det = bs.FactoryDetectDescribe.surfColorFast(None, None, None, bs.ImageType.pl(3, np.float32))
+    det.setWorkspace(2, 0)                                       # several chunks and a partial one
+    det.detectBatch(torch.as_tensor(frames, device="cuda"))
+    for f in range(len(frames)):
+        _same(det.readFrame(f), orc.surf_color_fast(frames[f]))
