@@ -132,6 +132,18 @@ class AssociateGreedyGPU:
     def uniqueDestination(self):
         return self._backwards
 
+    def associateFrames(self, det, frameSrc, frameDst, surfBasic=False, stream=None):
+        """detect -> associate without leaving the GPU (bs_assoc_frames_device): features of two frames of `det`'s last
+        batch.  Returns (pairs int32[n], fit float64[n]) CUDA tensors."""
+        import torch
+        n = det.countFrame(frameSrc)
+        dev = torch.device("cuda", self.device)
+        pairs = torch.empty(n, dtype=torch.int32, device=dev); fit = torch.empty(n, dtype=torch.float64, device=dev)
+        st = (stream if stream is not None else torch.cuda.current_stream(dev).cuda_stream) or 1
+        N.check(N.lib().bs_assoc_frames_device(self._h, det._h, int(frameSrc), int(frameDst), int(bool(surfBasic)),
+                                               C.c_void_p(pairs.data_ptr()), C.c_void_p(fit.data_ptr()), C.c_void_p(st)))
+        return pairs, fit
+
     # device-resident variant (torch float64 tensors [n,dof], [m,dof]); returns (pairs int32[n], fit float64[n]) tensors
     def associateDevice(self, src, dst, stream=None):
         import torch

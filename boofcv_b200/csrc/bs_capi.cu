@@ -1250,6 +1250,30 @@ int bs_assoc_surf_matches(const int32_t* pairs, const double* fit, const uint8_t
 	});
 }
 
+// detect -> associate without leaving the GPU: the features of two frames of the detector's last batch are the source and
+// destination lists (what DetectDescribeAssociate / ExampleAssociatePoints do through host lists in the reference)
+int bs_assoc_frames_device(bs_assoc* a, bs_surf* s, int frame_src, int frame_dst, int surf_basic, int32_t* d_pairs, double* d_fit,
+                           void* stream) {
+	return guarded([&] {
+		if (!a || !s) fail(BS_ERR_ARG, "handle is null");
+		if (a->device != s->device) fail(BS_ERR_ARG, "detector and associator live on different devices");
+		DeviceGuard g(a->device);
+		check_ready(s);
+		if (frame_src < 0 || frame_src >= s->batch || frame_dst < 0 || frame_dst >= s->batch) fail(BS_ERR_ARG, "frame out of range");
+		const std::vector<int>& fo = s->h_frame_offset;
+		if (fo[s->batch] > s->pool.view.cap) fail(BS_ERR_CAPACITY, "feature pool too small for this batch");
+		const int n = fo[frame_src + 1] - fo[frame_src], m = fo[frame_dst + 1] - fo[frame_dst];
+		if (n > 0 && (!d_pairs || !d_fit)) fail(BS_ERR_ARG, "null argument");
+		const Pool& p = s->pool.view;
+		const int dof = s->out_dof();
+		cudaStream_t st = stream ? static_cast<cudaStream_t>(stream) : a->stream;
+		const double* src = p.desc + (long)fo[frame_src] * dof;
+		const double* dst = p.desc + (long)fo[frame_dst] * dof;
+		if (surf_basic) a->run_surf_basic(src, p.white + fo[frame_src], n, dst, p.white + fo[frame_dst], m, dof, d_pairs, d_fit, st);
+		else a->run(src, n, dst, m, dof, d_pairs, d_fit, st);
+	});
+}
+
 int bs_assoc_forward_device(bs_assoc* a, const double* d_src, int n, int row_offset, const double* d_dst, int m, int dof,
                             int32_t* d_pairs, double* d_fit, double* d_col_min, int32_t* d_col_first, int32_t* d_col_last,
                             void* stream) {

@@ -244,6 +244,14 @@ int bs_assoc_run(bs_assoc* a, const double* src, int n, const double* dst, int m
 int bs_assoc_run_device(bs_assoc* a, const double* d_src, int n, const double* d_dst, int m, int dof,
                         int32_t* d_pairs, double* d_fit, void* stream);
 
+/* detect -> associate on the device: source = the features of frame_src, destination = those of frame_dst of the last
+ * batch `s` detected (same device as `a`), i.e. the frame-to-frame use of the pair of interfaces by the reference's callers
+ * (ExampleAssociatePoints.java:125-160, DetectDescribeAssociate): no descriptor leaves the GPU.  surf_basic != 0 splits by
+ * the Laplacian sign first (AssociateSurfBasic).  d_pairs / d_fit hold bs_surf_count(s, frame_src) entries; the call is
+ * ordered after the detect on the host (it waits for the batch) and runs on `stream`. */
+int bs_assoc_frames_device(bs_assoc* a, bs_surf* s, int frame_src, int frame_dst, int surf_basic, int32_t* d_pairs,
+                           double* d_fit, void* stream);
+
 /* Sharded association: the src rows of one rank against ALL dst rows.
  * Step 1 (bs_assoc_forward_device): forward pass for the local rows + per-column partial minima over the local rows:
  *   d_col_min[m] (score), d_col_first[m], d_col_last[m] (GLOBAL row index = row_offset + local row; -1 if none).

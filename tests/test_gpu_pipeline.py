@@ -394,3 +394,27 @@ def test_surf_color_device_batch(bs, orc):
     det.detectBatch(torch.as_tensor(frames, device="cuda"))
     for f in range(len(frames)):
         _same(det.readFrame(f), orc.surf_color_fast(frames[f]))
+
+
+# ------------------------------------------------------------------ detect -> associate on the device (stereo / frame-to-frame)
+@pytest.mark.parametrize("surf_basic", [False, True])
+def test_associate_frames_on_device(bs, orc, surf_basic):
+    import torch
+    a0, b0 = shifted_pair(320, 240)
+    a1, b1 = shifted_pair(320, 240, seed=77)
+    frames = torch.as_tensor(np.stack([a0, b0, a1, b1]), device="cuda")
+    det = bs.FactoryDetectDescribe.surfFast(None, None, None, np.float32)
+    det.detectBatch(frames)
+    assoc = bs.FactoryAssociation.greedy(bs.ScoreAssociateEuclideanSq_F64(), 0.1, True)
+    for fa, fb, ia, ib in ((0, 1, a0, b0), (2, 3, a1, b1), (3, 0, b1, a0)):
+        p, f = assoc.associateFrames(det, fa, fb, surfBasic=surf_basic)
+        oa, ob = orc.surf_fast(ia), orc.surf_fast(ib)
+        if surf_basic:
+            matches, _, _ = orc.associate_surf_basic(oa["desc"], oa["white"], ob["desc"], ob["white"], 0.1, True)
+            got = {(i, int(d)): float(s) for i, (d, s) in enumerate(zip(p.cpu().numpy(), f.cpu().numpy())) if d >= 0}
+            assert got == {(s, d): sc for s, d, sc in matches} and (fa == 3 or len(matches) > 10)
+        else:
+            pairs, fit = orc.associate(oa["desc"], ob["desc"], 0.1, True)
+            assert np.array_equal(p.cpu().numpy(), pairs) and np.array_equal(f.cpu().numpy(), fit)
+            if fa < 3:
+                assert (pairs >= 0).sum() > 10
