@@ -272,9 +272,22 @@ __global__ void rescore_kernel(const double* __restrict__ A, int nA, const doubl
 		const int j = cand[(size_t)row * TC_CAND_CAP + c];
 		const double* b = B + (size_t)j * TC_DOF;
 		double s = 0.0;
-		for (int k = 0; k < TC_DOF; k++) {           // DescriptorDistance.euclideanSq :55-64, same order, no FMA
-			const double d = a[k] - b[k];
-			s += d * d;
+		// DescriptorDistance.euclideanSq :55-64, same order, no FMA.  The candidate's row is fetched 16 values at a time
+		// (eight 16-byte loads in flight per lane) ahead of the serial sum; the a row is a broadcast load
+		const double2* b2 = reinterpret_cast<const double2*>(b);
+		const double2* a2 = reinterpret_cast<const double2*>(a);
+#pragma unroll 1
+		for (int k0 = 0; k0 < TC_DOF / 2; k0 += 8) {
+			double2 bv[8], av[8];
+#pragma unroll
+			for (int u = 0; u < 8; u++) { bv[u] = __ldg(b2 + k0 + u); av[u] = __ldg(a2 + k0 + u); }
+#pragma unroll
+			for (int u = 0; u < 8; u++) {
+				const double d0 = av[u].x - bv[u].x;
+				s += d0 * d0;
+				const double d1 = av[u].y - bv[u].y;
+				s += d1 * d1;
+			}
 		}
 		if (first < 0 || s < best) { best = s; first = j; last = j; }
 		else if (s == best) { first = min(first, j); last = max(last, j); }
@@ -358,7 +371,8 @@ void launch_tc_filter(const void* d_opA, const float* d_normA, int nA, const voi
 	P.b_tiles = tc_pad_rows(nB) / TC_BN;
 	// column chunks only when there are fewer 256-row items than SMs: a row's running minimum (and with it the number of
 	// candidates it emits, ~ln(columns/32)) is per item; at least 8 B tiles per item to amortise loading A
-	int chunks = div_up(sm_count, P.a_tiles256);
+	// — and as many chunks as keep all items in ONE wave of CTAs (a second, mostly empty wave costs a whole item time)
+	int chunks = sm_count / std::max(P.a_tiles256, 1);
 	chunks = std::max(1, std::min(chunks, P.b_tiles / 8 > 0 ? P.b_tiles / 8 : 1));
 	P.tiles_per_chunk = div_up(P.b_tiles, chunks);
 	P.chunks = div_up(P.b_tiles, P.tiles_per_chunk);

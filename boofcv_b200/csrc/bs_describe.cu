@@ -18,6 +18,7 @@
 #include "bs_box.cuh"
 #include "bs_math.cuh"
 #include <climits>
+#include <math_constants.h>
 #include <cstdlib>
 
 namespace bs {
@@ -81,64 +82,67 @@ __device__ __forceinline__ void orientation_sample(const T* __restrict__ ii, int
 	if (P.ori_variant == 1) ang[k] = sm_atan2(dy, dx);
 }
 
-// reduction by the feature's own warp, in the reference's order
-__device__ double orientation_reduce(const DescribeParams& P, const double* dX, const double* dY, const double* ang, int* order) {
+// ImplOrientationSlidingWindowIntegral.compute :104 sorts the sample angles ascending (ddogleg QuickSort_F64 index sort; ties
+// are unpinned there — here towards the lower index, like the oracle's stable argsort).  One warp sorts the indices of
+// its feature with a bitonic network over NP = next power of two >= n slots; slots >= n are padding that compares as
+// +infinity.  (angle, index) is a total order, so the network's result is the stable ascending order.
+__device__ __forceinline__ int next_pow2(int n) { int p = 1; while (p < n) p <<= 1; return p; }
+__device__ void warp_argsort(const double* __restrict__ ang, int n, int NP, int* __restrict__ order) {
 	const int lane = threadIdx.x & 31;
-	const int sw = 2 * P.ori_radius + 1, n = sw * sw;
-	double angle = 0.0;
-	if (P.ori_variant == 0) {
-		// computeUnweighted/computeWeighted: Dx += w*dx in sample order; lane 0 sums x, lane 1 sums y
-		double total = 0.0;
-		if (lane < 2) {
-			const double* src = lane == 0 ? dX : dY;
-			for (int k = 0; k < n; k++) total += src[k];
-		}
-		const double Dx = __shfl_sync(0xffffffffu, total, 0);
-		const double Dy = __shfl_sync(0xffffffffu, total, 1);
-		angle = sm_atan2(Dy, Dx);
-	} else {
-		// ascending argsort, ties towards the lower index (rank by counting: the key (angle,index) is a total order)
-		for (int i = lane; i < n; i += 32) {
-			const double a = ang[i];
-			int rank = 0;
-			for (int j = 0; j < n; j++) {
-				const double b = ang[j];
-				rank += (b < a || (b == a && j < i)) ? 1 : 0;
-			}
-			order[rank] = i;
-		}
-		__syncwarp();
-		if (lane == 0) {
-			// estimateAngle :139-188
-			int start = 0, end = 1;
-			int startIndex = order[start], endIndex = order[end];
-			double sumX = dX[startIndex], sumY = dY[startIndex];
-			double best = sumX * sumX + sumY * sumY, bestX = sumX, bestY = sumY;
-			double endAngle = ang[endIndex];
-			while (start != n) {
-				startIndex = order[start];
-				const double startAngle = ang[startIndex];
-				while (angle_dist(startAngle, endAngle) <= P.ori_window) {
-					sumX += dX[endIndex];
-					sumY += dY[endIndex];
-					const double mag = sumX * sumX + sumY * sumY;
-					if (mag > best) { best = mag; bestX = sumX; bestY = sumY; }
-					end++;
-					if (end >= n) end = 0;
-					endIndex = order[end];
-					endAngle = ang[endIndex];
-					if (endIndex == startIndex) break;
-				}
-				sumX -= dX[startIndex];
-				sumY -= dY[startIndex];
-				start++;
-			}
-			angle = sm_atan2(bestY, bestX);
-		}
-		angle = __shfl_sync(0xffffffffu, angle, 0);
-	}
+	for (int i = lane; i < NP; i += 32) order[i] = i;
 	__syncwarp();
-	return angle;
+	for (int k = 2; k <= NP; k <<= 1)
+		for (int j = k >> 1; j > 0; j >>= 1) {
+			for (int t = lane; t < (NP >> 1); t += 32) {
+				const int i = ((t & ~(j - 1)) << 1) | (t & (j - 1)), p = i | j;
+				const int a = order[i], b = order[p];
+				if (a >= n && b >= n) continue;                        // two paddings: any order will do
+				const double ka = a < n ? ang[a] : CUDART_INF, kb = b < n ? ang[b] : CUDART_INF;
+				const bool gt = ka > kb || (ka == kb && a > b);
+				if (gt == ((i & k) == 0)) { order[i] = b; order[p] = a; }
+			}
+			__syncwarp();
+		}
+}
+
+// out[k] = in[order[k]] by one warp
+__device__ __forceinline__ void warp_gather(double* __restrict__ out, const double* __restrict__ in, const int* __restrict__ order, int n) {
+	for (int k = threadIdx.x & 31; k < n; k += 32) out[k] = in[order[k]];
+	__syncwarp();
+}
+
+// estimateAngle :139-188 — the circular two-pointer sweep over the samples in sorted order (sA, sX, sY = angle, dx, dy of
+// the k-th smallest angle; the reference's startIndex == endIndex test becomes start == end), one lane per feature: the
+// running sums are order-sensitive fp64, so the walk itself is serial; several features walk side by side in one warp.
+__device__ double sliding_window_sweep(const DescribeParams& P, const double* sX, const double* sY, const double* sA, int n) {
+	// The reference's nested loops as one flat loop (a step either grows the window at `end` or drops `start`), so that the
+	// lanes of the warp, each on its own feature, stay converged.  `may_grow` is false right after the inner loop's
+	// "wrapped around to start" break, which sends the reference to the subtraction as well.
+	int start = 0, end = 1;
+	double sumX = sX[0], sumY = sY[0];
+	double best = sumX * sumX + sumY * sumY, bestX = sumX, bestY = sumY;
+	double startAngle = sA[0], endAngle = sA[1];
+	bool may_grow = true;
+	while (true) {
+		if (may_grow && angle_dist(startAngle, endAngle) <= P.ori_window) {
+			sumX += sX[end];
+			sumY += sY[end];
+			const double mag = sumX * sumX + sumY * sumY;
+			if (mag > best) { best = mag; bestX = sumX; bestY = sumY; }
+			end++;
+			if (end >= n) end = 0;
+			endAngle = sA[end];
+			may_grow = end != start;
+		} else {
+			sumX -= sX[start];
+			sumY -= sY[start];
+			start++;
+			if (start == n) break;
+			startAngle = sA[start];
+			may_grow = true;
+		}
+	}
+	return sm_atan2(bestY, bestX);
 }
 
 // ---------------------------------------------------------------- descriptor
@@ -299,7 +303,9 @@ static DescribeSmem describe_smem(const DescribeParams& p) {
 	s.tab_ori = p.ori_weighted ? s.ori_n : 0;
 	s.tab_w = p.variant == 0 ? region * region : (p.sub + 2 * ov) * (p.sub + 2 * ov);
 	s.tab_wgrid = p.variant == 1 ? p.grid * p.grid : 0;
-	const int ori_bytes = s.ori_n * (p.ori_variant == 1 ? 8 * 3 + 4 : 8 * 2);
+	int np2 = 1;
+	while (np2 < s.ori_n) np2 <<= 1;
+	const int ori_bytes = p.ori_variant == 1 ? s.ori_n * 8 * 4 + np2 * 4 : s.ori_n * 8 * 2;   // dX, dY (, ang, spare, sort slots)
 	const int desc_bytes = p.dof * 8 + s.desc_g2 * 4 * 2;
 	s.per_warp = ((ori_bytes > desc_bytes ? ori_bytes : desc_bytes) + 15) & ~15;
 	s.total = (s.tab_ori + s.tab_w + s.tab_wgrid) * 8 + DESC_WARPS * ((int)sizeof(Slot) + s.per_warp);
@@ -377,12 +383,26 @@ describe_kernel(const T* __restrict__ ii_all, int W, int H, DescribeParams P, De
 						pool.angle[slots[j].f] = angle;
 					}
 				}
-			} else if (me.f >= 0) {
-				double* dX = reinterpret_cast<double*>(mine);
-				double* dY = dX + S.ori_n;
-				double* ang = dY + S.ori_n;
-				const double angle = orientation_reduce(P, dX, dY, ang, reinterpret_cast<int*>(ang + S.ori_n));
-				if (lane == 0) { me.angle = angle; pool.angle[me.f] = angle; }
+			} else {
+				// sliding window: every warp sorts the sample angles of its own feature and walks the window over them
+				if (me.f >= 0) {
+					// scratch: dX | dY | ang | spare | order.  After the sort the three arrays are rewritten in sorted order,
+					// ping-pong through the spare: sA = spare, sX = old ang, sY = old dX
+					double* dX = reinterpret_cast<double*>(mine);
+					double* dY = dX + S.ori_n; double* ang = dY + S.ori_n; double* spare = ang + S.ori_n;
+					int* order = reinterpret_cast<int*>(spare + S.ori_n);
+					warp_argsort(ang, S.ori_n, next_pow2(S.ori_n), order);
+					warp_gather(spare, ang, order, S.ori_n);
+					warp_gather(ang, dX, order, S.ori_n);
+					warp_gather(dX, dY, order, S.ori_n);
+					// measured: walking the windows of all slots side by side in warp 0 (4x fewer issue slots) leaves the other
+					// warps at the barrier for the whole walk and is slower (767 vs 679 us per 1080p frame); each warp walks its own
+					if (lane == 0) {
+						const double angle = sliding_window_sweep(P, ang, dX, spare, S.ori_n);
+						me.angle = angle;
+						pool.angle[me.f] = angle;
+					}
+				}
 			}
 			__syncthreads();                   // angles are in the slots
 		}
