@@ -79,30 +79,57 @@ __device__ __forceinline__ void orientation_sample(const T* __restrict__ ii, int
 	double dx = (double)gdx, dy = (double)gdy;
 	if (P.ori_weighted) { const double w = wts[k]; dx = w * dx; dy = w * dy; }
 	dX[k] = dx; dY[k] = dy;
+#ifdef BS_EXP_NOATAN
+	if (P.ori_variant == 1) ang[k] = dy + dx;
+#else
 	if (P.ori_variant == 1) ang[k] = sm_atan2(dy, dx);
+#endif
 }
 
 // ImplOrientationSlidingWindowIntegral.compute :104 sorts the sample angles ascending (ddogleg QuickSort_F64 index sort; ties
-// are unpinned there — here towards the lower index, like the oracle's stable argsort).  One warp sorts the indices of
-// its feature with a bitonic network over NP = next power of two >= n slots; slots >= n are padding that compares as
-// +infinity.  (angle, index) is a total order, so the network's result is the stable ascending order.
-__device__ __forceinline__ int next_pow2(int n) { int p = 1; while (p < n) p <<= 1; return p; }
-__device__ void warp_argsort(const double* __restrict__ ang, int n, int NP, int* __restrict__ order) {
+// are unpinned there — here towards the lower index, like the oracle's stable argsort).
+// Stable ascending argsort of ang[0..n) by one warp: sorted runs of 16 (insertion sort, lane = run), then merge levels where
+// every element finds its place in the sibling run by binary search.  (angle, index) is a total order, so "rank among the
+// smaller ones" is well defined and equal to the stable order.  ordA receives the result; ordB is scratch.
+__device__ __forceinline__ bool key_less(const double* ang, int a, int b) {
+	const double ka = ang[a], kb = ang[b];
+	return ka < kb || (ka == kb && a < b);
+}
+__device__ void warp_merge_argsort(const double* __restrict__ ang, int n, int* ordA, int* ordB) {
 	const int lane = threadIdx.x & 31;
-	for (int i = lane; i < NP; i += 32) order[i] = i;
-	__syncwarp();
-	for (int k = 2; k <= NP; k <<= 1)
-		for (int j = k >> 1; j > 0; j >>= 1) {
-			for (int t = lane; t < (NP >> 1); t += 32) {
-				const int i = ((t & ~(j - 1)) << 1) | (t & (j - 1)), p = i | j;
-				const int a = order[i], b = order[p];
-				if (a >= n && b >= n) continue;                        // two paddings: any order will do
-				const double ka = a < n ? ang[a] : CUDART_INF, kb = b < n ? ang[b] : CUDART_INF;
-				const bool gt = ka > kb || (ka == kb && a > b);
-				if (gt == ((i & k) == 0)) { order[i] = b; order[p] = a; }
-			}
-			__syncwarp();
+	for (int r0 = lane * 16; r0 < n; r0 += 32 * 16) {                // runs of 16
+		const int r1 = min(r0 + 16, n);
+		for (int i = r0; i < r1; i++) {
+			int j = i;
+			while (j > r0 && key_less(ang, i, ordA[j - 1])) { ordA[j] = ordA[j - 1]; j--; }
+			ordA[j] = i;
 		}
+	}
+	__syncwarp();
+	for (int len = 16; len < n; len <<= 1) {
+		for (int e = lane; e < n; e += 32) {
+			const int run0 = e & ~(len - 1);                          // start of my run
+			const bool right = (run0 & len) != 0;
+			const int pair0 = run0 & ~len;
+			const int s0 = min(right ? pair0 : pair0 + len, n), s1 = min(s0 + len, n);   // sibling run
+			const int me = ordA[e];
+			int lo = s0, hi = s1;                                     // number of sibling elements smaller than me
+			while (lo < hi) {
+				const int mid = (lo + hi) >> 1;
+				if (key_less(ang, ordA[mid], me)) lo = mid + 1; else hi = mid;
+			}
+			ordB[pair0 + (e - run0) + (lo - s0)] = me;
+		}
+		__syncwarp();
+		int* t = ordA; ordA = ordB; ordB = t;
+	}
+	// an odd number of levels leaves the result in the caller's ordB: copy it home
+	int levels = 0;
+	for (int len = 16; len < n; len <<= 1) levels++;
+	if (levels & 1) {
+		for (int e = lane; e < n; e += 32) ordB[e] = ordA[e];         // (ordA/ordB were swapped: ordB is the caller's ordA)
+		__syncwarp();
+	}
 }
 
 // out[k] = in[order[k]] by one warp
@@ -303,9 +330,7 @@ static DescribeSmem describe_smem(const DescribeParams& p) {
 	s.tab_ori = p.ori_weighted ? s.ori_n : 0;
 	s.tab_w = p.variant == 0 ? region * region : (p.sub + 2 * ov) * (p.sub + 2 * ov);
 	s.tab_wgrid = p.variant == 1 ? p.grid * p.grid : 0;
-	int np2 = 1;
-	while (np2 < s.ori_n) np2 <<= 1;
-	const int ori_bytes = p.ori_variant == 1 ? s.ori_n * 8 * 4 + np2 * 4 : s.ori_n * 8 * 2;   // dX, dY (, ang, spare, sort slots)
+	const int ori_bytes = p.ori_variant == 1 ? s.ori_n * (8 * 4 + 4 * 2) : s.ori_n * 8 * 2;   // dX, dY (, ang, spare, two index arrays)
 	const int desc_bytes = p.dof * 8 + s.desc_g2 * 4 * 2;
 	s.per_warp = ((ori_bytes > desc_bytes ? ori_bytes : desc_bytes) + 15) & ~15;
 	s.total = (s.tab_ori + s.tab_w + s.tab_wgrid) * 8 + DESC_WARPS * ((int)sizeof(Slot) + s.per_warp);
@@ -391,14 +416,23 @@ describe_kernel(const T* __restrict__ ii_all, int W, int H, DescribeParams P, De
 					double* dX = reinterpret_cast<double*>(mine);
 					double* dY = dX + S.ori_n; double* ang = dY + S.ori_n; double* spare = ang + S.ori_n;
 					int* order = reinterpret_cast<int*>(spare + S.ori_n);
-					warp_argsort(ang, S.ori_n, next_pow2(S.ori_n), order);
+#ifdef BS_EXP_NOSORT
+					for (int k = lane; k < S.ori_n; k += 32) order[k] = k;
+					__syncwarp();
+#else
+					warp_merge_argsort(ang, S.ori_n, order, order + S.ori_n);
+#endif
 					warp_gather(spare, ang, order, S.ori_n);
 					warp_gather(ang, dX, order, S.ori_n);
 					warp_gather(dX, dY, order, S.ori_n);
 					// measured: walking the windows of all slots side by side in warp 0 (4x fewer issue slots) leaves the other
 					// warps at the barrier for the whole walk and is slower (767 vs 679 us per 1080p frame); each warp walks its own
 					if (lane == 0) {
+#ifdef BS_EXP_NOSWEEP
+						const double angle = sm_atan2(dX[0], ang[0]);
+#else
 						const double angle = sliding_window_sweep(P, ang, dX, spare, S.ori_n);
+#endif
 						me.angle = angle;
 						pool.angle[me.f] = angle;
 					}
