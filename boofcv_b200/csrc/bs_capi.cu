@@ -62,7 +62,7 @@ struct DescribeSetup {
 	DescribeParams p{};
 	std::vector<double> ori_w, w, wgrid;
 	std::vector<uint16_t> perm;
-	DevBuf d_ori_w, d_w, d_wgrid, d_perm;
+	DevBuf d_ori_w, d_w, d_wgrid, d_perm, d_walk;
 	DescribeTables tables{};
 
 	// visiting order of the G x G sample grid per orientation bin (see DescribeTables::d_perm)
@@ -135,8 +135,19 @@ struct DescribeSetup {
 		d_perm.reserve(perm.size() * sizeof(uint16_t));
 		h2d_sync(d_perm.p, perm.data(), perm.size() * sizeof(uint16_t));
 		tables.d_perm = d_perm.as<uint16_t>();
+		tables.d_walk = nullptr; tables.walk_cap = 0;
 	}
-	void release() { d_ori_w.release(); d_w.release(); d_wgrid.release(); d_perm.release(); }
+	// scratch of the sliding-window walks (DescribeTables::d_walk) for up to `features` features per launch, at most 6 GB
+	void reserve_walk(long features) {
+		if (p.ori_variant != 1) return;
+		const size_t per = ori_w.size() * 32;
+		const long cap = std::max<long>(1, std::min<long>(features, (long)((6UL << 30) / per)));
+		if (cap > tables.walk_cap) {
+			d_walk.reserve((size_t)cap * per);
+			tables.d_walk = d_walk.as<double>(); tables.walk_cap = cap;
+		}
+	}
+	void release() { d_ori_w.release(); d_w.release(); d_wgrid.release(); d_perm.release(); d_walk.release(); }
 };
 
 struct PoolBufs {
@@ -263,6 +274,7 @@ void bs_surf::ensure(int w, int h, int nbatch) {
 	d_frame_offset.reserve((size_t)(nbatch + 1) * sizeof(int));
 	long cap = pool_req > 0 ? pool_req : (long)nbatch * std::max<long>((long)px / 64, 256);
 	pool.reserve(cap, out_dof());
+	ds.reserve_walk(std::min<long>(cap, (long)chunk * std::max<long>((long)px / 96, 256)));   // a chunk's features (~3x the synthetic density)
 	if (bands > 0) {
 		d_gray.reserve(px * elem_size(pixel_type) * group);
 		d_ii_bands.reserve(px * 4 * group * bands);

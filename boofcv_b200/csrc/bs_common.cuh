@@ -161,6 +161,12 @@ struct DescribeTables {
 	// bin (angle mod pi): samples sorted into thin bands of equal image row, left to right, so that the 32 lanes of a
 	// warp read a few cache lines instead of one each.  The order only decides which lane fetches which sample.
 	const uint16_t* d_perm;
+	// sliding-window orientation: optional global scratch for the sorted samples of the first walk_cap features of a launch,
+	// [walk_cap][n] records {w*dx, w*dy, angle, -} of 32 bytes.  With it the window walks run one per THREAD in their own
+	// kernel (thousands in flight per SM) instead of one per warp inside describe_kernel; features beyond walk_cap, and
+	// launches without scratch (the stage entry points), walk in describe_kernel.  One scratch per handle, i.e. per stream.
+	double* d_walk;
+	long walk_cap;
 };
 constexpr int DESC_PERM_BINS = 32;
 // Orientation + descriptor for pool entries [*d_begin, *d_end) (device-side range, persistent warps loop over it).

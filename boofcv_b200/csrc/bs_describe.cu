@@ -366,7 +366,9 @@ describe_kernel(const T* __restrict__ ii_all, int W, int H, DescribeParams P, De
 
 	long end = *d_end;
 	if (end > pool.cap) end = pool.cap;
-	for (long base = *d_begin + (long)blockIdx.x * DESC_WARPS; base < end; base += (long)gridDim.x * DESC_WARPS) {
+	const long begin = *d_begin;
+	const bool emit_walk = do_orientation == 2;        // sliding window: leave the walks to sliding_walk_kernel
+	for (long base = begin + (long)blockIdx.x * DESC_WARPS; base < end; base += (long)gridDim.x * DESC_WARPS) {
 		__syncthreads();                       // previous round (and the table fill) done with slots and scratch
 		const int live = (int)(end - base < DESC_WARPS ? end - base : DESC_WARPS);
 		if (lane == 0) {
@@ -411,6 +413,7 @@ describe_kernel(const T* __restrict__ ii_all, int W, int H, DescribeParams P, De
 			} else {
 				// sliding window: every warp sorts the sample angles of its own feature and walks the window over them
 				if (me.f >= 0) {
+					bool continue_walk = true;
 					// scratch: dX | dY | ang | spare | order.  After the sort the three arrays are rewritten in sorted order,
 					// ping-pong through the spare: sA = spare, sX = old ang, sY = old dX
 					double* dX = reinterpret_cast<double*>(mine);
@@ -422,6 +425,18 @@ describe_kernel(const T* __restrict__ ii_all, int W, int H, DescribeParams P, De
 #else
 					warp_merge_argsort(ang, S.ori_n, order, order + S.ori_n);
 #endif
+					const long f_local = me.f - begin;
+					if (emit_walk && f_local < tabs.walk_cap) {
+						// sorted records to the scratch; sliding_walk_kernel walks them, one thread per feature
+						double2* rec = reinterpret_cast<double2*>(tabs.d_walk) + (size_t)f_local * S.ori_n * 2;
+						for (int k = lane; k < S.ori_n; k += 32) {
+							const int o = order[k];
+							rec[2 * k] = make_double2(dX[o], dY[o]);
+							rec[2 * k + 1] = make_double2(ang[o], 0.0);
+						}
+						continue_walk = false;
+					}
+					if (continue_walk) {
 					warp_gather(spare, ang, order, S.ori_n);
 					warp_gather(ang, dX, order, S.ori_n);
 					warp_gather(dX, dY, order, S.ori_n);
@@ -435,6 +450,7 @@ describe_kernel(const T* __restrict__ ii_all, int W, int H, DescribeParams P, De
 #endif
 						me.angle = angle;
 						pool.angle[me.f] = angle;
+					}
 					}
 				}
 			}
@@ -467,6 +483,60 @@ describe_kernel(const T* __restrict__ ii_all, int W, int H, DescribeParams P, De
 	}
 }
 
+// estimateAngle :139-188 for the features whose sorted samples describe_kernel left in the scratch: one THREAD per feature.
+// Same flat walk as sliding_window_sweep over 32-byte records {dx, dy, angle, -}; the record each pointer will need next is
+// loaded one step ahead.  Every step is a dependent chain (and an L2 access), so the kernel lives on the number of walks
+// in flight: 1024 per SM here against 16 when every walk owns a warp.
+__device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+constexpr int WALK_AHEAD = 12;     // records (32 B) the L2 prefetch runs ahead of each pointer
+__global__ void __launch_bounds__(128, 10) sliding_walk_kernel(const double2* __restrict__ rec_all, int n, DescribeParams P, Pool pool,
+                                                           const int* __restrict__ d_begin, const int* __restrict__ d_end, long walk_cap) {
+	long end_f = *d_end;
+	if (end_f > pool.cap) end_f = pool.cap;
+	const long begin_f = *d_begin;
+	long count = end_f - begin_f;
+	if (count > walk_cap) count = walk_cap;
+	for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < count; i += (long)gridDim.x * blockDim.x) {
+		const double2* r = rec_all + (size_t)i * n * 2;
+		int start = 0, end = 1;
+		double2 sxy = __ldg(r), sa = __ldg(r + 1);                       // record at `start`
+		double2 exy = __ldg(r + 2), ea = __ldg(r + 3);                   // record at `end`
+		int ne = 2 < n ? 2 : 0;                                          // index of the record after `end`
+		double2 nexy = __ldg(r + 2 * ne), nea = __ldg(r + 2 * ne + 1);
+		double2 nsxy = exy, nsa = ea;                                    // record after `start` (index 1)
+		double sumX = sxy.x, sumY = sxy.y;
+		double best = sumX * sumX + sumY * sumY, bestX = sumX, bestY = sumY;
+		bool may_grow = true;
+		// the scratch of a chunk is far larger than L2: pull the lines both pointers are about to reach out of DRAM early
+		for (int k = 4; k < WALK_AHEAD && k < n; k += 4) prefetch_l2(r + 2 * k);
+		while (true) {
+			if (may_grow && angle_dist(sa.x, ea.x) <= P.ori_window) {
+				sumX += exy.x;
+				sumY += exy.y;
+				const double mag = sumX * sumX + sumY * sumY;
+				if (mag > best) { best = mag; bestX = sumX; bestY = sumY; }
+				end = ne;
+				exy = nexy; ea = nea;
+				ne = end + 1 < n ? end + 1 : 0;
+				nexy = __ldg(r + 2 * ne); nea = __ldg(r + 2 * ne + 1);
+				if ((end & 3) == 0) { const int pf = end + WALK_AHEAD; prefetch_l2(r + 2 * (pf < n ? pf : pf - n)); }   // one 128-byte line = 4 records
+				may_grow = end != start;
+			} else {
+				sumX -= sxy.x;
+				sumY -= sxy.y;
+				start++;
+				if (start == n) break;
+				sxy = nsxy; sa = nsa;
+				const int ns = start + 1 < n ? start + 1 : start;
+				nsxy = __ldg(r + 2 * ns); nsa = __ldg(r + 2 * ns + 1);
+				if ((start & 3) == 0 && start + WALK_AHEAD < n) prefetch_l2(r + 2 * (start + WALK_AHEAD));
+				may_grow = true;
+			}
+		}
+		pool.angle[begin_f + i] = sm_atan2(bestY, bestX);
+	}
+}
+
 template <typename T>
 void launch_describe(const T* d_ii, int W, int H, const DescribeParams& p, const DescribeTables& t, const Pool& pool,
                      const int* d_begin, const int* d_end, int frame0, bool do_orientation, bool do_describe, cudaStream_t st) {
@@ -484,6 +554,15 @@ void launch_describe(const T* d_ii, int W, int H, const DescribeParams& p, const
 	static const int env_cap = getenv("BS_DESC_CTAS") ? atoi(getenv("BS_DESC_CTAS")) : 0;
 	ctas_per_sm = ctas_per_sm > cap ? cap : (ctas_per_sm < 1 ? 1 : ctas_per_sm);
 	if (env_cap > 0 && env_cap < ctas_per_sm) ctas_per_sm = env_cap;
+	if (do_orientation && p.ori_variant == 1 && t.d_walk && t.walk_cap > 0) {
+		// sliding window with scratch: samples + argsort (describe_kernel, mode 2), the walks (one thread each), then the descriptors
+		BS_LAUNCH((describe_kernel<T>), sm_count * ctas_per_sm, DESC_WARPS * 32, S.total, st, d_ii, W, H, p, t, S, pool, d_begin, d_end, frame0, 2, 0);
+		BS_LAUNCH(sliding_walk_kernel, sm_count * 10, 128, 0, st, reinterpret_cast<const double2*>(t.d_walk), S.ori_n, p, pool, d_begin, d_end,
+		          t.walk_cap);
+		if (do_describe)
+			BS_LAUNCH((describe_kernel<T>), sm_count * ctas_per_sm, DESC_WARPS * 32, S.total, st, d_ii, W, H, p, t, S, pool, d_begin, d_end, frame0, 0, 1);
+		return;
+	}
 	BS_LAUNCH((describe_kernel<T>), sm_count * ctas_per_sm, DESC_WARPS * 32, S.total, st, d_ii, W, H, p, t, S, pool, d_begin, d_end, frame0,
 	          do_orientation ? 1 : 0, do_describe ? 1 : 0);
 }
