@@ -178,18 +178,27 @@ struct bs_surf {
 	int out_dof() const { return ds.p.dof * std::max(bands, 1); }
 	cudaStream_t stream = nullptr;
 	cudaEvent_t done = nullptr;
-	// Optional (BS_OVERLAP=1): orientation+descriptor on a second stream, one chunk behind detection.  Measured +1.5 %
-	// (4591 vs 4522 frames/s): both kernels are persistent and fill every SM, so they barely co-run; off by default because
-	// it also blurs the per-stage timings.
-	cudaStream_t side = nullptr;
-	cudaEvent_t ev_chunk = nullptr, ev_group[2] = {nullptr, nullptr}, ev_side = nullptr;
-	bool overlap = false;
+	// A device-resident batch is worked on by up to MAX_WAYS streams ("ways"), each with its own integral / intensity /
+	// staging buffers, group after group in turn: the latency-bound kernels of one group (NMS, compaction, the tails of the
+	// persistent kernels) overlap the throughput-bound ones of another.  All ways write one pool: the compaction of a chunk
+	// continues the frame offsets of the chunk before it, so it waits for that chunk's compaction event.  Way 0 runs on
+	// the caller's stream.  (Measured at 1080p, 1024 frames: see DESIGN.md section 4.)
+	static constexpr int MAX_WAYS = 4;
+	struct Way {
+		DevBuf d_ii, d_inten, d_stage, d_counts, d_offsets, d_keys, d_keep;
+		cudaStream_t st = nullptr;                 // internal stream (ways >= 1)
+		cudaEvent_t ev_compact = nullptr, ev_done = nullptr;
+		void release() { d_ii.release(); d_inten.release(); d_stage.release(); d_counts.release(); d_offsets.release(); d_keys.release(); d_keep.release(); }
+	};
+	Way ways[MAX_WAYS];
+	int n_ways = 3, ways_used = 1;
+	cudaEvent_t ev_in = nullptr;
 	DescribeSetup ds;
 	// workspace
 	int chunk_req = 0; long pool_req = 0;
 	int W = 0, H = 0, chunk = 0;
 	Plan plan{};
-	DevBuf d_plan, d_in, d_ii, d_inten, d_stage, d_counts, d_offsets, d_frame_offset, d_keys, d_keep;
+	DevBuf d_plan, d_in, d_frame_offset;
 	DevBuf d_gray, d_ii_bands;    // colour SURF: band average (pixel type) and the band integrals [band][group][H][W]
 	PoolBufs pool;
 	void* h_pinned = nullptr; size_t h_pinned_bytes = 0;
@@ -261,15 +270,21 @@ void bs_surf::ensure(int w, int h, int nbatch) {
 	gframes = std::max(chunk, (gframes / chunk) * chunk);
 	group = std::min(std::max(gframes, chunk), std::max(nbatch, 1));
 	if (group < chunk) group = chunk;
-	d_ii.reserve(px * 4 * group * (overlap ? 2 : 1));        // two integral groups in flight when describe overlaps detection
-	d_inten.reserve((size_t)std::max<long>(plan.inten_per_frame, 1) * 4 * chunk);
+	// the walk scratch of the sliding-window orientation and the colour buffers exist once per handle: one way for those
+	const int groups = (nbatch + group - 1) / group;
+	ways_used = (ds.p.ori_variant == 1 || bands > 0) ? 1 : std::max(1, std::min(std::min(n_ways, (int)MAX_WAYS), groups));
 	const size_t nctas = (size_t)std::max(plan.ctas_per_frame, 1) * chunk;
-	d_stage.reserve(nctas * NMS_CTA_BLOCKS * sizeof(RawPoint));
-	d_counts.reserve(nctas * sizeof(int));
-	d_offsets.reserve((nctas + chunk) * sizeof(int));      // + one frame total per frame of the chunk
-	if (plan.max_per_level > 0) {          // SelectNBestFeatures scratch: one key and one flag per NMS block
-		d_keys.reserve(nctas * NMS_CTA_BLOCKS * sizeof(unsigned));
-		d_keep.reserve(nctas * NMS_CTA_BLOCKS);
+	for (int k = 0; k < ways_used; k++) {
+		Way& w = ways[k];
+		w.d_ii.reserve(px * 4 * group);
+		w.d_inten.reserve((size_t)std::max<long>(plan.inten_per_frame, 1) * 4 * chunk);
+		w.d_stage.reserve(nctas * NMS_CTA_BLOCKS * sizeof(RawPoint));
+		w.d_counts.reserve(nctas * sizeof(int));
+		w.d_offsets.reserve((nctas + chunk) * sizeof(int));      // + one frame total per frame of the chunk
+		if (plan.max_per_level > 0) {          // SelectNBestFeatures scratch: one key and one flag per NMS block
+			w.d_keys.reserve(nctas * NMS_CTA_BLOCKS * sizeof(unsigned));
+			w.d_keep.reserve(nctas * NMS_CTA_BLOCKS);
+		}
 	}
 	d_frame_offset.reserve((size_t)(nbatch + 1) * sizeof(int));
 	long cap = pool_req > 0 ? pool_req : (long)nbatch * std::max<long>((long)px / 64, 256);
@@ -290,43 +305,46 @@ template <typename TI, typename TII>
 void bs_surf::run_typed(const void* d_pixels, long frame_stride, int stride, int nbatch, cudaStream_t st) {
 	int* fo = d_frame_offset.as<int>();
 	const long px = (long)W * H;
-	cudaStream_t ds_st = overlap ? side : st;              // stream of the describe launches
-	int gi = 0;
+	const int nw = ways_used;
+	if (nw > 1) {                                           // the other ways start once the caller's stream has the input (and fo[0])
+		BS_CUDA(cudaEventRecord(ev_in, st));
+		for (int k = 1; k < nw; k++) BS_CUDA(cudaStreamWaitEvent(ways[k].st, ev_in, 0));
+	}
+	int gi = 0, prev_way = -1;
 	for (int g0 = 0; g0 < nbatch; g0 += group, gi++) {
 		const int g = std::min(group, nbatch - g0);
-		const int gb = overlap ? (gi & 1) : 0;
-		TII* ii = d_ii.as<TII>() + (long)gb * group * px;
+		const int wi = gi % nw;
+		Way& w = ways[wi];
+		cudaStream_t ws = wi == 0 ? st : w.st;
+		TII* ii = w.d_ii.as<TII>();
 		const TI* in = static_cast<const TI*>(d_pixels) + (long)g0 * frame_stride;
-		if (overlap && gi >= 2) BS_CUDA(cudaStreamWaitEvent(st, ev_group[gb], 0));   // describe of group gi-2 is done with this buffer
-		stage_begin(0, st);
-		launch_integral<TI, TII>(in, frame_stride, stride, ii, W, H, g, st);
-		stage_end(st);
+		stage_begin(0, ws);
+		launch_integral<TI, TII>(in, frame_stride, stride, ii, W, H, g, ws);
+		stage_end(ws);
 		for (int f0 = g0; f0 < g0 + g; f0 += chunk) {
 			const int c = std::min(chunk, g0 + g - f0);
 			const TII* cii = ii + (long)(f0 - g0) * px;
-			stage_begin(1, st);
-			launch_hessian_plan<TII>(cii, plan, d_plan.as<Plan>(), d_inten.as<float>(), c, st);
-			stage_end(st);
-			stage_begin(2, st);
-			launch_nms(plan, d_plan.as<Plan>(), d_inten.as<float>(), c, d_stage.as<RawPoint>(), d_counts.as<int>(), d_keys.as<unsigned>(),
-			           d_keep.as<unsigned char>(), st);
-			stage_end(st);
-			stage_begin(3, st);
-			launch_compact(plan, c, f0, d_stage.as<RawPoint>(), d_counts.as<int>(), d_offsets.as<int>(), fo, pool.view, st);
-			stage_end(st);
-			if (overlap) {
-				BS_CUDA(cudaEventRecord(ev_chunk, st));
-				BS_CUDA(cudaStreamWaitEvent(side, ev_chunk, 0));
-			}
-			stage_begin(4, ds_st);
-			launch_describe<TII>(cii, W, H, ds.p, ds.tables, pool.view, fo + f0, fo + f0 + c, f0, true, true, ds_st);
-			stage_end(ds_st);
+			stage_begin(1, ws);
+			launch_hessian_plan<TII>(cii, plan, d_plan.as<Plan>(), w.d_inten.as<float>(), c, ws);
+			stage_end(ws);
+			stage_begin(2, ws);
+			launch_nms(plan, d_plan.as<Plan>(), w.d_inten.as<float>(), c, w.d_stage.as<RawPoint>(), w.d_counts.as<int>(), w.d_keys.as<unsigned>(),
+			           w.d_keep.as<unsigned char>(), ws);
+			stage_end(ws);
+			if (prev_way >= 0 && prev_way != wi) BS_CUDA(cudaStreamWaitEvent(ws, ways[prev_way].ev_compact, 0));   // fo[f0] is final
+			stage_begin(3, ws);
+			launch_compact(plan, c, f0, w.d_stage.as<RawPoint>(), w.d_counts.as<int>(), w.d_offsets.as<int>(), fo, pool.view, ws);
+			stage_end(ws);
+			if (nw > 1) BS_CUDA(cudaEventRecord(w.ev_compact, ws));
+			prev_way = wi;
+			stage_begin(4, ws);
+			launch_describe<TII>(cii, W, H, ds.p, ds.tables, pool.view, fo + f0, fo + f0 + c, f0, true, true, ws);
+			stage_end(ws);
 		}
-		if (overlap) BS_CUDA(cudaEventRecord(ev_group[gb], side));
 	}
-	if (overlap) {                                          // everything later on `st` (and the `done` event) follows the describes
-		BS_CUDA(cudaEventRecord(ev_side, side));
-		BS_CUDA(cudaStreamWaitEvent(st, ev_side, 0));
+	for (int k = 1; k < nw; k++) {                          // everything later on `st` (and the `done` event) follows all ways
+		BS_CUDA(cudaEventRecord(ways[k].ev_done, ways[k].st));
+		BS_CUDA(cudaStreamWaitEvent(st, ways[k].ev_done, 0));
 	}
 }
 
@@ -343,7 +361,7 @@ void bs_surf::run_planar_typed(const void* d_pixels, long frame_stride, long ban
 	const int dof = ds.p.dof, total = dof * bands;
 	for (int g0 = 0; g0 < nbatch; g0 += group) {
 		const int g = std::min(group, nbatch - g0);
-		TII* ii = d_ii.as<TII>();
+		TII* ii = ways[0].d_ii.as<TII>();
 		TII* bii = d_ii_bands.as<TII>();
 		const TI* in = static_cast<const TI*>(d_pixels) + (long)g0 * frame_stride;
 		stage_begin(0, st);
@@ -355,14 +373,14 @@ void bs_surf::run_planar_typed(const void* d_pixels, long frame_stride, long ban
 			const int c = std::min(chunk, g0 + g - f0);
 			const TII* cii = ii + (long)(f0 - g0) * px;
 			stage_begin(1, st);
-			launch_hessian_plan<TII>(cii, plan, d_plan.as<Plan>(), d_inten.as<float>(), c, st);
+			launch_hessian_plan<TII>(cii, plan, d_plan.as<Plan>(), ways[0].d_inten.as<float>(), c, st);
 			stage_end(st);
 			stage_begin(2, st);
-			launch_nms(plan, d_plan.as<Plan>(), d_inten.as<float>(), c, d_stage.as<RawPoint>(), d_counts.as<int>(), d_keys.as<unsigned>(),
-			           d_keep.as<unsigned char>(), st);
+			launch_nms(plan, d_plan.as<Plan>(), ways[0].d_inten.as<float>(), c, ways[0].d_stage.as<RawPoint>(), ways[0].d_counts.as<int>(), ways[0].d_keys.as<unsigned>(),
+			           ways[0].d_keep.as<unsigned char>(), st);
 			stage_end(st);
 			stage_begin(3, st);
-			launch_compact(plan, c, f0, d_stage.as<RawPoint>(), d_counts.as<int>(), d_offsets.as<int>(), fo, pool.view, st);
+			launch_compact(plan, c, f0, ways[0].d_stage.as<RawPoint>(), ways[0].d_counts.as<int>(), ways[0].d_offsets.as<int>(), fo, pool.view, st);
 			stage_end(st);
 			stage_begin(4, st);
 			DescribeParams po = ds.p;
@@ -461,12 +479,13 @@ int bs_surf_create(int device, const bs_fh_cfg* fh, const bs_ori_cfg* ori, const
 		s->device = device; s->fh = f; s->ori = o; s->desc = d; s->pixel_type = pixel_type;
 		BS_CUDA(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
 		BS_CUDA(cudaEventCreateWithFlags(&s->done, cudaEventDisableTiming));
-		BS_CUDA(cudaStreamCreateWithFlags(&s->side, cudaStreamNonBlocking));
-		BS_CUDA(cudaEventCreateWithFlags(&s->ev_chunk, cudaEventDisableTiming));
-		BS_CUDA(cudaEventCreateWithFlags(&s->ev_group[0], cudaEventDisableTiming));
-		BS_CUDA(cudaEventCreateWithFlags(&s->ev_group[1], cudaEventDisableTiming));
-		BS_CUDA(cudaEventCreateWithFlags(&s->ev_side, cudaEventDisableTiming));
-		s->overlap = getenv("BS_OVERLAP") != nullptr;
+		BS_CUDA(cudaEventCreateWithFlags(&s->ev_in, cudaEventDisableTiming));
+		for (int k = 0; k < bs_surf::MAX_WAYS; k++) {
+			if (k > 0) BS_CUDA(cudaStreamCreateWithFlags(&s->ways[k].st, cudaStreamNonBlocking));
+			BS_CUDA(cudaEventCreateWithFlags(&s->ways[k].ev_compact, cudaEventDisableTiming));
+			BS_CUDA(cudaEventCreateWithFlags(&s->ways[k].ev_done, cudaEventDisableTiming));
+		}
+		if (const char* e = getenv("BS_WAYS")) s->n_ways = std::min(std::max(atoi(e), 1), (int)bs_surf::MAX_WAYS);
 		if (const char* e = getenv("BS_LANES")) s->n_lanes = std::min(std::max(atoi(e), 2), (int)bs_surf::MAX_LANES);
 		s->ds.build(o, d);
 		s->ds.upload();
@@ -530,16 +549,17 @@ int bs_surf_destroy(bs_surf* s) {
 		DeviceGuard g(s->device);
 		cudaDeviceSynchronize();
 		s->ds.release(); s->pool.release();
-		s->d_plan.release(); s->d_in.release(); s->d_ii.release(); s->d_inten.release(); s->d_stage.release();
-		s->d_counts.release(); s->d_offsets.release(); s->d_frame_offset.release(); s->d_keys.release(); s->d_keep.release();
+		s->d_plan.release(); s->d_in.release(); s->d_frame_offset.release();
 		s->d_gray.release(); s->d_ii_bands.release();
 		if (s->h_pinned) cudaFreeHost(s->h_pinned);
 		if (s->done) cudaEventDestroy(s->done);
-		if (s->ev_chunk) cudaEventDestroy(s->ev_chunk);
-		if (s->ev_group[0]) cudaEventDestroy(s->ev_group[0]);
-		if (s->ev_group[1]) cudaEventDestroy(s->ev_group[1]);
-		if (s->ev_side) cudaEventDestroy(s->ev_side);
-		if (s->side) cudaStreamDestroy(s->side);
+		if (s->ev_in) cudaEventDestroy(s->ev_in);
+		for (int k = 0; k < bs_surf::MAX_WAYS; k++) {
+			s->ways[k].release();
+			if (s->ways[k].ev_compact) cudaEventDestroy(s->ways[k].ev_compact);
+			if (s->ways[k].ev_done) cudaEventDestroy(s->ways[k].ev_done);
+			if (s->ways[k].st) cudaStreamDestroy(s->ways[k].st);
+		}
 		for (cudaEvent_t e : s->ev) cudaEventDestroy(e);
 		if (s->stream) cudaStreamDestroy(s->stream);
 		delete s;
