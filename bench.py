@@ -134,6 +134,7 @@ def run_gpu(args, rank, world, local_rank):
     det = FactoryDetectDescribe.surfFast(None, None, None, np.float32, device=local_rank)
     if args.chunk:
         det.setWorkspace(args.chunk, 0)
+    det.setWays(args.ways)
 
     def barrier():
         torch.cuda.synchronize(dev)
@@ -146,7 +147,6 @@ def run_gpu(args, rank, world, local_rank):
     for _ in range(args.warmup):
         step()
     total_features = det.totalFeatures()          # synchronises; also proves the pool did not overflow
-    det.setTiming(True)
     launches0 = _native.lib().bs_launch_count()
     sampler = ClockSampler(local_rank)
     if rank == 0:
@@ -161,10 +161,29 @@ def run_gpu(args, rank, world, local_rank):
     ms = e0.elapsed_time(e1)
     clocks = sampler.stop() if rank == 0 else None
     launches = _native.lib().bs_launch_count() - launches0
-    timing = det.getTiming()
-    det.setTiming(False)
+    # Per-kernel durations for the roofline: the timed region above spreads the batch over `ways` streams, so a stage's
+    # event pair there would also count the kernels of the other streams that share the SMs with it.  The same K steps are
+    # therefore run once more with every kernel on ONE stream and an event pair around each stage launch.
+    timing, ms_single = None, None
+    if rank == 0:
+        det.setWays(1)
+        step()
+        det.totalFeatures()
+        det.setTiming(True)
+        torch.cuda.synchronize(dev)
+        s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s0.record()
+        for _ in range(args.steps):
+            step()
+        s1.record()
+        torch.cuda.synchronize(dev)
+        ms_single = s0.elapsed_time(s1)
+        timing = det.getTiming()
+        det.setTiming(False)
+        det.setWays(args.ways)
+    barrier()
     return dict(torch=torch, dist=dist, dev=dev, det=det, frames=frames, ms=ms, clocks=clocks, launches=launches,
-                timing=timing, total_features=total_features, B=B)
+                timing=timing, ms_single=ms_single, total_features=total_features, B=B)
 
 
 def run_e2e(g, steps):
@@ -230,6 +249,7 @@ def main():
     ap.add_argument("--impl", default="native", choices=["native", "reference"])
     ap.add_argument("--batch", type=int, default=1024, help="1080p frames per step per GPU (BASELINE configs[1]: 1024)")
     ap.add_argument("--chunk", type=int, default=0, help="frames per kernel wave (0 = library default)")
+    ap.add_argument("--ways", type=int, default=2, help="streams a device-resident batch is spread over (1..4)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-assoc", action="store_true", help="skip the association leg (100k x 100k, rank 0)")
     ap.add_argument("--no-e2e", action="store_true")
@@ -294,11 +314,14 @@ def main():
             "dtype": "f32", "data": "synthetic",
             "config": {"workload": "surfFast detect+describe, %d x 1920x1080 GrayF32 per GPU per step (BASELINE configs[1])" % B,
                        "batch_per_gpu": B, "features_per_frame": nfeat,
+                       "ways": args.ways,
                        "l2": "inputs larger than L2 (%.1f GB batch per step)" % (B * W * H * 4 / 1e9)},
             "roofline": {"bound": "hbm", "kernel": kernel_name, "achieved": achieved, "peak": pk["hbm_gbs"],
                          "unit": "GB/s", "frac": achieved / pk["hbm_gbs"], "traffic": traffic, "peak_kind": pk_kind,
                          "frames_per_launch": chunk_frames, "algorithmic_bytes_per_launch": alg_bytes,
                          "share_of_step": hess_ms / total_stage,
+                         "timed": "event pair per stage launch over the same %d steps run on one stream (%.1f ms per step); "
+                                  "the timed region of `value` overlaps %d streams" % (args.steps, g["ms_single"] / args.steps, args.ways),
                          "pipeline_achieved_gbs": value / world * pipeline_bytes / 1e9,
                          "pipeline_frac": value / world * pipeline_bytes / 1e9 / pk["hbm_gbs"]},
             "stage_ms_per_step": {k: v / args.steps for k, v in stage_ms.items()},

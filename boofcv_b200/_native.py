@@ -55,6 +55,7 @@ SIGNATURES = {
     "bs_surf_create": (_i, [_i, C.POINTER(FhCfg), C.POINTER(OriCfg), C.POINTER(DescCfg), _i, C.POINTER(_vp)]),
     "bs_surf_destroy": (_i, [_vp]),
     "bs_surf_set_workspace": (_i, [_vp, _i, _l]),
+    "bs_surf_set_ways": (_i, [_vp, _i]),
     "bs_surf_detect": (_i, [_vp, _vp, _i, _i, _i, _i]),
     "bs_surf_create_planar": (_i, [_i, C.POINTER(FhCfg), C.POINTER(OriCfg), C.POINTER(DescCfg), _i, _i, C.POINTER(_vp)]),
     "bs_surf_detect_planar": (_i, [_vp, C.POINTER(_vp), _i, _i, _i, _i, _i]),
@@ -72,6 +73,7 @@ SIGNATURES = {
     "bs_surf_view": (_i, [_vp, C.POINTER(DeviceView)]),
     "bs_integral": (_i, [_i, _i, _vp, _i, _i, _i, _vp]),
     "bs_hessian": (_i, [_i, _i, _vp, _i, _i, _i, _i, _vp]),
+    "bs_fh_intensity": (_i, [_i, _i, _vp, _i, _i, C.POINTER(FhCfg), _pi, _vp, C.POINTER(C.c_long), _vp, _l]),
     "bs_fh_detect": (_i, [_i, _i, _vp, _i, _i, C.POINTER(FhCfg), _i, _pi, _vp, _vp, _vp]),
     "bs_orientation": (_i, [_i, _i, _vp, _i, _i, C.POINTER(OriCfg), _vp, _i, _vp]),
     "bs_describe": (_i, [_i, _i, _vp, _i, _i, C.POINTER(DescCfg), _vp, _vp, _i, _vp, _vp]),

@@ -191,7 +191,7 @@ struct bs_surf {
 		void release() { d_ii.release(); d_inten.release(); d_stage.release(); d_counts.release(); d_offsets.release(); d_keys.release(); d_keep.release(); }
 	};
 	Way ways[MAX_WAYS];
-	int n_ways = 3, ways_used = 1;
+	int n_ways = 2, ways_used = 1;
 	cudaEvent_t ev_in = nullptr;
 	DescribeSetup ds;
 	// workspace
@@ -574,6 +574,15 @@ int bs_surf_set_workspace(bs_surf* s, int chunk_frames, long pool_features) {
 	});
 }
 
+int bs_surf_set_ways(bs_surf* s, int ways) {
+	return guarded([&] {
+		if (!s) fail(BS_ERR_ARG, "handle is null");
+		if (ways < 1 || ways > bs_surf::MAX_WAYS) fail(BS_ERR_ARG, "ways must be 1..4");
+		s->finish();
+		s->n_ways = ways;
+	});
+}
+
 int bs_surf_dof(const bs_surf* s) { return s ? s->out_dof() : 0; }
 
 int bs_surf_set_timing(bs_surf* s, int on) {
@@ -859,6 +868,40 @@ int bs_hessian(int device, int ii_type, const void* ii, int width, int height, i
 		BS_CUDA(cudaStreamSynchronize(ts.st));
 		BS_CUDA(cudaMemcpy(out, d_out.p, n * 4, cudaMemcpyDeviceToHost));
 		d_ii.release(); d_out.release();
+	});
+}
+
+int bs_fh_intensity(int device, int ii_type, const void* ii, int width, int height, const bs_fh_cfg* cfg, int* n_layers, long* layers,
+                    long* n_floats, float* out, long max_floats) {
+	return guarded([&] {
+		bs_fh_cfg f;
+		if (cfg) f = *cfg; else bs_fh_cfg_default(&f);
+		check_fh_cfg(f);
+		if (!n_layers || !n_floats) fail(BS_ERR_ARG, "null argument");
+		if (width <= 0 || height <= 0) fail(BS_ERR_ARG, "image width and height must be positive");
+		Plan plan = make_plan(f, width, height);
+		*n_layers = plan.n_layers; *n_floats = plan.inten_per_frame;
+		if (layers)
+			for (int k = 0; k < plan.n_layers; k++) {
+				const Layer& L = plan.layers[k];
+				layers[5 * k] = L.size; layers[5 * k + 1] = L.skip; layers[5 * k + 2] = L.w; layers[5 * k + 3] = L.h; layers[5 * k + 4] = L.offset;
+			}
+		if (!out || plan.inten_per_frame == 0) return;
+		if (max_floats < plan.inten_per_frame) fail(BS_ERR_CAPACITY, "output buffer smaller than the scale space");
+		check_device(device);
+		DeviceGuard g(device);
+		TempStream ts;
+		DevBuf d_ii, d_plan, d_inten;
+		upload_ii(d_ii, ii, width, height);
+		d_plan.reserve(sizeof(Plan));
+		h2d_sync(d_plan.p, &plan, sizeof(Plan));
+		d_inten.reserve((size_t)plan.inten_per_frame * 4);
+		BS_CUDA(cudaDeviceSynchronize());
+		if (ii_type == BS_PIXEL_F32) launch_hessian_plan<float>(d_ii.as<float>(), plan, d_plan.as<Plan>(), d_inten.as<float>(), 1, ts.st);
+		else launch_hessian_plan<int32_t>(d_ii.as<int32_t>(), plan, d_plan.as<Plan>(), d_inten.as<float>(), 1, ts.st);
+		BS_CUDA(cudaStreamSynchronize(ts.st));
+		BS_CUDA(cudaMemcpy(out, d_inten.p, (size_t)plan.inten_per_frame * 4, cudaMemcpyDeviceToHost));
+		d_ii.release(); d_plan.release(); d_inten.release();
 	});
 }
 

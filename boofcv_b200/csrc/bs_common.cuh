@@ -80,7 +80,10 @@ struct Plan {
 	Layer layers[MAX_LAYERS];
 	Level levels[MAX_LEVELS];
 };
-constexpr int NMS_CTA_BLOCKS = 256;   // NMS blocks (=threads) per CTA; also the staging slots per CTA
+#ifndef BS_NMS_CTA
+#define BS_NMS_CTA 256
+#endif
+constexpr int NMS_CTA_BLOCKS = BS_NMS_CTA;   // NMS blocks (=threads) per CTA; also the staging slots per CTA
 
 Plan make_plan(const bs_fh_cfg& cfg, int W, int H);
 void check_fh_cfg(const bs_fh_cfg& c);

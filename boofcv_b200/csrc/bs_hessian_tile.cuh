@@ -179,6 +179,59 @@ template <int SKIP, int S0, int STEP, int NS, int TX, int TY> struct TmaGeo {
 	}
 };
 
+// Border samples out of the staged tile.  computeHessian / block_zero (ImplIntegralImageFeatureIntensity.java:115-127,
+// ImplIntegralImageOps.java:195-214) reads 0 where a corner coordinate is negative and clamps coordinates beyond the last
+// column / row.  The TMA unit zero-fills everything outside the image, so the negative side needs nothing; the far side
+// reads the tile with clamped row / column indices.  The border ring cannot simply take the compile-time path above even
+// where no clamp is needed: hessianInner sums the Dyy boxes as br-bl-tr+tl (:185-186) while block_zero sums every box as
+// br-tr-bl+tl, and the two round differently.  One out-of-line copy, runtime box size.  cr, cc = tile row / column of the
+// sample's pixel; rmax, cmax = tile row / column of the image's last row / column.
+template <typename G, int SKIP>
+static __device__ __noinline__ float tile_clamped_response(const float* __restrict__ tile, int size, int cr, int cc, int rmax, int cmax) {
+	const int bs = size / 3, bl = size - bs - 1, rf = size / 2, rs = bl / 2;
+	const float norm = 1.0f / (float)(size * size);
+	auto at = [&](int dr, int dc) -> float {
+		const int r = min(cr + dr, rmax), c = min(cc + dc, cmax);
+		return SKIP == 1 ? tile[r * G::BOXW + c] : tile[r * G::PW + (c % SKIP) * G::PLANE + c / SKIP];
+	};
+	const int t = -rs - 1, bo = t + bl, c0 = -rf - 1;
+	float Dxx = at(bo, c0 + 3 * bs) - at(t, c0 + 3 * bs) - at(bo, c0) + at(t, c0);
+	Dxx -= 3.0f * (at(bo, c0 + 2 * bs) - at(t, c0 + 2 * bs) - at(bo, c0 + bs) + at(t, c0 + bs));
+	const int l = -rs - 1, r = l + bl, r0 = -rf - 1;
+	float Dyy = at(r0 + 3 * bs, r) - at(r0, r) - at(r0 + 3 * bs, l) + at(r0, l);                     // block_zero order: br - tr - bl + tl
+	Dyy -= 3.0f * (at(r0 + 2 * bs, r) - at(r0 + bs, r) - at(r0 + 2 * bs, l) + at(r0 + bs, l));
+	const int y1 = -bs - 1, y2 = -1, y3 = 0, y4 = bs, x0 = -bs - 1, x1 = x0 + bs, x3 = x0 + bs + 1, x4 = x3 + bs;
+	float Dxy = at(y2, x1) - at(y1, x1) - at(y2, x0) + at(y1, x0);
+	Dxy -= at(y2, x4) - at(y1, x4) - at(y2, x3) + at(y1, x3);
+	Dxy += at(y4, x4) - at(y3, x4) - at(y4, x3) + at(y3, x3);
+	Dxy -= at(y4, x1) - at(y3, x1) - at(y4, x0) + at(y3, x0);
+	Dxx *= norm; Dxy *= norm; Dyy *= norm;
+	const float a = Dxx * Dyy;
+	float bb = 0.81f * Dxy;
+	bb = bb * Dxy;
+	return a - bb;
+}
+
+// EDGE = the tile holds samples of the reference's border ring of some layer (uniform per tile)
+template <typename G, int SKIP, int S0, int STEP, int NS, int I, bool EDGE>
+struct TmaLayers {
+	static __device__ __forceinline__ void run(const float* __restrict__ base, const float* __restrict__ tile, int cr, int cc, int rmax, int cmax,
+	                                           const Layer* __restrict__ layers, float* __restrict__ inten, int x, int y) {
+		constexpr int SIZE = S0 + I * STEP;
+		constexpr int border = InnerBorder<SIZE, SKIP>::value;
+		const Layer& L = layers[I];
+		float v;
+		if (EDGE && !(x >= border && x < L.w - border && y >= border && y < L.h - border)) v = tile_clamped_response<G, SKIP>(tile, SIZE, cr, cc, rmax, cmax);
+		else v = tile_response<SIZE, G>(base);
+		inten[L.offset + (long)y * L.w + x] = v;
+		TmaLayers<G, SKIP, S0, STEP, NS, I + 1, EDGE>::run(base, tile, cr, cc, rmax, cmax, layers, inten, x, y);
+	}
+};
+template <typename G, int SKIP, int S0, int STEP, int NS, bool EDGE>
+struct TmaLayers<G, SKIP, S0, STEP, NS, NS, EDGE> {
+	static __device__ __forceinline__ void run(const float*, const float*, int, int, int, int, const Layer*, float*, int, int) {}
+};
+
 template <int SKIP, int S0, int STEP, int NS, int TX, int TY, int THREADS>
 __global__ void __launch_bounds__(THREADS)
 hessian_tma_kernel(const __grid_constant__ CUtensorMap tm, const float* __restrict__ ii_all, int W, int H, OctaveLayers oct, int tiles_x,
@@ -233,14 +286,27 @@ hessian_tma_kernel(const __grid_constant__ CUtensorMap tm, const float* __restri
 		}
 		const int frame = (int)(item / per_frame), t = (int)(item - (long)frame * per_frame);
 		const int tyi = t / tiles_x, txi = t - tyi * tiles_x;
-		const float* ii = ii_all + (long)frame * W * H;
 		float* inten = inten_all + (long)frame * inten_per_frame;
 		const int x = txi * TX + tx;
+		// tile row / column of the image's last row / column; edge tile = it reaches into the widest border ring of the octave
+		const int rmax = H - 1 - (tyi * TY * SKIP - G::HALO), cmax = W - 1 - (txi * TX * SKIP - G::HALO_X);
+		constexpr int MB = InnerBorder<G::SMAX, SKIP>::value;
+		const bool edge = txi * TX < MB || txi * TX + TX > w - MB || tyi * TY < MB || tyi * TY + TY > h - MB;
+		constexpr int ROWP = SKIP == 1 ? G::BOXW : G::PW;
 		if (x < w) {
+			if (!edge) {
 #pragma unroll 1
-			for (int ty = ty0; ty < TY; ty += ROWS_PER_PASS) {
-				const int y = tyi * TY + ty;
-				if (y < h) TileLayers<G, SKIP, S0, STEP, NS, 0>::run(tile + ty * SKIP * (SKIP == 1 ? G::BOXW : G::PW) + tx, ii, W, H, oct.l, inten, x, y);
+				for (int ty = ty0; ty < TY; ty += ROWS_PER_PASS) {
+					const int y = tyi * TY + ty;
+					if (y < h) TmaLayers<G, SKIP, S0, STEP, NS, 0, false>::run(tile + ty * SKIP * ROWP + tx, tile, 0, 0, 0, 0, oct.l, inten, x, y);
+				}
+			} else {
+#pragma unroll 1
+				for (int ty = ty0; ty < TY; ty += ROWS_PER_PASS) {
+					const int y = tyi * TY + ty;
+					if (y < h) TmaLayers<G, SKIP, S0, STEP, NS, 0, true>::run(tile + ty * SKIP * ROWP + tx, tile, G::HALO + ty * SKIP, G::HALO_X + tx * SKIP,
+					                                                           rmax, cmax, oct.l, inten, x, y);
+				}
 			}
 		}
 		__syncthreads();

@@ -83,6 +83,24 @@ def hessian(ii, skip, size, device=0):
     return out
 
 
+def fh_intensity(ii, cfg=None, device=0):
+    """Every layer of the Fast-Hessian scale space, computed by the kernels the batch path uses (FastHessianFeatureDetector
+    .detectOctave's intensity[] images).  Returns a list of dicts {size, skip, intensity[h,w]} in (octave, scale) order."""
+    a, t = _ii(ii)
+    h, w = a.shape
+    c = fh_cfg(cfg)
+    nl, nf = C.c_int(0), C.c_long(0)
+    layers = np.zeros((64, 5), np.int64)
+    N.check(N.lib().bs_fh_intensity(device, t, _p(a), w, h, C.byref(c), C.byref(nl), _p(layers), C.byref(nf), None, 0))
+    out = np.zeros(max(nf.value, 1), np.float32)
+    N.check(N.lib().bs_fh_intensity(device, t, _p(a), w, h, C.byref(c), C.byref(nl), _p(layers), C.byref(nf), _p(out), out.size))
+    res = []
+    for k in range(nl.value):
+        size, skip, lw, lh, off = (int(v) for v in layers[k])
+        res.append(dict(size=size, skip=skip, intensity=out[off:off + lw * lh].reshape(lh, lw).copy()))
+    return res
+
+
 def fh_detect(ii, cfg=None, device=0, max_out=None):
     a, t = _ii(ii)
     h, w = a.shape

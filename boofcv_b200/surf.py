@@ -169,6 +169,9 @@ class DetectDescribeSurf:
     def setWorkspace(self, chunkFrames=0, poolFeatures=0):
         N.check(N.lib().bs_surf_set_workspace(self._h, chunkFrames, poolFeatures))
 
+    def setWays(self, ways):
+        N.check(N.lib().bs_surf_set_ways(self._h, ways))
+
     # --- InterestPointDetector.detect
     def detect(self, input):
         a = np.asarray(input)

@@ -115,6 +115,9 @@ int bs_surf_destroy(bs_surf* s);
  * intensity workspace: 4*sum(layers) bytes per frame); pool_features = capacity of the feature pool of one detect call
  * (0 = batch * width*height/64). */
 int bs_surf_set_workspace(bs_surf* s, int chunk_frames, long pool_features);
+/* Streams ("ways", 1..4, default 2) a device-resident batch is spread over, integral group by integral group; 1 = every
+ * kernel on the caller's stream (what the per-stage timing of bs_surf_set_timing wants).  Results do not depend on it. */
+int bs_surf_set_ways(bs_surf* s, int ways);
 
 /* WrapDetectDescribeSurf.detect(T input) :75-96.  HOST image with BoofCV's {data,startIndex,stride,width,height}
  * (sub-images legal, main/boofcv-types/src/main/java/boofcv/struct/image/ImageBase.java:34-52).  Copies the pixels in,
@@ -191,6 +194,13 @@ int bs_integral(int device, int pixel_type, const void* in, int in_stride, int w
  * ii dense width*height of integral type (ii_type: BS_PIXEL_F32 -> float, else int32); out dense (w/skip)*(h/skip). */
 int bs_hessian(int device, int ii_type, const void* ii, int width, int height, int skip, int size, float* out);
 
+/* The whole Fast-Hessian scale space of one image through the batch path's own kernels (FastHessianFeatureDetector's
+ * intensity[] layers, F/alg/feature/detect/interest/FastHessianFeatureDetector.java:198-221, each layer =
+ * IntegralImageFeatureIntensity.hessian(integral, skip, size, intensity)).  layers[5*k..] = {size, skip, w, h, offset} of
+ * layer k (offset in floats into out); *n_layers / *n_floats are always set; out may be NULL to query the sizes, else it must
+ * hold max_floats >= *n_floats floats. */
+int bs_fh_intensity(int device, int ii_type, const void* ii, int width, int height, const bs_fh_cfg* cfg, int* n_layers,
+                    long* layers, long* n_floats, float* out, long max_floats);
 /* FastHessianFeatureDetector.detect on a given integral image
  * (F/alg/feature/detect/interest/FastHessianFeatureDetector.java:156-188).  Returns the number found in *n and fills
  * up to max_out entries: xys[3k] = {x, y, scale}, meta[4k] = {octave, level, px, py}, response[k]. */

@@ -79,6 +79,28 @@ def test_hessian_small_image(st, orc):
     assert np.array_equal(st.hessian(ii, 1, 9), orc.hessian(ii, 1, 9))
 
 
+@pytest.mark.parametrize("shape", [(400, 300), (644, 196), (250, 197), (64, 48), (1920, 1080)])
+def test_scale_space_layers_bit_exact(st, orc, shape):
+    """Every layer of the scale space as the batch path's kernels write it (TMA-staged tile kernels for octaves 0-1 when the
+    width is a multiple of 4, manual staging otherwise, the generic kernel for the sparse octaves): border ring in
+    block_zero's summation order, inner region in hessianInner's, both bit for bit."""
+    ii = orc.integral(_noise(shape[0], shape[1], 21, 0, 255))
+    layers = st.fh_intensity(ii)
+    sizes = [(L["skip"], L["size"]) for L in layers]
+    assert sizes[:4] == [(1, 9), (1, 15), (1, 21), (1, 27)]
+    for L in layers:
+        o = orc.hessian(ii, L["skip"], L["size"], nthreads=8)
+        assert L["intensity"].shape == o.shape
+        assert np.array_equal(L["intensity"].view(np.uint32), o.view(np.uint32)), (L["skip"], L["size"])
+
+
+def test_scale_space_integer_integral(st, orc):
+    u8 = np.random.default_rng(8).integers(0, 256, (120, 160), dtype=np.uint8)
+    ii = orc.integral(u8)
+    for L in st.fh_intensity(ii):
+        assert np.array_equal(L["intensity"], orc.hessian(ii, L["skip"], L["size"])), (L["skip"], L["size"])
+
+
 # ------------------------------------------------------------------ detector
 def _same_detection(g, o):
     assert len(g["x"]) == len(o["x"])
