@@ -81,7 +81,7 @@ struct Plan {
 	Level levels[MAX_LEVELS];
 };
 #ifndef BS_NMS_CTA
-#define BS_NMS_CTA 256
+#define BS_NMS_CTA 64
 #endif
 constexpr int NMS_CTA_BLOCKS = BS_NMS_CTA;   // NMS blocks (=threads) per CTA; also the staging slots per CTA
 

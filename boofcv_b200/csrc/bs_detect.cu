@@ -12,6 +12,7 @@
 #include "bs_common.cuh"
 
 #include <cfloat>
+#include <math_constants.h>
 
 namespace bs {
 
@@ -86,19 +87,19 @@ nms_kernel(const Plan* __restrict__ plan, const float* __restrict__ inten_all, R
 		}
 		ok = peak >= plan->threshold && peak != FLT_MAX;
 		if (ok) {
-			// part of checkLocalMax, done per thread before the warp-wide window test: the four direct neighbours (most block
-			// maxima that are not window maxima lose against one of them)
+			// Part of checkLocalMax, done per thread before the warp-wide window test: the four direct neighbours (most block
+			// maxima that are not window maxima lose against one of them).  Every test must pass for a point to be emitted, so
+			// their order is free: the two cheapest reads of checkMax (the same pixel in the neighbouring layers,
+			// FastHessianFeatureDetector.java:304-313) are fetched in the same round trip — not in the n-best modes, where the
+			// extractor's own output is needed.
 			const long c = (long)peakY * w + peakX;
-			if ((peakX > 0 && __ldg(mid + c - 1) >= peak) || (peakX + 1 < w && __ldg(mid + c + 1) >= peak) ||
-			    (peakY > 0 && __ldg(mid + c - w) >= peak) || (peakY + 1 < h && __ldg(mid + c + w) >= peak))
-				ok = false;
-		}
-		if (ok && mode == NMS_PLAIN) {
-			// Every test below must pass for a point to be emitted, so their order is free: try the two cheapest reads of
-			// checkMax first (the same pixel in the neighbouring layers, FastHessianFeatureDetector.java:304-313).  Not in the
-			// n-best modes, where the extractor's own output is needed.
-			const long c = (long)peakY * w + peakX;
-			if (__ldg(inten + plan->layers[V.lower].offset + c) >= peak || __ldg(inten + plan->layers[V.upper].offset + c) >= peak) ok = false;
+			const float NONE = -CUDART_INF_F;
+			const bool plain = mode == NMS_PLAIN;
+			const float nl = peakX > 0 ? __ldg(mid + c - 1) : NONE, nr = peakX + 1 < w ? __ldg(mid + c + 1) : NONE;
+			const float nu = peakY > 0 ? __ldg(mid + c - w) : NONE, nd = peakY + 1 < h ? __ldg(mid + c + w) : NONE;
+			const float sl = plain ? __ldg(inten + plan->layers[V.lower].offset + c) : NONE;
+			const float su = plain ? __ldg(inten + plan->layers[V.upper].offset + c) : NONE;
+			if (nl >= peak || nr >= peak || nu >= peak || nd >= peak || sl >= peak || su >= peak) ok = false;
 		}
 	}
 	// From here on the warp works on one candidate at a time, all 32 lanes together: ncu showed the per-thread version at 12
@@ -307,10 +308,13 @@ scan_counts_kernel(const int* __restrict__ counts, int ctas, int* __restrict__ o
 	const int f = blockIdx.x;
 	if (threadIdx.x == 0) carry = 0;
 	__syncthreads();
-	for (int c0 = 0; c0 < ctas; c0 += SCAN_THREADS) {
-		const int c = c0 + threadIdx.x;
-		const int v = c < ctas ? counts[(long)f * ctas + c] : 0;
-		int incl = v;
+	constexpr int ITEMS = 4;                   // consecutive counts per thread and pass
+	for (int c0 = 0; c0 < ctas; c0 += SCAN_THREADS * ITEMS) {
+		const int c = c0 + threadIdx.x * ITEMS;
+		int v[ITEMS], mine = 0;
+#pragma unroll
+		for (int k = 0; k < ITEMS; k++) { v[k] = c + k < ctas ? counts[(long)f * ctas + c + k] : 0; mine += v[k]; }
+		int incl = mine;
 #pragma unroll
 		for (int d = 1; d < 32; d <<= 1) {
 			const int t = __shfl_up_sync(0xffffffffu, incl, d);
@@ -325,7 +329,12 @@ scan_counts_kernel(const int* __restrict__ counts, int ctas, int* __restrict__ o
 			chunk_total += s;
 		}
 		const int base = carry;
-		if (c < ctas) offsets[(long)f * ctas + c] = base + wbase + incl - v;
+		int run = base + wbase + incl - mine;
+#pragma unroll
+		for (int k = 0; k < ITEMS; k++) {
+			if (c + k < ctas) offsets[(long)f * ctas + c + k] = run;
+			run += v[k];
+		}
 		__syncthreads();
 		if (threadIdx.x == 0) carry = base + chunk_total;
 		__syncthreads();
@@ -351,15 +360,21 @@ __global__ void frame_offsets_kernel(const int* __restrict__ frame_total, int ba
 	}
 }
 
-__global__ void __launch_bounds__(NMS_CTA_BLOCKS)
+// one thread per staging slot; a CTA covers GATHER_THREADS / NMS_CTA_BLOCKS consecutive NMS CTAs of one frame
+constexpr int GATHER_THREADS = NMS_CTA_BLOCKS > 256 ? NMS_CTA_BLOCKS : 256;
+__global__ void __launch_bounds__(GATHER_THREADS)
 gather_points_kernel(const RawPoint* __restrict__ stage, const int* __restrict__ counts, const int* __restrict__ offsets,
                      const int* __restrict__ frame_offset, int ctas, int frame0, Pool pool) {
-	const long idx = (long)blockIdx.y * ctas + blockIdx.x;
+	constexpr int PER = GATHER_THREADS / NMS_CTA_BLOCKS;
+	const int sub = threadIdx.x / NMS_CTA_BLOCKS, slot = threadIdx.x - sub * NMS_CTA_BLOCKS;
+	const int cta = blockIdx.x * PER + sub;
+	if (cta >= ctas) return;
+	const long idx = (long)blockIdx.y * ctas + cta;
 	const int n = counts[idx];
-	if ((int)threadIdx.x >= n) return;
-	const long dst = (long)frame_offset[frame0 + blockIdx.y] + offsets[idx] + threadIdx.x;
+	if (slot >= n) return;
+	const long dst = (long)frame_offset[frame0 + blockIdx.y] + offsets[idx] + slot;
 	if (dst >= pool.cap) return;      // counted, not stored: the host reports BS_ERR_CAPACITY
-	const RawPoint p = stage[idx * NMS_CTA_BLOCKS + threadIdx.x];
+	const RawPoint p = stage[idx * NMS_CTA_BLOCKS + slot];
 	pool.xy[2 * dst] = p.x; pool.xy[2 * dst + 1] = p.y;
 	pool.scale[dst] = p.scale;
 	pool.meta[4 * dst] = p.octave; pool.meta[4 * dst + 1] = p.level; pool.meta[4 * dst + 2] = p.px; pool.meta[4 * dst + 3] = p.py;
@@ -375,7 +390,7 @@ void launch_compact(const Plan& plan, int batch, int frame0, const RawPoint* d_s
 	BS_LAUNCH(scan_counts_kernel, batch, SCAN_THREADS, 0, st, d_cta_counts, plan.ctas_per_frame, d_cta_offsets, d_frame_total);
 	BS_LAUNCH(frame_offsets_kernel, 1, 32, 0, st, (const int*)d_frame_total, batch, frame0, d_frame_offset);
 	if (plan.ctas_per_frame == 0) return;
-	BS_LAUNCH(gather_points_kernel, dim3(plan.ctas_per_frame, batch), NMS_CTA_BLOCKS, 0, st, d_stage, d_cta_counts, (const int*)d_cta_offsets,
+	BS_LAUNCH(gather_points_kernel, dim3(div_up(plan.ctas_per_frame, GATHER_THREADS / NMS_CTA_BLOCKS), batch), GATHER_THREADS, 0, st, d_stage, d_cta_counts, (const int*)d_cta_offsets,
 	          (const int*)d_frame_offset, plan.ctas_per_frame, frame0, pool);
 }
 
