@@ -43,18 +43,21 @@ __device__ __forceinline__ T box_zero(const T* __restrict__ ii, int W, int H, in
 // (SparseGradientSafe.compute, main/boofcv-types/src/main/java/boofcv/struct/sparse/SparseGradientSafe.java:56-61).
 // The reference also has an unchecked path that it only takes after SurfDescribeOps.isInside proved every sample is
 // inside; the check is kept here on both paths because a GPU thread must never read outside the allocation.
+// Index arithmetic is 32-bit on purpose (one IMAD.WIDE per load instead of 64-bit multiplies and adds: ncu's source page
+// had the address code at 12 % of describe_kernel's instructions): W*H < 2^31 is checked where the image enters the library.
 template <typename T>
 __device__ __forceinline__ void sparse_gradient(const T* __restrict__ ii, int W, int H, int r, int x, int y, T& dx, T& dy) {
-	if (x - r - 1 < 0 || y - r - 1 < 0 || x + r >= W || y + r >= H) { dx = 0; dy = 0; return; }
+	const int x0 = x - r - 1, y0 = y - r - 1;
+	if ((x0 | y0) < 0 || x + r >= W || y + r >= H) { dx = 0; dy = 0; return; }
 	const int w = 2 * r + 1;
-	const T* a = ii + (long)(y - r - 1) * W + (x - r - 1);
-	const T* b = a + (long)r * W;
-	const T* c = b + W;
-	const T* d = c + (long)r * W;
-	const T p0 = __ldg(a), p1 = __ldg(a + r), p2 = __ldg(a + r + 1), p3 = __ldg(a + w);
-	const T p11 = __ldg(b), p4 = __ldg(b + w);
-	const T p10 = __ldg(c), p5 = __ldg(c + w);
-	const T p9 = __ldg(d), p8 = __ldg(d + r), p7 = __ldg(d + r + 1), p6 = __ldg(d + w);
+	const int a = y0 * W + x0;
+	const int b = a + r * W;
+	const int c = b + W;
+	const int d = c + r * W;
+	const T p0 = __ldg(ii + a), p1 = __ldg(ii + (a + r)), p2 = __ldg(ii + (a + r + 1)), p3 = __ldg(ii + (a + w));
+	const T p11 = __ldg(ii + b), p4 = __ldg(ii + (b + w));
+	const T p10 = __ldg(ii + c), p5 = __ldg(ii + (c + w));
+	const T p9 = __ldg(ii + d), p8 = __ldg(ii + (d + r)), p7 = __ldg(ii + (d + r + 1)), p6 = __ldg(ii + (d + w));
 	const T left = Arith<T>::sum4(p8, p9, p1, p0);
 	const T right = Arith<T>::sum4(p6, p7, p3, p2);
 	const T top = Arith<T>::sum4(p4, p11, p3, p0);

@@ -800,6 +800,7 @@ void check_device(int device) {
 // upload a dense integral image of either type
 void upload_ii(DevBuf& d, const void* ii, int width, int height) {
 	if (!ii || width <= 0 || height <= 0) fail(BS_ERR_ARG, "bad integral image");
+	if ((long)width * height >= (1L << 31)) fail(BS_ERR_ARG, "integral image of 2^31 pixels or more (the sample kernels index it with 32-bit offsets)");
 	d.reserve((size_t)width * height * 4);
 	h2d_sync(d.p, ii, (size_t)width * height * 4);
 }

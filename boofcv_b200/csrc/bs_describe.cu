@@ -51,11 +51,13 @@ __device__ __forceinline__ double angle_dist(double a, double b) {
 // sampling geometry of one feature, computed once per feature
 struct OriGeo {
 	int r, sw;
+	float inv_sw;                  // (k + 0.5f) * inv_sw truncates to k / sw for every k of the grid (never within 1/(2 sw) of an integer)
 	double period, tl_x, tl_y;
 };
 __device__ __forceinline__ OriGeo ori_geometry(const DescribeParams& P, double c_x, double c_y, double ptScale) {
 	OriGeo g;
 	g.sw = 2 * P.ori_radius + 1;
+	g.inv_sw = 1.0f / (float)g.sw;
 	// setObjectRadius(scale*BoofDefaults.SURF_SCALE_TO_RADIUS): scale = radius*objectRadiusToScale; kernel width = scale*sampleWidth
 	const double sc = (ptScale * P.ori_object_radius_mult) * P.ori_radius_to_scale;
 	g.r = gradient_radius(sc * P.ori_sample_width);
@@ -71,7 +73,7 @@ template <typename T>
 __device__ __forceinline__ void orientation_sample(const T* __restrict__ ii, int W, int H, const DescribeParams& P,
                                                    const double* __restrict__ wts, const OriGeo& g, int k, double* dX, double* dY,
                                                    double* ang) {
-	const int y = k / g.sw, x = k - y * g.sw;
+	const int y = (int)(((float)k + 0.5f) * g.inv_sw), x = k - y * g.sw;
 	const int py = (int)(g.tl_y + y * g.period);
 	const int px = (int)(g.tl_x + x * g.period);
 	T gdx, gdy;
@@ -217,6 +219,7 @@ __device__ __forceinline__ bool laplace_sign(const T* __restrict__ ii, int W, in
 // sample grid of the descriptor (DescribePointSurfMod samples the overlap once)
 struct DescGeo {
 	int r, regionR, ov, G;
+	float inv_G;                   // (k + 0.5f) * inv_G truncates to k / G
 	double c_x, c_y;
 };
 __device__ __forceinline__ DescGeo desc_geometry(const DescribeParams& P, double x, double y, double scale) {
@@ -226,6 +229,7 @@ __device__ __forceinline__ DescGeo desc_geometry(const DescribeParams& P, double
 	g.regionR = regionSize / 2;
 	g.ov = P.variant == 1 ? P.overlap : 0;
 	g.G = regionSize + 2 * g.ov;
+	g.inv_G = 1.0f / (float)g.G;
 	g.c_x = x + 0.5; g.c_y = y + 0.5;
 	return g;
 }
@@ -239,7 +243,7 @@ __device__ __forceinline__ void desc_pixel(const DescGeo& g, double c, double s,
 template <typename T>
 __device__ __forceinline__ void describe_sample(const T* __restrict__ ii, int W, int H, const DescGeo& g, double c, double s, double scale,
                                                 int k, T* gx, T* gy) {
-	const int gyi = k / g.G, gxi = k - gyi * g.G;
+	const int gyi = (int)(((float)k + 0.5f) * g.inv_G), gxi = k - gyi * g.G;
 	int pixelX, pixelY;
 	desc_pixel(g, c, s, scale, gxi, gyi, pixelX, pixelY);
 	T dx, dy;
@@ -308,6 +312,7 @@ struct Slot {                      // one feature of the round (shared memory)
 	double x, y, scale, angle, c, s;
 	long f;                        // pool index, -1: none
 	int frame;                     // frame index relative to the first frame of the launch
+	const void* ii;                // that frame's integral image
 	int bin;                       // orientation bin of the descriptor's sample visiting order
 	OriGeo og;
 	DescGeo dg;
@@ -377,6 +382,7 @@ describe_kernel(const T* __restrict__ ii_all, int W, int H, DescribeParams P, De
 			if (f < end) {
 				me.x = pool.xy[2 * f]; me.y = pool.xy[2 * f + 1]; me.scale = pool.scale[f];
 				me.frame = pool.frame[f] - frame0;
+				me.ii = ii_all + me.frame * frame_words;
 				if (do_orientation) me.og = ori_geometry(P, me.x, me.y, me.scale);
 				else me.angle = pool.angle[f];
 				if (do_describe) me.dg = desc_geometry(P, me.x, me.y, me.scale);
@@ -389,7 +395,7 @@ describe_kernel(const T* __restrict__ ii_all, int W, int H, DescribeParams P, De
 				const Slot& sj = slots[j];
 				double* dX = reinterpret_cast<double*>(scratch + (size_t)j * S.per_warp);
 				double* dY = dX + S.ori_n;
-				orientation_sample(ii_all + sj.frame * frame_words, W, H, P, t_ori, sj.og, k, dX, dY, dY + S.ori_n);
+				orientation_sample(static_cast<const T*>(sj.ii), W, H, P, t_ori, sj.og, k, dX, dY, dY + S.ori_n);
 			}
 			__syncthreads();
 			if (P.ori_variant == 0) {
@@ -470,13 +476,13 @@ describe_kernel(const T* __restrict__ ii_all, int W, int H, DescribeParams P, De
 				const Slot& sj = slots[j];
 				const int k = __ldg(tabs.d_perm + sj.bin * S.desc_g2 + (idx - j * S.desc_g2));
 				T* gx = reinterpret_cast<T*>(scratch + (size_t)j * S.per_warp + (size_t)P.dof * 8);
-				describe_sample(ii_all + sj.frame * frame_words, W, H, sj.dg, sj.c, sj.s, sj.scale, k, gx, gx + S.desc_g2);
+				describe_sample(static_cast<const T*>(sj.ii), W, H, sj.dg, sj.c, sj.s, sj.scale, k, gx, gx + S.desc_g2);
 			}
 			__syncthreads();
 			if (me.f >= 0) {
 				double* feat = reinterpret_cast<double*>(mine);
 				const T* gx = reinterpret_cast<const T*>(feat + P.dof);
-				describe_reduce(ii_all + me.frame * frame_words, W, H, P, t_w, t_wgrid, me.x, me.y, me.c, me.s, me.scale, gx, gx + S.desc_g2, feat,
+				describe_reduce(static_cast<const T*>(me.ii), W, H, P, t_w, t_wgrid, me.x, me.y, me.c, me.s, me.scale, gx, gx + S.desc_g2, feat,
 				                pool.desc + me.f * P.out_stride + P.out_offset, pool.white + me.f);
 			}
 		}
