@@ -89,6 +89,7 @@ SIGNATURES = {
     "bs_assoc_validate_device": (_i, [_vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp]),
     "bs_assoc_matches": (_i, [_vp, _vp, _i, _i, _vp, _vp, _vp, _pi, _vp, _pi, _vp, _pi]),
     "bs_assoc_frames_device": (_i, [_vp, _vp, _i, _i, _i, _vp, _vp, _vp]),
+    "bs_assoc_frames_batch_device": (_i, [_vp, _vp, _i, _vp, _vp, _vp, _vp, _l, _vp, _vp]),
     "bs_assoc_surf_run": (_i, [_vp, _vp, _vp, _i, _vp, _vp, _i, _i, _vp, _vp]),
     "bs_assoc_surf_run_device": (_i, [_vp, _vp, _vp, _i, _vp, _vp, _i, _i, _vp, _vp, _vp]),
     "bs_assoc_surf_matches": (_i, [_vp, _vp, _vp, _i, _i, _vp, _vp, _vp, _pi, _vp, _pi, _vp, _pi]),

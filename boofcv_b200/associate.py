@@ -61,7 +61,11 @@ class AssociateGreedyGPU:
             N.lib().bs_assoc_destroy(self._h)
             self._h = C.c_void_p()
 
-    __del__ = close
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:      # interpreter shutdown: the module globals may already be gone
+            pass
 
     def setSource(self, listSrc):
         self._src = _as_matrix(listSrc)
@@ -143,6 +147,24 @@ class AssociateGreedyGPU:
         N.check(N.lib().bs_assoc_frames_device(self._h, det._h, int(frameSrc), int(frameDst), int(bool(surfBasic)),
                                                C.c_void_p(pairs.data_ptr()), C.c_void_p(fit.data_ptr()), C.c_void_p(st)))
         return pairs, fit
+
+    def associateFramesBatch(self, det, framesSrc, framesDst, stream=None):
+        """associateFrames for a list of frame pairs of `det`'s last batch in one call (bs_assoc_frames_batch_device: the pairs
+        are queued back to back, one host synchronisation at the end).  Returns (pairs int32[total], fit float64[total],
+        offsets int64[len+1]): the results of pair k are [offsets[k], offsets[k+1])."""
+        import torch
+        fs = np.ascontiguousarray(framesSrc, dtype=np.int32); fd = np.ascontiguousarray(framesDst, dtype=np.int32)
+        if fs.shape != fd.shape or fs.ndim != 1:
+            raise ValueError("framesSrc and framesDst must be two lists of the same length")
+        total = int(sum(det.countFrame(int(f)) for f in fs))
+        dev = torch.device("cuda", self.device)
+        pairs = torch.empty(total, dtype=torch.int32, device=dev); fit = torch.empty(total, dtype=torch.float64, device=dev)
+        offsets = np.zeros(len(fs) + 1, np.int64)
+        st = (stream if stream is not None else torch.cuda.current_stream(dev).cuda_stream) or 1
+        N.check(N.lib().bs_assoc_frames_batch_device(self._h, det._h, len(fs), fs.ctypes.data_as(C.c_void_p), fd.ctypes.data_as(C.c_void_p),
+                                                     C.c_void_p(pairs.data_ptr()), C.c_void_p(fit.data_ptr()), total,
+                                                     offsets.ctypes.data_as(C.c_void_p), C.c_void_p(st)))
+        return pairs, fit, offsets
 
     # device-resident variant (torch float64 tensors [n,dof], [m,dof]); returns (pairs int32[n], fit float64[n]) tensors
     def associateDevice(self, src, dst, stream=None):

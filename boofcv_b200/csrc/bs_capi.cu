@@ -1127,11 +1127,20 @@ struct bs_assoc {
 		tc_runs++;
 		return h_overflow == 0;
 	}
-	// tensor-core filter + exact re-score; false if a candidate list overflowed (results then invalid).  Synchronises `st`.
-	bool run_tc(const double* src, int n, const double* dst, int m, int32_t* pairs, double* fit, cudaStream_t st) {
+	// workspace of the tensor-core path for problems up to n x m (so that queued runs never reallocate under a running kernel)
+	void tc_reserve(int n, int m) {
+		op_src.reserve(tc_operand_bytes(n)); op_dst.reserve(tc_operand_bytes(m));
+		norm_src.reserve((size_t)tc_pad_rows(n) * 4); norm_dst.reserve((size_t)tc_pad_rows(m) * 4);
+		tc_scalars.reserve(16);
+		const size_t rows = (size_t)std::max(n, m);
+		cand_count.reserve(rows * 4); cand.reserve(rows * tc_cand_cap() * 4);
+		col_min.reserve((size_t)m * 8); col_first.reserve((size_t)m * 4); col_last.reserve((size_t)m * 4);
+	}
+	// tensor-core filter + exact re-score, queued on `st` without a host round trip; *overflow (device, zeroed by the caller)
+	// becomes non-zero if a candidate list overflowed (results then invalid)
+	void queue_tc(const double* src, int n, const double* dst, int m, int32_t* pairs, double* fit, int* overflow, cudaStream_t st) {
 		tc_prepare(src, n, dst, m, st);
 		unsigned* sc = tc_scalars.as<unsigned>();
-		int* overflow = reinterpret_cast<int*>(sc + 2);
 		launch_tc_filter(op_src.p, norm_src.as<float>(), n, op_dst.p, norm_dst.as<float>(), sc + 1, m, cand_count.as<int>(), cand.as<int>(),
 		                 nullptr, sm_count, st);
 		launch_tc_rescore(src, n, dst, cand_count.as<int>(), cand.as<int>(), 0, max_fit, 0, pairs, fit, nullptr, nullptr, nullptr, overflow, st);
@@ -1143,12 +1152,19 @@ struct bs_assoc {
 			                  col_first.as<int32_t>(), col_last.as<int32_t>(), overflow, st);
 			launch_validate(n, 0, pairs, fit, col_min.as<double>(), col_first.as<int32_t>(), col_last.as<int32_t>(), st);
 		}
+		tc_runs++;
+	}
+	// the same, synchronising `st`; false if a candidate list overflowed
+	bool run_tc(const double* src, int n, const double* dst, int m, int32_t* pairs, double* fit, cudaStream_t st) {
+		tc_scalars.reserve(16);
+		int* overflow = reinterpret_cast<int*>(tc_scalars.as<unsigned>() + 2);    // zeroed by tc_prepare
+		queue_tc(src, n, dst, m, pairs, fit, overflow, st);
 		int h_overflow = 0;
 		BS_CUDA(cudaMemcpyAsync(&h_overflow, overflow, 4, cudaMemcpyDeviceToHost, st));
 		BS_CUDA(cudaStreamSynchronize(st));
-		tc_runs++;
 		return h_overflow == 0;
 	}
+	DevBuf batch_flags;
 };
 
 extern "C" {
@@ -1176,7 +1192,7 @@ int bs_assoc_destroy(bs_assoc* a) {
 		a->col_min.release(); a->col_first.release(); a->col_last.release();
 		a->d_src.release(); a->d_dst.release(); a->d_pairs.release(); a->d_fit.release();
 		a->op_src.release(); a->op_dst.release(); a->norm_src.release(); a->norm_dst.release(); a->tc_scalars.release();
-		a->cand_count.release(); a->cand.release();
+		a->cand_count.release(); a->cand.release(); a->batch_flags.release();
 		a->sb_idx_src.release(); a->sb_idx_dst.release(); a->sb_counts.release(); a->sb_src.release(); a->sb_dst.release();
 		a->sb_pairs.release(); a->sb_fit.release(); a->sb_white_src.release(); a->sb_white_dst.release();
 		if (a->stream) cudaStreamDestroy(a->stream);
@@ -1347,6 +1363,60 @@ int bs_assoc_frames_device(bs_assoc* a, bs_surf* s, int frame_src, int frame_dst
 		const double* dst = p.desc + (long)fo[frame_dst] * dof;
 		if (surf_basic) a->run_surf_basic(src, p.white + fo[frame_src], n, dst, p.white + fo[frame_dst], m, dof, d_pairs, d_fit, st);
 		else a->run(src, n, dst, m, dof, d_pairs, d_fit, st);
+	});
+}
+
+int bs_assoc_frames_batch_device(bs_assoc* a, bs_surf* s, int n_pairs, const int32_t* frame_src, const int32_t* frame_dst,
+                                 int32_t* d_pairs, double* d_fit, long cap, long* offsets, void* stream) {
+	return guarded([&] {
+		if (!a || !s) fail(BS_ERR_ARG, "handle is null");
+		if (a->device != s->device) fail(BS_ERR_ARG, "detector and associator live on different devices");
+		if (n_pairs < 0 || (n_pairs > 0 && (!frame_src || !frame_dst)) || !offsets) fail(BS_ERR_ARG, "bad pair list");
+		DeviceGuard g(a->device);
+		check_ready(s);
+		const std::vector<int>& fo = s->h_frame_offset;
+		if (fo[s->batch] > s->pool.view.cap) fail(BS_ERR_CAPACITY, "feature pool too small for this batch");
+		int max_n = 0, max_m = 0;
+		offsets[0] = 0;
+		for (int k = 0; k < n_pairs; k++) {
+			if (frame_src[k] < 0 || frame_src[k] >= s->batch || frame_dst[k] < 0 || frame_dst[k] >= s->batch) fail(BS_ERR_ARG, "frame out of range");
+			const int n = fo[frame_src[k] + 1] - fo[frame_src[k]], m = fo[frame_dst[k] + 1] - fo[frame_dst[k]];
+			offsets[k + 1] = offsets[k] + n;
+			max_n = std::max(max_n, n); max_m = std::max(max_m, m);
+		}
+		if (offsets[n_pairs] > cap) fail(BS_ERR_CAPACITY, "pairs / fit arrays smaller than the source features of the batch");
+		if (offsets[n_pairs] == 0) return;
+		if (!d_pairs || !d_fit) fail(BS_ERR_ARG, "null argument");
+		const Pool& p = s->pool.view;
+		const int dof = s->out_dof();
+		cudaStream_t st = stream ? static_cast<cudaStream_t>(stream) : a->stream;
+		a->batch_flags.reserve((size_t)n_pairs * 4);
+		BS_CUDA(cudaMemsetAsync(a->batch_flags.p, 0, (size_t)n_pairs * 4, st));
+		if (tc_supported(dof)) a->tc_reserve(max_n, std::max(max_m, 1));
+		std::vector<char> queued(n_pairs, 0);
+		for (int k = 0; k < n_pairs; k++) {
+			const int n = fo[frame_src[k] + 1] - fo[frame_src[k]], m = fo[frame_dst[k] + 1] - fo[frame_dst[k]];
+			if (n == 0) continue;
+			const double* src = p.desc + (long)fo[frame_src[k]] * dof;
+			const double* dst = p.desc + (long)fo[frame_dst[k]] * dof;
+			const bool want_tc = m > 0 && tc_supported(dof) && (a->mode == 1 || (a->mode == -1 && (long)n * m >= (1L << 22)));
+			if (want_tc) {
+				a->queue_tc(src, n, dst, m, d_pairs + offsets[k], d_fit + offsets[k], a->batch_flags.as<int>() + k, st);
+				queued[k] = 1;
+			} else {
+				a->run(src, n, dst, m, dof, d_pairs + offsets[k], d_fit + offsets[k], st);
+			}
+		}
+		std::vector<int> flags(n_pairs, 0);
+		BS_CUDA(cudaMemcpyAsync(flags.data(), a->batch_flags.p, (size_t)n_pairs * 4, cudaMemcpyDeviceToHost, st));
+		BS_CUDA(cudaStreamSynchronize(st));
+		for (int k = 0; k < n_pairs; k++)
+			if (queued[k] && flags[k] != 0) {        // a row had more candidates than the list holds: redo this pair exactly
+				const int n = fo[frame_src[k] + 1] - fo[frame_src[k]], m = fo[frame_dst[k] + 1] - fo[frame_dst[k]];
+				a->tc_fallbacks++;
+				a->run_exact(p.desc + (long)fo[frame_src[k]] * dof, n, p.desc + (long)fo[frame_dst[k]] * dof, m, dof, d_pairs + offsets[k],
+				             d_fit + offsets[k], st);
+			}
 	});
 }
 

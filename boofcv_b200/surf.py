@@ -138,7 +138,11 @@ class HostFeatureBuffers:
             N.lib().bs_host_unregister(C.c_void_p(a.ctypes.data))
         self._pinned = []
 
-    __del__ = close
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:      # interpreter shutdown: the module globals may already be gone
+            pass
 
 
 class DetectDescribeSurf:
@@ -164,7 +168,11 @@ class DetectDescribeSurf:
             N.lib().bs_surf_destroy(self._h)
             self._h = C.c_void_p()
 
-    __del__ = close
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:      # interpreter shutdown: the module globals may already be gone
+            pass
 
     def setWorkspace(self, chunkFrames=0, poolFeatures=0):
         N.check(N.lib().bs_surf_set_workspace(self._h, chunkFrames, poolFeatures))

@@ -262,6 +262,14 @@ int bs_assoc_run_device(bs_assoc* a, const double* d_src, int n, const double* d
 int bs_assoc_frames_device(bs_assoc* a, bs_surf* s, int frame_src, int frame_dst, int surf_basic, int32_t* d_pairs,
                            double* d_fit, void* stream);
 
+/* The same for a list of frame pairs of the last batch (a stereo stream: pair k = frames 2k, 2k+1), queued back to back on
+ * `stream` with ONE host synchronisation at the end instead of one per pair.  offsets[n_pairs+1] (host, written by the
+ * call): the results of pair k are d_pairs / d_fit [offsets[k], offsets[k+1]), offsets[k+1]-offsets[k] = the number of
+ * features of frame_src[k].  cap = entries d_pairs / d_fit hold; BS_ERR_CAPACITY if the batch needs more.  Plain greedy
+ * association only (AssociateGreedy); results are those of n_pairs bs_assoc_frames_device calls. */
+int bs_assoc_frames_batch_device(bs_assoc* a, bs_surf* s, int n_pairs, const int32_t* frame_src, const int32_t* frame_dst,
+                                 int32_t* d_pairs, double* d_fit, long cap, long* offsets, void* stream);
+
 /* Sharded association: the src rows of one rank against ALL dst rows.
  * Step 1 (bs_assoc_forward_device): forward pass for the local rows + per-column partial minima over the local rows:
  *   d_col_min[m] (score), d_col_first[m], d_col_last[m] (GLOBAL row index = row_offset + local row; -1 if none).

@@ -418,3 +418,33 @@ def test_associate_frames_on_device(bs, orc, surf_basic):
             assert np.array_equal(p.cpu().numpy(), pairs) and np.array_equal(f.cpu().numpy(), fit)
             if fa < 3:
                 assert (pairs >= 0).sum() > 10
+
+
+@pytest.mark.parametrize("mode", [-1, 1])
+def test_associate_frame_pairs_batched(bs, orc, mode):
+    """bs_assoc_frames_batch_device: a list of frame pairs queued back to back == the same pairs one call at a time == the oracle."""
+    import torch
+    a0, b0 = shifted_pair(320, 240)
+    a1, b1 = shifted_pair(320, 240, seed=77)
+    imgs = [a0, b0, a1, b1]
+    det = bs.FactoryDetectDescribe.surfFast(None, None, None, np.float32)
+    det.detectBatch(torch.as_tensor(np.stack(imgs), device="cuda"))
+    assoc = bs.FactoryAssociation.greedy(bs.ScoreAssociateEuclideanSq_F64(), 0.1, True)
+    assoc.setMode(mode)
+    src, dst = [0, 2, 3, 1], [1, 3, 0, 1]
+    p, f, off = assoc.associateFramesBatch(det, src, dst)
+    assert off[0] == 0 and len(off) == 5 and off[-1] == p.numel() == f.numel()
+    feats = [orc.surf_fast(im) for im in imgs]
+    for k, (fa, fb) in enumerate(zip(src, dst)):
+        assert off[k + 1] - off[k] == det.countFrame(fa)
+        pk, fk = p[off[k]:off[k + 1]].cpu().numpy(), f[off[k]:off[k + 1]].cpu().numpy()
+        p1, f1 = assoc.associateFrames(det, fa, fb)
+        assert np.array_equal(pk, p1.cpu().numpy()) and np.array_equal(fk, f1.cpu().numpy())
+        pairs, fit = orc.associate(feats[fa]["desc"], feats[fb]["desc"], 0.1, True)
+        assert np.array_equal(pk, pairs) and np.array_equal(fk, fit)
+    # an empty list and a capacity that is too small
+    p, f, off = assoc.associateFramesBatch(det, [], [])
+    assert p.numel() == 0 and list(off) == [0]
+    with pytest.raises(Exception):
+        assoc.associateFramesBatch(det, [0], [9])
+    det.close(); assoc.close()

@@ -46,6 +46,8 @@ def main():
     ap.add_argument("--n4", type=int, default=100000, help="descriptors per side (config 4)")
     ap.add_argument("--pairs5", type=int, default=128, help="1080p stereo pairs per rank (config 5)")
     ap.add_argument("--only", type=int, default=0)
+    ap.add_argument("--serial5", action="store_true", help="config 5: one detector and one associator on one stream (no overlap)")
+    ap.add_argument("--per-pair-calls", action="store_true", help="config 5: one associate call (and host round trip) per pair")
     args = ap.parse_args()
     rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
     local = int(os.environ.get("LOCAL_RANK", 0))
@@ -100,20 +102,55 @@ def main():
         frames[0::2] = left[:, :, :1920]                            # right = left shifted by a disparity of 16 px
         frames[1::2] = left[:, :, 16:]
         del left
-        det = bs.FactoryDetectDescribe.surfFast(None, None, None, np.float32, device=local)
-        assoc = bs.FactoryAssociation.greedy(bs.ScoreAssociateEuclideanSq_F64(), 0.1, True, device=local)
+        # two detector / associator handles on two streams: the association of sub-batch i (tensor cores) overlaps the detection
+        # of sub-batch i+1 (shared-memory and L1 bound); the reference's interfaces allow it (independent instances)
+        dets = [bs.FactoryDetectDescribe.surfFast(None, None, None, np.float32, device=local) for _ in range(2)]
+        assocs = [bs.FactoryAssociation.greedy(bs.ScoreAssociateEuclideanSq_F64(), 0.1, True, device=local) for _ in range(2)]
+        lanes = [torch.cuda.Stream(device=dev) for _ in range(2)]
+        det, assoc = dets[0], assocs[0]
         sub = 32                                                    # pairs per detect call: association of one sub-batch follows it
 
-        def stream():
+        def stream_pipelined():
+            matched = 0
+            cur = torch.cuda.current_stream(dev)
+            for l in lanes:
+                l.wait_stream(cur)
+            starts = list(range(0, P, sub))
+
+            def detect(i):
+                p0 = starts[i]
+                dets[i % 2].detectBatch(frames[2 * p0:2 * min(p0 + sub, P)], stream=lanes[i % 2].cuda_stream)
+
+            detect(0)
+            for i, p0 in enumerate(starts):
+                if i + 1 < len(starts):
+                    detect(i + 1)                                   # queued before the host waits for sub-batch i
+                k = min(sub, P - p0)
+                pairs, _, off = assocs[i % 2].associateFramesBatch(dets[i % 2], np.arange(0, 2 * k, 2), np.arange(1, 2 * k, 2),
+                                                                   stream=lanes[i % 2].cuda_stream)
+                if p0 == 0:
+                    matched = int((pairs[:off[1]] >= 0).sum().item())
+            for l in lanes:
+                cur.wait_stream(l)
+            return matched
+
+        def stream_serial():
             matched = 0
             for p0 in range(0, P, sub):
                 det.detectBatch(frames[2 * p0:2 * min(p0 + sub, P)])
-                for p in range(min(sub, P - p0)):
-                    pairs, _ = assoc.associateFrames(det, 2 * p, 2 * p + 1)
-                    if p == 0 and p0 == 0:
-                        matched = int((pairs >= 0).sum().item())
+                k = min(sub, P - p0)
+                if args.per_pair_calls:
+                    for p in range(k):
+                        pairs, _ = assoc.associateFrames(det, 2 * p, 2 * p + 1)
+                        if p == 0 and p0 == 0:
+                            matched = int((pairs >= 0).sum().item())
+                else:                                               # one call per sub-batch: pairs queued back to back on the device
+                    pairs, _, off = assoc.associateFramesBatch(det, np.arange(0, 2 * k, 2), np.arange(1, 2 * k, 2))
+                    if p0 == 0:
+                        matched = int((pairs[:off[1]] >= 0).sum().item())
             return matched
 
+        stream = stream_serial if (args.per_pair_calls or args.serial5) else stream_pipelined
         ms, matched = timed(stream, dev, world)
         say({"config": 5, "workload": "stereo stream: %d x (2 x 1920x1080) per GPU, surfFast x2 + greedy(backward) per pair, device resident" % P,
              "n_gpus": world, "pairs_per_s": world * P / (ms / 1e3), "frames_per_s": 2 * world * P / (ms / 1e3), "ms": ms,
