@@ -186,15 +186,26 @@ def run_gpu(args, rank, world, local_rank):
                 timing=timing, ms_single=ms_single, total_features=total_features, B=B)
 
 
-def run_e2e(g, steps):
+def det_total_of_first(g, B):
+    """features of the first B frames of the device batch (the device path's own answer for them)"""
+    det = g["det"]
+    det.detectBatch(g["frames"][:B])
+    return det.totalFeatures()
+
+
+def run_e2e(g, steps, world=1):
     """Same metric through the host-facing call (bs_surf_detect_host_batch): the step's frames live in pinned HOST memory,
     the feature lists (frame offsets, xy, scale, angle, desc, white) land in pinned HOST memory; the library overlaps the
     copies of one 32-frame sub-batch with the kernels of the other.  Returns (frames/s, h2d, d2h bytes per step)."""
-    torch, det, dev, B = g["torch"], g["det"], g["dev"], g["B"]
+    torch, det, dev = g["torch"], g["det"], g["dev"]
     from boofcv_b200 import HostFeatureBuffers
-    host = g["frames"].cpu().pin_memory()                       # the step's input lives on the host
-    cap = int(g["total_features"] * 1.1) + 4096
+    # host memory is bounded when several ranks share one box: 1024 frames are 8.5 GB of pinned input + 6 GB of pinned output per rank
+    B = g["B"] if world == 1 else min(g["B"], 256)
+    host = torch.empty((B, H, W), dtype=torch.float32, pin_memory=True)      # the step's input lives on the host
+    host.copy_(g["frames"][:B])
+    cap = int(g["total_features"] * 1.1 * B / g["B"]) + 4096
     out = HostFeatureBuffers(B, cap, 64, pinned=True)
+    expect = int(det_total_of_first(g, B))
 
     def one_step():
         det.detectHostBatch(host, out)
@@ -206,8 +217,8 @@ def run_e2e(g, steps):
     for _ in range(steps):
         h2d, d2h = one_step()                                   # synchronous: returns when the results are on the host
     dt = time.perf_counter() - t0
-    if out.total != g["total_features"]:
-        raise RuntimeError("host path found %d features, device path %d" % (out.total, g["total_features"]))
+    if out.total != expect:
+        raise RuntimeError("host path found %d features, device path %d" % (out.total, expect))
     out.close()
     return B * steps / dt, h2d, d2h
 
@@ -266,6 +277,8 @@ def main():
     import torch.distributed as dist
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
+            os.environ["NCCL_DEBUG"] = "WARN"                     # NCCL's version banner goes to stdout: keep stdout to the one JSON line
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     g = run_gpu(args, rank, world, local_rank)
     dev = g["dev"]
@@ -280,12 +293,12 @@ def main():
 
     e2e = None
     if not args.no_e2e:
-        fps, h2d, d2h = run_e2e(g, max(1, min(args.steps, 2)))
+        fps, h2d, d2h = run_e2e(g, max(1, min(args.steps, 2)), world)
         t = torch.tensor([fps], device=dev, dtype=torch.float64)
         if world > 1:
             dist.all_reduce(t, op=dist.ReduceOp.MIN)          # slowest rank bounds the job
         e2e = {"value": float(t.item()) * world, "unit": UNIT, "h2d_bytes_per_step": int(h2d) * world,
-               "d2h_bytes_per_step": int(d2h) * world}
+               "d2h_bytes_per_step": int(d2h) * world, "batch_per_gpu": B if world == 1 else min(B, 256)}
 
     if rank == 0:
         pk, pk_kind = peaks()
@@ -335,7 +348,7 @@ def main():
                 out["association"] = run_association(g["torch"], dev)
             except Exception as ex:                              # never lose the headline line over the extra leg
                 out["association"] = {"error": str(ex)[:200]}
-        if not args.no_cpu:
+        if not args.no_cpu and world == 1:
             from boofcv_b200.synth import blob_image
             cores = os.cpu_count() or 1
             frames = [blob_image(W, H, 234 + i) for i in range(2)]
