@@ -266,7 +266,8 @@ void bs_surf::ensure(int w, int h, int nbatch) {
 	chunk = std::max(c, 1);
 	const size_t px = (size_t)W * H;
 	// integral group: a multiple of the chunk, about 32 frames (or ~1 GB of integral images, whichever is smaller)
-	int gframes = (int)std::max<size_t>(1, std::min<size_t>(32, ((size_t)1 << 30) / (px * 4)));
+	static const int group_cap = getenv("BS_GROUP") ? std::max(1, atoi(getenv("BS_GROUP"))) : 32;
+	int gframes = (int)std::max<size_t>(1, std::min<size_t>(group_cap, ((size_t)1 << 30) / (px * 4)));
 	gframes = std::max(chunk, (gframes / chunk) * chunk);
 	group = std::min(std::max(gframes, chunk), std::max(nbatch, 1));
 	if (group < chunk) group = chunk;
