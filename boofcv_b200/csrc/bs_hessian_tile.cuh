@@ -38,8 +38,11 @@ template <int SKIP, int S0, int STEP, int NS, int TX, int TY> struct TileGeo {
 	}
 };
 
-template <int SIZE, typename G>
-__device__ __forceinline__ float tile_response(const float* __restrict__ b) {
+// RING: the sample may belong to the reference's border ring (`ring` true), whose boxes block_zero sums as br-tr-bl+tl; only the
+// Dyy boxes differ from hessianInner's order (br-bl-tr+tl, ImplIntegralImageFeatureIntensity.java:185-186), so both sums are
+// formed from the same eight loads and selected — no divergence between ring and inner lanes of a warp.
+template <int SIZE, typename G, bool RING = false>
+__device__ __forceinline__ float tile_response(const float* __restrict__ b, bool ring = false) {
 	typedef BoxGeo<SIZE> B;
 	constexpr int bs = B::bs, bl = B::bl, rf = B::rf, rs = B::rs;
 	constexpr float norm = 1.0f / (float)(SIZE * SIZE);
@@ -50,8 +53,15 @@ __device__ __forceinline__ float tile_response(const float* __restrict__ b) {
 	Dxx -= 3.0f * (BS_T(bo, c0 + 2 * bs) - BS_T(t, c0 + 2 * bs) - BS_T(bo, c0 + bs) + BS_T(t, c0 + bs));
 	// Dyy: columns left = -rs-1, right = left+bl; rows -rf-1 + {0, bs, 2bs, 3bs}
 	constexpr int l = -rs - 1, r = l + bl, r0 = -rf - 1;
-	float Dyy = BS_T(r0 + 3 * bs, r) - BS_T(r0 + 3 * bs, l) - BS_T(r0, r) + BS_T(r0, l);
-	Dyy -= 3.0f * (BS_T(r0 + 2 * bs, r) - BS_T(r0 + 2 * bs, l) - BS_T(r0 + bs, r) + BS_T(r0 + bs, l));
+	const float a_br = BS_T(r0 + 3 * bs, r), a_bl = BS_T(r0 + 3 * bs, l), a_tr = BS_T(r0, r), a_tl = BS_T(r0, l);
+	const float b_br = BS_T(r0 + 2 * bs, r), b_bl = BS_T(r0 + 2 * bs, l), b_tr = BS_T(r0 + bs, r), b_tl = BS_T(r0 + bs, l);
+	float Dyy = a_br - a_bl - a_tr + a_tl;
+	Dyy -= 3.0f * (b_br - b_bl - b_tr + b_tl);
+	if (RING) {
+		float Dyy_ring = a_br - a_tr - a_bl + a_tl;
+		Dyy_ring -= 3.0f * (b_br - b_tr - b_bl + b_tl);
+		Dyy = ring ? Dyy_ring : Dyy;
+	}
 	// Dxy: rows y1 = -bs-1, y2 = -1, y3 = 0, y4 = bs; columns -bs-1 + {0, bs, bs+1, 2bs+1}
 	constexpr int y1 = -bs - 1, y2 = -1, y3 = 0, y4 = bs, x0 = -bs - 1, x1 = x0 + bs, x3 = x0 + bs + 1, x4 = x3 + bs;
 	float Dxy = BS_T(y2, x1) - BS_T(y1, x1) - BS_T(y2, x0) + BS_T(y1, x0);
@@ -221,8 +231,15 @@ struct TmaLayers {
 		constexpr int border = InnerBorder<SIZE, SKIP>::value;
 		const Layer& L = layers[I];
 		float v;
-		if (EDGE && !(x >= border && x < L.w - border && y >= border && y < L.h - border)) v = tile_clamped_response<G, SKIP>(tile, SIZE, cr, cc, rmax, cmax);
-		else v = tile_response<SIZE, G>(base);
+		if (EDGE) {
+			// ring samples whose boxes stay left of / above the last column / row need no clamp: TMA's zero fill is block_zero's
+			// zero, only the summation order is the ring's; the clamped path is left to the right / bottom edge
+			const bool ring = !(x >= border && x < L.w - border && y >= border && y < L.h - border);
+			if (cc + SIZE / 2 > cmax || cr + SIZE / 2 > rmax) v = tile_clamped_response<G, SKIP>(tile, SIZE, cr, cc, rmax, cmax);
+			else v = tile_response<SIZE, G, true>(base, ring);
+		} else {
+			v = tile_response<SIZE, G>(base);
+		}
 		inten[L.offset + (long)y * L.w + x] = v;
 		TmaLayers<G, SKIP, S0, STEP, NS, I + 1, EDGE>::run(base, tile, cr, cc, rmax, cmax, layers, inten, x, y);
 	}
