@@ -226,7 +226,7 @@ static __device__ __noinline__ float tile_clamped_response(const float* __restri
 template <typename G, int SKIP, int S0, int STEP, int NS, int I, bool EDGE>
 struct TmaLayers {
 	static __device__ __forceinline__ void run(const float* __restrict__ base, const float* __restrict__ tile, int cr, int cc, int rmax, int cmax,
-	                                           const Layer* __restrict__ layers, float* __restrict__ inten, int x, int y) {
+	                                           const Layer* __restrict__ layers, float* __restrict__ inten, int x, int y, int at) {
 		constexpr int SIZE = S0 + I * STEP;
 		constexpr int border = InnerBorder<SIZE, SKIP>::value;
 		const Layer& L = layers[I];
@@ -240,13 +240,13 @@ struct TmaLayers {
 		} else {
 			v = tile_response<SIZE, G>(base);
 		}
-		inten[L.offset + (long)y * L.w + x] = v;
-		TmaLayers<G, SKIP, S0, STEP, NS, I + 1, EDGE>::run(base, tile, cr, cc, rmax, cmax, layers, inten, x, y);
+		(inten + L.offset)[at] = v;                // at = y * w + x: every layer of an octave has the same dimensions
+		TmaLayers<G, SKIP, S0, STEP, NS, I + 1, EDGE>::run(base, tile, cr, cc, rmax, cmax, layers, inten, x, y, at);
 	}
 };
 template <typename G, int SKIP, int S0, int STEP, int NS, bool EDGE>
 struct TmaLayers<G, SKIP, S0, STEP, NS, NS, EDGE> {
-	static __device__ __forceinline__ void run(const float*, const float*, int, int, int, int, const Layer*, float*, int, int) {}
+	static __device__ __forceinline__ void run(const float*, const float*, int, int, int, int, const Layer*, float*, int, int, int) {}
 };
 
 template <int SKIP, int S0, int STEP, int NS, int TX, int TY, int THREADS>
@@ -266,8 +266,9 @@ hessian_tma_kernel(const __grid_constant__ CUtensorMap tm, const float* __restri
 	}
 	__syncthreads();
 	auto issue = [=](long item, int b) {           // thread 0 only: TMA of work item `item` into TMA buffer b
-		const int frame = (int)(item / per_frame), t = (int)(item - (long)frame * per_frame);
-		const int tyi = t / tiles_x, txi = t - tyi * tiles_x;
+		const unsigned it = (unsigned)item;        // total < 2^31 (checked by the launcher): 32-bit divisions
+		const int frame = (int)(it / (unsigned)per_frame), t = (int)(it - (unsigned)frame * (unsigned)per_frame);
+		const int tyi = (int)((unsigned)t / (unsigned)tiles_x), txi = t - tyi * tiles_x;
 		sm100::mbar_expect_tx(&full[b], G::BOX_WORDS * 4);
 		sm100::tma_load_3d(buf + b * G::BUF, tmap, txi * TX * SKIP - G::HALO_X, tyi * TY * SKIP - G::HALO, frame, &full[b]);
 	};
@@ -288,21 +289,22 @@ hessian_tma_kernel(const __grid_constant__ CUtensorMap tm, const float* __restri
 			// TMA buffer = buf, planes = buf + BUF
 			sm100::mbar_wait(&full[0], n & 1);
 			float* planes = buf + G::BUF;
-			const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-			for (int r = warp; r < G::TH; r += THREADS / 32) {
-				const float2* src = reinterpret_cast<const float2*>(buf + r * G::BOXW);
-				for (int j = lane; j < G::PW; j += 32) {
-					const float2 v = src[j];
-					planes[r * G::PW + j] = v.x;
-					planes[G::PLANE + r * G::PW + j] = v.y;
-				}
+			// BOXW = 2 PW: float2 i of the TMA buffer holds columns (2j, 2j+1) of row r with i = r PW + j, which is also the
+			// element's place inside either plane — the de-interleave is a flat copy
+			const float2* src = reinterpret_cast<const float2*>(buf);
+#pragma unroll 4
+			for (int i = threadIdx.x; i < G::PLANE; i += THREADS) {
+				const float2 v = src[i];
+				planes[i] = v.x;
+				planes[G::PLANE + i] = v.y;
 			}
 			__syncthreads();                       // TMA buffer drained, planes complete
 			if (threadIdx.x == 0 && item + gridDim.x < total) issue(item + gridDim.x, 0);
 			tile = planes;
 		}
-		const int frame = (int)(item / per_frame), t = (int)(item - (long)frame * per_frame);
-		const int tyi = t / tiles_x, txi = t - tyi * tiles_x;
+		const unsigned it = (unsigned)item;
+		const int frame = (int)(it / (unsigned)per_frame), t = (int)(it - (unsigned)frame * (unsigned)per_frame);
+		const int tyi = (int)((unsigned)t / (unsigned)tiles_x), txi = t - tyi * tiles_x;
 		float* inten = inten_all + (long)frame * inten_per_frame;
 		const int x = txi * TX + tx;
 		// tile row / column of the image's last row / column; edge tile = it reaches into the widest border ring of the octave
@@ -315,14 +317,14 @@ hessian_tma_kernel(const __grid_constant__ CUtensorMap tm, const float* __restri
 #pragma unroll 1
 				for (int ty = ty0; ty < TY; ty += ROWS_PER_PASS) {
 					const int y = tyi * TY + ty;
-					if (y < h) TmaLayers<G, SKIP, S0, STEP, NS, 0, false>::run(tile + ty * SKIP * ROWP + tx, tile, 0, 0, 0, 0, oct.l, inten, x, y);
+					if (y < h) TmaLayers<G, SKIP, S0, STEP, NS, 0, false>::run(tile + ty * SKIP * ROWP + tx, tile, 0, 0, 0, 0, oct.l, inten, x, y, y * w + x);
 				}
 			} else {
 #pragma unroll 1
 				for (int ty = ty0; ty < TY; ty += ROWS_PER_PASS) {
 					const int y = tyi * TY + ty;
 					if (y < h) TmaLayers<G, SKIP, S0, STEP, NS, 0, true>::run(tile + ty * SKIP * ROWP + tx, tile, G::HALO + ty * SKIP, G::HALO_X + tx * SKIP,
-					                                                           rmax, cmax, oct.l, inten, x, y);
+					                                                           rmax, cmax, oct.l, inten, x, y, y * w + x);
 				}
 			}
 		}
@@ -375,6 +377,7 @@ bool launch_hessian_tma(const float* d_ii, const Plan& plan, int first_layer, fl
 	static const int per_sm_cap = getenv("BS_HT_PER_SM") ? atoi(getenv("BS_HT_PER_SM")) : 4;
 	per_sm = per_sm > per_sm_cap ? per_sm_cap : (per_sm < 1 ? 1 : per_sm);
 	const long total = (long)tiles_x * tiles_y * batch;
+	if (total >= (1L << 31)) return false;
 	const int grid = (int)std::min<long>(total, (long)sm_count * per_sm);
 	BS_LAUNCH(kern, grid, THREADS, smem, st, tm, d_ii, plan.W, plan.H, oct, tiles_x, tiles_y, batch, plan.inten_per_frame, d_inten);
 	return true;
