@@ -260,7 +260,7 @@ def main():
     ap.add_argument("--impl", default="native", choices=["native", "reference"])
     ap.add_argument("--batch", type=int, default=1024, help="1080p frames per step per GPU (BASELINE configs[1]: 1024)")
     ap.add_argument("--chunk", type=int, default=0, help="frames per kernel wave (0 = library default)")
-    ap.add_argument("--ways", type=int, default=2, help="streams a device-resident batch is spread over (1..4)")
+    ap.add_argument("--ways", type=int, default=3, help="streams a device-resident batch is spread over (1..4)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-assoc", action="store_true", help="skip the association leg (100k x 100k, rank 0)")
     ap.add_argument("--no-e2e", action="store_true")

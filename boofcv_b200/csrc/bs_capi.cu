@@ -191,7 +191,7 @@ struct bs_surf {
 		void release() { d_ii.release(); d_inten.release(); d_stage.release(); d_counts.release(); d_offsets.release(); d_keys.release(); d_keep.release(); }
 	};
 	Way ways[MAX_WAYS];
-	int n_ways = 2, ways_used = 1;
+	int n_ways = 3, ways_used = 1;
 	cudaEvent_t ev_in = nullptr;
 	DescribeSetup ds;
 	// workspace
