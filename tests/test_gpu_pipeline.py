@@ -124,6 +124,33 @@ def test_surf_device_batch_equals_single_frames(bs, orc):
     det.close()
 
 
+def test_surf_device_batch_on_several_streams(bs, orc):
+    """More frames than one integral group (32): the batch is spread over three streams that write one pool in frame order.
+    Same features as on one stream, and as the oracle finds frame by frame."""
+    from boofcv_b200.synth import blob_images_torch
+    n = 75
+    frames = blob_images_torch(200, 152, n, seed=900, device="cuda")
+    det = bs.FactoryDetectDescribe.surfFast(None, None, None, np.float32)
+    det.setWorkspace(8, 0)
+    res = {}
+    for ways in (3, 1, 4):
+        det.setWays(ways)
+        det.detectBatch(frames)
+        res[ways] = [det.readFrame(f) for f in range(n)]
+    for f in range(n):
+        for k in ("x", "y", "scale", "angle", "desc", "white"):
+            assert np.array_equal(res[3][f][k], res[1][f][k]) and np.array_equal(res[4][f][k], res[1][f][k]), (f, k)
+    host = frames.cpu().numpy()
+    for f in (0, 31, 32, 33, 74):
+        _same(res[3][f], orc.surf_fast(host[f]))
+    assert sum(len(r["x"]) for r in res[3]) == det.totalFeatures() > n
+    with pytest.raises(ValueError):                   # IllegalArgumentException on the Java side
+        det.setWays(0)
+    with pytest.raises(ValueError):
+        det.setWays(5)
+    det.close()
+
+
 def test_surf_pool_overflow_is_reported(bs):
     from boofcv_b200._native import BoofSurfError, BS_ERR_CAPACITY
     img = blob_image(320, 240, 41)
