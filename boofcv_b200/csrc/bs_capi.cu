@@ -235,9 +235,9 @@ struct bs_surf {
 	// bs_surf_detect_host_batch: workers, each with its own stream and workspace.  A lane's turn is upload -> kernels ->
 	// download in stream order; with three or more lanes the GPU always has the kernels of another turn queued while one lane
 	// uploads and one downloads (two lanes leave it idle for the difference between copy and kernel time).
-	static constexpr int MAX_LANES = 4;
-	bs_surf* lane[MAX_LANES] = {nullptr, nullptr, nullptr, nullptr};
-	int n_lanes = 4;
+	static constexpr int MAX_LANES = 6;
+	bs_surf* lane[MAX_LANES] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+	int n_lanes = 6;
 
 	int group = 0;
 	template <typename TI, typename TII>
@@ -648,7 +648,11 @@ int bs_surf_detect_host_batch(bs_surf* s, const void* pixels, long frame_stride,
 			}
 		const size_t es = elem_size(s->pixel_type);
 		const int dof = s->out_dof();
-		const int sub = 32;                        // frames per lane turn = one integral group
+		static const int sub_env = getenv("BS_HOST_SUB") ? std::max(1, atoi(getenv("BS_HOST_SUB"))) : 16;
+		// frames per lane turn.  Measured at 1080p (e2e frames/s, lanes x sub): 4x32 5354, 3x32 5352, 6x32 5184, 4x16 5269, 6x16 5544,
+		// 4x64 5157 — against a PCIe ceiling of 55.6 GB/s one way, 45.7 GB/s each way at once (tools/probe/pcie_bw.py): 8.3 MB in and
+		// 5.5 MB out per frame make the host path PCIe-bound at about 5.5 k frames/s
+		const int sub = sub_env;
 		frame_offset[0] = 0;
 		long base = 0;                             // features of the frames drained so far
 		struct Turn { int first = 0, n = 0; bool busy = false; } turn[bs_surf::MAX_LANES];
