@@ -15,7 +15,10 @@ namespace bs {
 
 constexpr int ROWS_WARPS = 2;        // warps per CTA in the row pass (32 rows each)
 constexpr int COL_THREADS = 64;      // threads per CTA in the column pass
-constexpr int COL_UNROLL = 16;       // rows per step in the column pass (one step ahead is in flight)
+#ifndef BS_COL_UNROLL
+#define BS_COL_UNROLL 32
+#endif
+constexpr int COL_UNROLL = BS_COL_UNROLL;       // rows per step in the column pass (one step ahead is in flight)
 
 template <typename TI, typename TO, typename ACC>
 __global__ void __launch_bounds__(ROWS_WARPS * 32)
