@@ -18,6 +18,7 @@
 // epilogue (one TMEM lane = one row per thread, one warp set per resident A tile).  A (2 x 128 rows) stays resident per work item, B tiles stream through a
 // 2-stage ring; two accumulator buffers in TMEM let the epilogue of tile t overlap the MMAs of tile t+1.
 #include "bs_common.cuh"
+#include <cstdlib>
 #include "bs_sm100.cuh"
 
 #include <cuda_bf16.h>
@@ -390,6 +391,8 @@ void launch_tc_filter(const void* d_opA, const float* d_normA, int nA, const voi
 	// — and as many chunks as keep all items in ONE wave of CTAs (a second, mostly empty wave costs a whole item time)
 	int chunks = sm_count / std::max(P.a_tiles256, 1);
 	chunks = std::max(1, std::min(chunks, P.b_tiles / 8 > 0 ? P.b_tiles / 8 : 1));
+	static const int env_chunks = getenv("BS_TC_CHUNKS") ? atoi(getenv("BS_TC_CHUNKS")) : 0;     // experiments
+	if (env_chunks > 0) chunks = std::min(env_chunks, std::max(P.b_tiles, 1));
 	P.tiles_per_chunk = div_up(P.b_tiles, chunks);
 	P.chunks = div_up(P.b_tiles, P.tiles_per_chunk);
 	P.norm_a = d_normA; P.norm_b = d_normB; P.max_norm_b_bits = d_max_norm_b_bits;
