@@ -275,9 +275,15 @@ def main():
 
     import torch
     import torch.distributed as dist
+    saved_stdout = None
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")   # NCCL logs (its version banner) to stdout by default: keep stdout to the one JSON line
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+        # NCCL (or the launcher's environment) prints a version banner on stdout when the first communicator comes up: everything
+        # before the result goes to stderr at the file-descriptor level, stdout carries the one JSON line
+        sys.stdout.flush()
+        saved_stdout = os.dup(1)
+        os.dup2(2, 1)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     g = run_gpu(args, rank, world, local_rank)
     dev = g["dev"]
@@ -355,7 +361,10 @@ def main():
             out["cpu_baseline"] = {"value": fps, "unit": UNIT, "cores": cores, "kind": "port",
                                    "sample": "%d x 1080p frames (same generator, seeds 234..235 cycled), surfFast, %d threads; "
                                              "C++ restatement of the reference Java (no JVM on this box)" % (n, cores)}
-        print(json.dumps(out))
+        if saved_stdout is not None:
+            sys.stdout.flush()
+            os.dup2(saved_stdout, 1)
+        print(json.dumps(out), flush=True)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
