@@ -199,8 +199,9 @@ def run_e2e(g, steps, world=1):
     copies of one 32-frame sub-batch with the kernels of the other.  Returns (frames/s, h2d, d2h bytes per step)."""
     torch, det, dev = g["torch"], g["det"], g["dev"]
     from boofcv_b200 import HostFeatureBuffers
-    # host memory is bounded when several ranks share one box: 1024 frames are 8.5 GB of pinned input + 6 GB of pinned output per rank
-    B = g["B"] if world == 1 else min(g["B"], 256)
+    # host memory is bounded when several ranks share one box: 1024 frames are 8.5 GB of pinned input + 6 GB of pinned output per
+    # rank, so the ranks of a box share 2048 frames between them
+    B = min(g["B"], max(2048 // world, 64))
     host = torch.empty((B, H, W), dtype=torch.float32, pin_memory=True)      # the step's input lives on the host
     host.copy_(g["frames"][:B])
     cap = int(g["total_features"] * 1.1 * B / g["B"]) + 4096
@@ -303,7 +304,7 @@ def main():
         if world > 1:
             dist.all_reduce(t, op=dist.ReduceOp.MIN)          # slowest rank bounds the job
         e2e = {"value": float(t.item()) * world, "unit": UNIT, "h2d_bytes_per_step": int(h2d) * world,
-               "d2h_bytes_per_step": int(d2h) * world, "batch_per_gpu": B if world == 1 else min(B, 256)}
+               "d2h_bytes_per_step": int(d2h) * world, "batch_per_gpu": min(B, max(2048 // world, 64))}
 
     if rank == 0:
         pk, pk_kind = peaks()
