@@ -105,6 +105,19 @@ constexpr int TC_PEND = 8;                // candidates an epilogue thread colle
 constexpr int TC_SMEM_BYTES = 1024 /*alignment slack*/ + 2 * TC_TILE_BYTES + TC_STAGES * TC_TILE_BYTES + 2 * TC_BN * 4 + (int)sizeof(FilterBarriers) +
                               TC_PEND * 32 * TC_EPI_WARPS * 4;
 
+// Row items that run side by side would all stream the same B tiles at the same moment (every CTA starts at the first tile of its
+// chunk): each row item walks its chunk from a different starting tile instead.  The running minimum and the candidate lists do not
+// depend on the order of the columns.
+__device__ __forceinline__ int rotated_tile(int t, int t0, int t1, int rp) {
+#ifdef BS_TC_NO_ROTATE
+	return t;
+#else
+	const int len = t1 - t0;
+	int tt = t + (int)(((unsigned)rp * 11u) % (unsigned)len);
+	return tt >= t1 ? tt - len : tt;
+#endif
+}
+
 __global__ void __launch_bounds__(TC_THREADS, 1)
 filter_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, FilterArgs P) {
 	extern __shared__ unsigned char smem_raw[];
@@ -149,7 +162,7 @@ filter_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ C
 					mbar_wait(&bar->b_empty[s], (use & 1) ^ 1);
 					mbar_expect_tx(&bar->b_full[s], TC_TILE_BYTES);
 					for (int a = 0; a < TC_ATOMS; a++)
-						tma_load_2d(sB + (s * TC_ATOMS + a) * TC_ATOM_BYTES, &tmB, a * 64, t * TC_BN, &bar->b_full[s]);
+						tma_load_2d(sB + (s * TC_ATOMS + a) * TC_ATOM_BYTES, &tmB, a * 64, rotated_tile(t, t0, t1, rp) * TC_BN, &bar->b_full[s]);
 				}
 			}
 		}
@@ -217,7 +230,7 @@ filter_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ C
 			for (int t = t0; t < t1; t++, n_tile++) {
 				const int as = n_tile & 1;
 				const uint32_t acc_use = n_tile >> 1;
-				const int col0 = t * TC_BN;
+				const int col0 = rotated_tile(t, t0, t1, rp) * TC_BN;
 				if (e < TC_BN) s_nb[as * TC_BN + e] = P.norm_b[col0 + e];
 				asm volatile("bar.sync 1, 256;" ::: "memory");        // the 256 epilogue threads only
 				mbar_wait(&bar->acc_full[as], acc_use & 1);
