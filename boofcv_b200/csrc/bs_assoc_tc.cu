@@ -91,6 +91,7 @@ struct FilterArgs {
 	int* cand_count;            // [nA]
 	int* cand;                  // [nA][TC_CAND_CAP]
 	float* dbg;                 // optional [nA][nB] dump of d' + |a|^2 (tests)
+	const double* row_bound;    // optional [nA]: an exact |a-b_j|^2 of some column j per row (an upper bound of the row's minimum), else huge
 };
 
 struct __align__(8) FilterBarriers {
@@ -214,7 +215,17 @@ filter_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ C
 			const bool live = row < P.nA;
 			const float na = live ? P.norm_a[row] : 0.0f;
 			const float tol = tolerance_of(na, nb_max);
+			// A row's candidates are the columns within tol of its running minimum; while that minimum is loose nearly every
+			// 32-column group has SOME lane of the warp with a new minimum and the whole warp pays the candidate path (a third of
+			// the filter at 10k x 10k).  Where the caller knows a distance the row really attains — the second direction takes
+			// it from the first one's matches — the minimum starts there: the true minimum and its ties are still within tol
+			// (the estimate of a column at most bound = tol/2 above the exact value lies below start + tol; a quarter of tol is
+			// added for the float roundings of the start value itself).
 			float run = INFINITY;
+			if (P.row_bound && live) {
+				const double ub = P.row_bound[row];
+				if (ub < 1e30) run = __double2float_ru(ub) - na + 0.25f * tol;
+			}
 			// Candidates are collected per thread (a row belongs to one thread inside an item) and appended to the row's list
 			// TC_PEND at a time: ONE atomicAdd reserves the slots, the stores do not depend on each other.  ncu had 21 % of the
 			// stall samples of the 10k x 10k filter on the atomic-then-store chain of one candidate at a time.
@@ -388,7 +399,7 @@ void launch_tc_split(const double* d_x, int n, int arrangement, void* d_operand,
 // rows of A against all rows of B: candidate lists for the rows of A
 void launch_tc_filter(const void* d_opA, const float* d_normA, int nA, const void* d_opB, const float* d_normB,
                       const unsigned* d_max_norm_b_bits, int nB, int* d_cand_count, int* d_cand, float* d_dbg, int sm_count,
-                      cudaStream_t st) {
+                      cudaStream_t st, const double* d_row_bound) {
 	if (nA <= 0 || nB <= 0) return;
 	static bool attr_set = false;
 	if (!attr_set) {
@@ -410,11 +421,29 @@ void launch_tc_filter(const void* d_opA, const float* d_normA, int nA, const voi
 	P.chunks = div_up(P.b_tiles, P.tiles_per_chunk);
 	P.norm_a = d_normA; P.norm_b = d_normB; P.max_norm_b_bits = d_max_norm_b_bits;
 	P.cand_count = d_cand_count; P.cand = d_cand; P.dbg = d_dbg;
+	static const bool no_bound = getenv("BS_TC_NO_BOUND") != nullptr;      // experiments
+	P.row_bound = no_bound ? nullptr : d_row_bound;
 	const CUtensorMap tmA = operand_map(d_opA, tc_pad_rows(nA));
 	const CUtensorMap tmB = operand_map(d_opB, tc_pad_rows(nB));
 	BS_CUDA(cudaMemsetAsync(d_cand_count, 0, (size_t)nA * 4, st));
 	const int grid = std::min(P.a_tiles256 * P.chunks, sm_count);
 	BS_LAUNCH(filter_kernel, grid, TC_THREADS, TC_SMEM_BYTES, st, tmA, tmB, P);
+}
+
+// bound[j] = min over the rows i that chose column j of fit[i] (exact distances; non-negative doubles order like their bit patterns);
+// columns nobody chose keep the fill value 0x7f7f... (huge).  The caller fills `bound` with cudaMemsetAsync(0x7f) first.
+__global__ void row_bounds_kernel(const int32_t* __restrict__ pairs, const double* __restrict__ fit, int n, int m, unsigned long long* __restrict__ bound) {
+	const int i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n) return;
+	const int j = pairs[i];
+	const double f = fit[i];
+	if (j >= 0 && j < m && f >= 0.0) atomicMin(bound + j, (unsigned long long)__double_as_longlong(f));
+}
+void launch_tc_row_bounds(const int32_t* d_pairs, const double* d_fit, int n, int m, double* d_bound, cudaStream_t st) {
+	if (m <= 0) return;
+	BS_CUDA(cudaMemsetAsync(d_bound, 0x7f, (size_t)m * 8, st));
+	if (n <= 0) return;
+	BS_LAUNCH(row_bounds_kernel, div_up(n, 256), 256, 0, st, d_pairs, d_fit, n, m, reinterpret_cast<unsigned long long*>(d_bound));
 }
 
 void launch_tc_rescore(const double* d_A, int nA, const double* d_B, const int* d_cand_count, const int* d_cand, int mode, double max_fit,

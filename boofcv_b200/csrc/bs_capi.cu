@@ -1123,8 +1123,10 @@ struct bs_assoc {
 		launch_tc_filter(op_src.p, norm_src.as<float>(), n, op_dst.p, norm_dst.as<float>(), sc + 1, m, cand_count.as<int>(), cand.as<int>(),
 		                 nullptr, sm_count, st);
 		launch_tc_rescore(src, n, dst, cand_count.as<int>(), cand.as<int>(), 0, max_fit, 0, pairs, fit, nullptr, nullptr, nullptr, overflow, st);
+		tc_bound.reserve((size_t)m * 8);
+		launch_tc_row_bounds(pairs, fit, n, m, tc_bound.as<double>(), st);
 		launch_tc_filter(op_dst.p, norm_dst.as<float>(), m, op_src.p, norm_src.as<float>(), sc + 0, n, cand_count.as<int>(), cand.as<int>(),
-		                 nullptr, sm_count, st);
+		                 nullptr, sm_count, st, tc_bound.as<double>());
 		launch_tc_rescore(dst, m, src, cand_count.as<int>(), cand.as<int>(), 1, 0.0, row_offset, nullptr, nullptr, cmin, cfirst, clast, overflow, st);
 		int h_overflow = 0;
 		BS_CUDA(cudaMemcpyAsync(&h_overflow, overflow, 4, cudaMemcpyDeviceToHost, st));
@@ -1140,6 +1142,7 @@ struct bs_assoc {
 		const size_t rows = (size_t)std::max(n, m);
 		cand_count.reserve(rows * 4); cand.reserve(rows * tc_cand_cap() * 4);
 		col_min.reserve((size_t)m * 8); col_first.reserve((size_t)m * 4); col_last.reserve((size_t)m * 4);
+		tc_bound.reserve((size_t)m * 8);
 	}
 	// tensor-core filter + exact re-score, queued on `st` without a host round trip; *overflow (device, zeroed by the caller)
 	// becomes non-zero if a candidate list overflowed (results then invalid)
@@ -1151,8 +1154,11 @@ struct bs_assoc {
 		launch_tc_rescore(src, n, dst, cand_count.as<int>(), cand.as<int>(), 0, max_fit, 0, pairs, fit, nullptr, nullptr, nullptr, overflow, st);
 		if (backwards) {
 			col_min.reserve((size_t)m * 8); col_first.reserve((size_t)m * 4); col_last.reserve((size_t)m * 4);
+			// the column minimum of j is at most the fit of any row that chose j: the second direction starts from it
+			tc_bound.reserve((size_t)m * 8);
+			launch_tc_row_bounds(pairs, fit, n, m, tc_bound.as<double>(), st);
 			launch_tc_filter(op_dst.p, norm_dst.as<float>(), m, op_src.p, norm_src.as<float>(), sc + 0, n, cand_count.as<int>(), cand.as<int>(),
-			                 nullptr, sm_count, st);
+			                 nullptr, sm_count, st, tc_bound.as<double>());
 			launch_tc_rescore(dst, m, src, cand_count.as<int>(), cand.as<int>(), 1, 0.0, 0, nullptr, nullptr, col_min.as<double>(),
 			                  col_first.as<int32_t>(), col_last.as<int32_t>(), overflow, st);
 			launch_validate(n, 0, pairs, fit, col_min.as<double>(), col_first.as<int32_t>(), col_last.as<int32_t>(), st);
@@ -1169,7 +1175,7 @@ struct bs_assoc {
 		BS_CUDA(cudaStreamSynchronize(st));
 		return h_overflow == 0;
 	}
-	DevBuf batch_flags;
+	DevBuf batch_flags, tc_bound;
 };
 
 extern "C" {
@@ -1197,7 +1203,7 @@ int bs_assoc_destroy(bs_assoc* a) {
 		a->col_min.release(); a->col_first.release(); a->col_last.release();
 		a->d_src.release(); a->d_dst.release(); a->d_pairs.release(); a->d_fit.release();
 		a->op_src.release(); a->op_dst.release(); a->norm_src.release(); a->norm_dst.release(); a->tc_scalars.release();
-		a->cand_count.release(); a->cand.release(); a->batch_flags.release();
+		a->cand_count.release(); a->cand.release(); a->batch_flags.release(); a->tc_bound.release();
 		a->sb_idx_src.release(); a->sb_idx_dst.release(); a->sb_counts.release(); a->sb_src.release(); a->sb_dst.release();
 		a->sb_pairs.release(); a->sb_fit.release(); a->sb_white_src.release(); a->sb_white_dst.release();
 		if (a->stream) cudaStreamDestroy(a->stream);

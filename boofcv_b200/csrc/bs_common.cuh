@@ -198,7 +198,8 @@ int tc_cand_cap();
 void launch_tc_split(const double* d_x, int n, int arrangement, void* d_operand, float* d_norm, unsigned* d_max_norm_bits, cudaStream_t st);
 void launch_tc_filter(const void* d_opA, const float* d_normA, int nA, const void* d_opB, const float* d_normB,
                       const unsigned* d_max_norm_b_bits, int nB, int* d_cand_count, int* d_cand, float* d_dbg, int sm_count,
-                      cudaStream_t st);
+                      cudaStream_t st, const double* d_row_bound = nullptr);
+void launch_tc_row_bounds(const int32_t* d_pairs, const double* d_fit, int n, int m, double* d_bound, cudaStream_t st);
 void launch_tc_rescore(const double* d_A, int nA, const double* d_B, const int* d_cand_count, const int* d_cand, int mode, double max_fit,
                        int index_offset, int32_t* pairs, double* fit, double* o_min, int32_t* o_first, int32_t* o_last, int* d_overflow,
                        cudaStream_t st);
