@@ -344,7 +344,7 @@ static DescribeSmem describe_smem(const DescribeParams& p) {
 }
 
 #ifndef BS_DESC_MIN_BLOCKS
-#define BS_DESC_MIN_BLOCKS 8
+#define BS_DESC_MIN_BLOCKS 7
 #endif
 template <typename T>
 __global__ void __launch_bounds__(DESC_WARPS * 32, BS_DESC_MIN_BLOCKS)
