@@ -106,7 +106,7 @@ def run_reference(args, rank, world):
     per_step = []
     sample_frames = 0
     for s in range(args.warmup + args.steps):
-        fps, n, feats = cpu_surf_fps(frames, cores, min_seconds=4.0, max_frames=16)
+        fps, n, feats = cpu_surf_fps(frames, cores, min_seconds=4.0, max_frames=1024)
         if s >= args.warmup:
             per_step.append(fps); sample_frames += n
     v = float(np.mean(per_step))
@@ -358,7 +358,7 @@ def main():
             from boofcv_b200.synth import blob_image
             cores = os.cpu_count() or 1
             frames = [blob_image(W, H, 234 + i) for i in range(2)]
-            fps, n, _ = cpu_surf_fps(frames, cores, min_seconds=12.0, max_frames=32)
+            fps, n, _ = cpu_surf_fps(frames, cores, min_seconds=12.0, max_frames=4096)
             out["cpu_baseline"] = {"value": fps, "unit": UNIT, "cores": cores, "kind": "port",
                                    "sample": "%d x 1080p frames (same generator, seeds 234..235 cycled), surfFast, %d threads; "
                                              "C++ restatement of the reference Java (no JVM on this box)" % (n, cores)}
