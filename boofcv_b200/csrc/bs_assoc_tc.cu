@@ -6,17 +6,22 @@
 //
 // The reference evaluates all N*M distances in fp64.  Here the N*M work runs on the 5th-generation tensor cores and only
 // a handful of pairs per row is re-scored in fp64, in the reference's summation order, so the result is bit-identical:
-//   1. split_kernel: every descriptor x is split into bf16 hi + bf16 lo (x = hi + lo + r, |r| <= 2^-18 |x|) and stored as a
-//      K = 192 row: P = [hi | hi | lo] or Q = [hi | lo | hi], so that P(a) . Q(b) = hi.hi + hi.lo + lo.hi.
-//   2. filter_kernel (tcgen05): s = P(a).Q(b) for 256 rows x 128 columns per step, fp32 accumulators in TMEM;
-//      d' = |b|^2 - 2 s.  Each row keeps the running minimum m of d' and emits column j as a CANDIDATE whenever
-//      d'_j <= m + tol.  tol = 2 * (bound on |d' - exact|), so the exact minimum — and every exact tie — is always among
-//      the candidates (the bound and its margin are stated at tolerance_of()).
+//   1. split_kernel: every descriptor is rounded to bf16 (one K = 64 row = one 128-byte swizzle atom) and its squared norm
+//      kept in fp32.
+//   2. filter_kernel (tcgen05): s = a~ . b~ for 128 rows x 128 columns per accumulator, fp32 in TMEM; d' = |b|^2 - 2 s.
+//      Each row keeps the running minimum m of d' and emits column j as a CANDIDATE whenever d'_j <= m + tol.
+//      tol = 2 * (bound on |d' - exact|), so the exact minimum — and every exact tie — is always among the candidates
+//      (the bound is stated at tolerance_of()).
 //   3. rescore_kernel: exact fp64 distance of every candidate, sequential over k without FMA like the reference; minimum,
 //      first and last index of the minimum -> pairs/fit (forward) or the column statistics used by backward validation.
-// Roles inside the filter CTA (320 threads): warp 0 = TMA producer, warp 1 = MMA issuer (one thread), warps 2-9 =
-// epilogue (one TMEM lane = one row per thread, one warp set per resident A tile).  A (2 x 128 rows) stays resident per work item, B tiles stream through a
-// 2-stage ring; two accumulator buffers in TMEM let the epilogue of tile t overlap the MMAs of tile t+1.
+// The filter's shape follows what tools/probe/tc_probe.cu measured on this GPU (profiles/r2_tc_probe.txt): a 128x128x16 UMMA
+// with both operands in shared memory takes 97 cycles (operand fetch), 73 with A in TMEM (floor 64), and reading a whole
+// accumulator back costs far less than producing it (tcgen05.ld: ~880 B/cycle/SM).  So: the 256 rows of a row block live in
+// TMEM as the A operand (written there by the epilogue threads with tcgen05.st), B tiles stream through an 8-stage TMA ring
+// together with their column norms, three 128-column accumulators rotate between the MMA issuer and two epilogue groups.
+// Roles inside the CTA (320 threads): warp 0 = TMA producer, warp 1 = MMA issuer (one elected thread), warps 2-5 / 6-9 =
+// epilogue of the first / second 128 rows (one TMEM lane = one row per thread).  The work of a launch is the sequence of
+// (row block, B tile) pairs in row-block-major order, cut into one contiguous range per CTA: equal shares whatever the shape.
 #include "bs_common.cuh"
 #include <cstdlib>
 #include "bs_sm100.cuh"
@@ -31,36 +36,29 @@ namespace bs {
 using namespace sm100;
 
 constexpr int TC_DOF = 64;                 // descriptor length this path is built for (SURF-64)
-constexpr int TC_K = 3 * TC_DOF;           // 192 bf16 per operand row
-constexpr int TC_ATOMS = TC_K / 64;        // 128-byte swizzle atoms along K
-constexpr int TC_BM = 128, TC_BN = 128;    // one UMMA: 128 x 128 x 16
-constexpr int TC_MROWS = 2 * TC_BM;        // rows per work item (two resident A tiles)
-constexpr int TC_STAGES = 2;
-constexpr int TC_ATOM_BYTES = TC_BM * 128; // 16 KB: 128 rows x 128 B
-constexpr int TC_TILE_BYTES = TC_ATOMS * TC_ATOM_BYTES;   // 48 KB
-constexpr int TC_EPI_WARPS = 8;           // two per TMEM lane quarter: one per resident A tile
+constexpr int TC_K = TC_DOF;               // bf16 per operand row: one 128-byte swizzle atom
+constexpr int TC_BM = 128, TC_BN = 128;    // one accumulator: 128 x 128, four 128x128x16 UMMAs
+constexpr int TC_MROWS = 2 * TC_BM;        // rows per row block (two A halves resident in TMEM)
+constexpr int TC_STAGES = 8;               // B ring
+constexpr int TC_TILE_BYTES = TC_BN * 128; // 16 KB: 128 rows x 128 B
+constexpr int TC_SLOTS = 3;                // accumulators in flight
+constexpr int TC_A_COL = TC_SLOTS * TC_BN; // TMEM columns [384, 448): the two A halves, 32 columns each
+constexpr int TC_EPI_WARPS = 8;
 constexpr int TC_THREADS = 64 + 32 * TC_EPI_WARPS;
 constexpr int TC_CAND_CAP = 64;            // candidates kept per row; more -> the caller falls back to the exact kernel
 constexpr int TC_TMEM_COLS = 512;
 
 // ---------------------------------------------------------------- 1. split
-// arrangement 0: P = [hi | hi | lo], 1: Q = [hi | lo | hi].  Rows >= n (padding) are zero with norm = +inf.
-__global__ void split_kernel(const double* __restrict__ x, int n, int n_pad, int arrangement, __nv_bfloat16* __restrict__ out,
-                             float* __restrict__ norm, unsigned* __restrict__ max_norm_bits) {
+// Rows >= n (padding up to a multiple of 256) are zero with norm = +inf.
+__global__ void split_kernel(const double* __restrict__ x, int n, int n_pad, __nv_bfloat16* __restrict__ out, float* __restrict__ norm,
+                             unsigned* __restrict__ max_norm_bits) {
 	const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
 	const int lane = threadIdx.x & 31;
 	if (row >= n_pad) return;
-	__nv_bfloat16* o = out + (size_t)row * TC_K;
-	double sq = 0.0;
-	for (int k = lane; k < TC_DOF; k += 32) {
-		const double v = row < n ? x[(size_t)row * TC_DOF + k] : 0.0;
-		const __nv_bfloat16 hi = __double2bfloat16(v);
-		const __nv_bfloat16 lo = __double2bfloat16(v - (double)__bfloat162float(hi));
-		o[k] = hi;
-		o[TC_DOF + k] = arrangement == 0 ? hi : lo;
-		o[2 * TC_DOF + k] = arrangement == 0 ? lo : hi;
-		sq += v * v;
-	}
+	double2 v = make_double2(0.0, 0.0);
+	if (row < n) v = reinterpret_cast<const double2*>(x + (size_t)row * TC_DOF)[lane];
+	reinterpret_cast<__nv_bfloat162*>(out + (size_t)row * TC_K)[lane] = __nv_bfloat162(__double2bfloat16(v.x), __double2bfloat16(v.y));
+	double sq = v.x * v.x + v.y * v.y;
 	for (int d = 16; d > 0; d >>= 1) sq += __shfl_xor_sync(0xffffffffu, sq, d);
 	if (lane == 0) {
 		const float f = row < n ? (float)sq : INFINITY;
@@ -69,22 +67,25 @@ __global__ void split_kernel(const double* __restrict__ x, int n, int n_pad, int
 	}
 }
 
-// Bound on |d'_computed - d'_exact| for one pair, d' = |b|^2 - 2 a.b:
-//   split: dropped terms lo.lo, r_a.b, a.r_b               <= 3 * 2^-18 |a||b|      = 1.2e-5 |a||b|
-//   fp32 accumulation of 192 exact bf16 x bf16 products    <= 192 * 2^-23 * 3|a||b| = 6.9e-5 |a||b|   (truncating adder assumed)
-//   => |s - a.b| <= 8.1e-5 |a||b|; budgeted 3e-4 (3.7x margin) ; d' doubles it: 6e-4 |a||b|
-//   fp32 rounding of |b|^2 and of the final fma            <= 2.4e-7 (|a|^2 + |b|^2); budgeted 1e-6
-// tol = 2 * bound (tests/test_gpu_assoc_tc.py measures the real error and asserts it stays below a quarter of the budget)
+// Bound on |d'_computed - d'_exact| for one pair, d' = |b|^2 - 2 a.b, s = fp32 sum of the 64 products a~_k b~_k:
+//   rounding to bf16 (round to nearest, 8-bit significand): a~_k = a_k (1 + e), |e| <= 2^-9
+//       |a~.b~ - a.b| <= (2 * 2^-9 + 2^-18) sum |a_k b_k| <= 3.91e-3 |a||b|            (Cauchy-Schwarz)
+//   fp32 accumulation of 64 exact bf16 x bf16 products: <= 64 * 2^-23 |a~||b~| = 7.7e-6 |a||b|   (truncating adder assumed)
+//   => |s - a.b| <= 3.92e-3 |a||b|, budgeted 4e-3; d' doubles it: 8e-3 |a||b|
+//   fp32 rounding of |b|^2 and of the final fma: <= 2.4e-7 (|a|^2 + |b|^2); budgeted 1e-6
+// tol = 2 * bound (tests/test_gpu_assoc_tc.py measures the real error and asserts it stays below a quarter of the budget).
+// Values beyond bf16's range (|x| >= 3.4e38) make the norms infinite, tol infinite, every column a candidate: the lists overflow and the
+// caller redoes the problem with the exact kernel.
 __device__ __forceinline__ float tolerance_of(float na, float nb_max) {
-	return 1.2e-3f * sqrtf(na * nb_max) + 2e-6f * (na + nb_max);
+	return 1.6e-2f * sqrtf(na * nb_max) + 2e-6f * (na + nb_max);
 }
 
 // ---------------------------------------------------------------- 2. filter
 struct FilterArgs {
 	int nA, nB;                 // real rows / columns
-	int a_tiles256;             // ceil(nA / 256)
+	int a_blocks;               // ceil(nA / 256)
 	int b_tiles;                // ceil(nB / 128)
-	int chunks, tiles_per_chunk;
+	const __nv_bfloat16* opA;   // [a_blocks * 256][64]
 	const float* norm_a;        // [nA_pad]
 	const float* norm_b;        // [nB_pad] (+inf in the padding)
 	const unsigned* max_norm_b_bits;
@@ -95,45 +96,32 @@ struct FilterArgs {
 };
 
 struct __align__(8) FilterBarriers {
-	uint64_t a_full, a_empty;
+	uint64_t a_full;
 	uint64_t b_full[TC_STAGES], b_empty[TC_STAGES];
-	uint64_t acc_full[2], acc_empty[2];
+	uint64_t acc_full[TC_SLOTS], acc_empty[TC_SLOTS];
 	uint32_t tmem_base;
 	uint32_t pad;
 };
 
 constexpr int TC_PEND = 8;                // candidates an epilogue thread collects before it reserves slots in its row's list
-constexpr int TC_SMEM_BYTES = 1024 /*alignment slack*/ + 2 * TC_TILE_BYTES + TC_STAGES * TC_TILE_BYTES + 2 * TC_BN * 4 + (int)sizeof(FilterBarriers) +
+constexpr int TC_SMEM_BYTES = 1024 /*alignment slack*/ + TC_STAGES * TC_TILE_BYTES + TC_STAGES * TC_BN * 4 + (int)sizeof(FilterBarriers) +
                               TC_PEND * 32 * TC_EPI_WARPS * 4;
 
-// Row items that run side by side would all stream the same B tiles at the same moment (every CTA starts at the first tile of its
-// chunk): each row item walks its chunk from a different starting tile instead.  The running minimum and the candidate lists do not
-// depend on the order of the columns.
-__device__ __forceinline__ int rotated_tile(int t, int t0, int t1, int rp) {
-#ifdef BS_TC_NO_ROTATE
-	return t;
-#else
-	const int len = t1 - t0;
-	int tt = t + (int)(((unsigned)rp * 11u) % (unsigned)len);
-	return tt >= t1 ? tt - len : tt;
-#endif
-}
-
+template <bool DBG>
 __global__ void __launch_bounds__(TC_THREADS, 1)
-filter_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, FilterArgs P) {
+filter_kernel(const __grid_constant__ CUtensorMap tmB, FilterArgs P) {
 	extern __shared__ unsigned char smem_raw[];
 	unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-	unsigned char* sA = smem;                                        // [2][3 atoms][128 rows][128 B]
-	unsigned char* sB = sA + 2 * TC_TILE_BYTES;                      // [stages][3 atoms][128 rows][128 B]
-	float* s_nb = reinterpret_cast<float*>(sB + TC_STAGES * TC_TILE_BYTES);   // [2][128]
-	FilterBarriers* bar = reinterpret_cast<FilterBarriers*>(s_nb + 2 * TC_BN);
+	unsigned char* sB = smem;                                                       // [stages][128 rows][128 B]
+	float* s_nb = reinterpret_cast<float*>(sB + TC_STAGES * TC_TILE_BYTES);         // [stages][128]: column norms of the stage's tile
+	FilterBarriers* bar = reinterpret_cast<FilterBarriers*>(s_nb + TC_STAGES * TC_BN);
 	int* s_pend = reinterpret_cast<int*>(bar + 1);                   // [TC_PEND][256]: pending candidates, one column per epilogue thread
 
 	const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 	if (threadIdx.x == 0) {
-		mbar_init(&bar->a_full, 1); mbar_init(&bar->a_empty, 1);
-		for (int s = 0; s < TC_STAGES; s++) { mbar_init(&bar->b_full[s], 1); mbar_init(&bar->b_empty[s], 1); }
-		for (int s = 0; s < 2; s++) { mbar_init(&bar->acc_full[s], 1); mbar_init(&bar->acc_empty[s], TC_EPI_WARPS); }
+		mbar_init(&bar->a_full, TC_EPI_WARPS);
+		for (int s = 0; s < TC_STAGES; s++) { mbar_init(&bar->b_full[s], 1); mbar_init(&bar->b_empty[s], TC_EPI_WARPS); }
+		for (int s = 0; s < TC_SLOTS; s++) { mbar_init(&bar->acc_full[s], 1); mbar_init(&bar->acc_empty[s], TC_EPI_WARPS / 2); }
 		mbar_fence_init();
 	}
 	__syncwarp();
@@ -143,152 +131,167 @@ filter_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ C
 	tc_fence_after();
 	const uint32_t tmem = bar->tmem_base;
 
-	const int n_items = P.a_tiles256 * P.chunks;
+	// this CTA's share of the (row block, B tile) sequence
+	const long long total = (long long)P.a_blocks * P.b_tiles;
+	const long long g0 = total * blockIdx.x / gridDim.x, g1 = total * (blockIdx.x + 1) / gridDim.x;
+	const int rp0 = (int)(g0 / P.b_tiles), t0 = (int)(g0 - (long long)rp0 * P.b_tiles);
+	const int n_tiles = (int)(g1 - g0);
+
 	if (warp == 0) {
-		// ===== TMA producer =====
-		if (lane == 0) {
-			tma_prefetch_desc(&tmA); tma_prefetch_desc(&tmB);
-			uint32_t n_item = 0, n_tile = 0;
-			for (int item = blockIdx.x; item < n_items; item += gridDim.x, n_item++) {
-				const int rp = item / P.chunks, ch = item - rp * P.chunks;
-				const int t0 = ch * P.tiles_per_chunk, t1 = min(t0 + P.tiles_per_chunk, P.b_tiles);
-				mbar_wait(&bar->a_empty, (n_item & 1) ^ 1);          // MMAs of the previous item are done with A
-				mbar_expect_tx(&bar->a_full, 2 * TC_TILE_BYTES);
-				for (int h = 0; h < 2; h++)
-					for (int a = 0; a < TC_ATOMS; a++)
-						tma_load_2d(sA + (h * TC_ATOMS + a) * TC_ATOM_BYTES, &tmA, a * 64, rp * TC_MROWS + h * TC_BM, &bar->a_full);
-				for (int t = t0; t < t1; t++, n_tile++) {
-					const int s = n_tile % TC_STAGES;
-					const uint32_t use = n_tile / TC_STAGES;
-					mbar_wait(&bar->b_empty[s], (use & 1) ^ 1);
-					mbar_expect_tx(&bar->b_full[s], TC_TILE_BYTES);
-					for (int a = 0; a < TC_ATOMS; a++)
-						tma_load_2d(sB + (s * TC_ATOMS + a) * TC_ATOM_BYTES, &tmB, a * 64, rotated_tile(t, t0, t1, rp) * TC_BN, &bar->b_full[s]);
-				}
+		// ===== TMA producer: B tile + its 128 column norms per stage =====
+		if (elect_one()) {
+			tma_prefetch_desc(&tmB);
+			int t = t0;
+			for (int n = 0; n < n_tiles; n++) {
+				const int s = n % TC_STAGES;
+				const uint32_t use = n / TC_STAGES;
+				mbar_wait(&bar->b_empty[s], (use & 1) ^ 1);          // the epilogue warps are done with the stage's norms (and the MMAs with its tile)
+				mbar_expect_tx(&bar->b_full[s], TC_TILE_BYTES + TC_BN * 4);
+				tma_load_2d(sB + s * TC_TILE_BYTES, &tmB, 0, t * TC_BN, &bar->b_full[s]);
+				bulk_load_1d(s_nb + s * TC_BN, P.norm_b + (size_t)t * TC_BN, TC_BN * 4, &bar->b_full[s]);
+				if (++t == P.b_tiles) t = 0;
 			}
 		}
 	} else if (warp == 1) {
 		// ===== MMA issuer =====
-		if (lane == 0) {
+		if (elect_one()) {
 			constexpr uint32_t idesc = umma_idesc_bf16(TC_BM, TC_BN);
-			uint32_t n_item = 0, n_tile = 0;
-			for (int item = blockIdx.x; item < n_items; item += gridDim.x, n_item++) {
-				const int rp = item / P.chunks, ch = item - rp * P.chunks;
-				const int t0 = ch * P.tiles_per_chunk, t1 = min(t0 + P.tiles_per_chunk, P.b_tiles);
-				mbar_wait(&bar->a_full, n_item & 1);
-				for (int t = t0; t < t1; t++, n_tile++) {
-					const int s = n_tile % TC_STAGES;
-					const uint32_t use = n_tile / TC_STAGES;
-					const int as = n_tile & 1;
-					const uint32_t acc_use = n_tile >> 1;
-					mbar_wait(&bar->b_full[s], use & 1);
-					mbar_wait(&bar->acc_empty[as], (acc_use & 1) ^ 1);   // epilogue drained this accumulator buffer
-					tc_fence_after();
-					for (int h = 0; h < 2; h++) {
-						const uint32_t d = tmem + (uint32_t)(as * 2 * TC_BN + h * TC_BN);
-						for (int a = 0; a < TC_ATOMS; a++) {
-							const uint64_t da = umma_desc_sw128(smem_u32(sA + (h * TC_ATOMS + a) * TC_ATOM_BYTES));
-							const uint64_t db = umma_desc_sw128(smem_u32(sB + (s * TC_ATOMS + a) * TC_ATOM_BYTES));
-#pragma unroll
-							for (int kk = 0; kk < 4; kk++)                   // 16 bf16 = 32 bytes = 2 descriptor units per step
-								umma_bf16(d, da + 2 * kk, db + 2 * kk, idesc, (a | kk) != 0 ? 1u : 0u);
-						}
-					}
-					umma_commit(&bar->b_empty[s]);                       // smem stage free once these MMAs have read it
-					umma_commit(&bar->acc_full[as]);                     // accumulators complete
+			int t = t0;
+			uint32_t seg = 0, m = 0;                                 // row-block segments started, accumulators produced
+			for (int n = 0; n < n_tiles; n++) {
+				if (t == 0 || n == 0) {                              // the epilogue threads have written this row block's A into TMEM
+					mbar_wait(&bar->a_full, seg & 1);
+					seg++;
 				}
-				umma_commit(&bar->a_empty);
+				const int s = n % TC_STAGES;
+				mbar_wait(&bar->b_full[s], (n / TC_STAGES) & 1);
+				tc_fence_after();
+				const uint64_t db = umma_desc_sw128(smem_u32(sB + s * TC_TILE_BYTES));
+#pragma unroll
+				for (int h = 0; h < 2; h++, m++) {
+					const uint32_t slot = m % TC_SLOTS;
+					mbar_wait(&bar->acc_empty[slot], ((m / TC_SLOTS) & 1) ^ 1);   // the epilogue drained this accumulator
+					tc_fence_after();
+					const uint32_t d = tmem + slot * TC_BN;
+					const uint32_t a = tmem + (uint32_t)(TC_A_COL + h * (TC_K / 2));
+#pragma unroll
+					for (int kk = 0; kk < TC_K / 16; kk++)               // 16 bf16 = 8 TMEM columns of A = 32 bytes = 2 descriptor units of B
+						umma_bf16_ts(d, a + 8 * kk, db + 2 * kk, idesc, kk != 0 ? 1u : 0u);
+					umma_commit(&bar->acc_full[slot]);
+				}
+				if (++t == P.b_tiles) t = 0;
 			}
 		}
 	} else {
-		// ===== epilogue: warps 2..9.  TMEM lane quarter = warp % 4 (hardware rule); warps 2-5 take A tile 0, 6-9 A tile 1 =====
+		// ===== epilogue: warps 2..9.  TMEM lane quarter = warp % 4 (hardware rule); warps 2-5 take A half 0, 6-9 A half 1 =====
 		const int q = warp & 3;
 		const int h = (warp - 2) >> 2;
 		const int e = (warp - 2) * 32 + lane;                        // 0..255 among the epilogue threads
-		const int L = q * 32 + lane;                                 // TMEM lane = row inside the 128-row tile
+		const int L = q * 32 + lane;                                 // TMEM lane = row inside the 128-row half
+		const uint32_t lane_base = tmem + ((uint32_t)(q * 32) << 16);
 		const float nb_max = __uint_as_float(*P.max_norm_b_bits);
-		uint32_t n_tile = 0;
-		for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
-			const int rp = item / P.chunks, ch = item - rp * P.chunks;
-			const int t0 = ch * P.tiles_per_chunk, t1 = min(t0 + P.tiles_per_chunk, P.b_tiles);
-			const int row = rp * TC_MROWS + h * TC_BM + L;
-			const bool live = row < P.nA;
-			const float na = live ? P.norm_a[row] : 0.0f;
-			const float tol = tolerance_of(na, nb_max);
-			// A row's candidates are the columns within tol of its running minimum; while that minimum is loose nearly every
-			// 32-column group has SOME lane of the warp with a new minimum and the whole warp pays the candidate path (a third of
-			// the filter at 10k x 10k).  Where the caller knows a distance the row really attains — the second direction takes
-			// it from the first one's matches — the minimum starts there: the true minimum and its ties are still within tol
-			// (the estimate of a column at most bound = tol/2 above the exact value lies below start + tol; a quarter of tol is
-			// added for the float roundings of the start value itself).
-			float run = INFINITY;
-			if (P.row_bound && live) {
-				const double ub = P.row_bound[row];
-				if (ub < 1e30) run = __double2float_ru(ub) - na + 0.25f * tol;
+		int rp = rp0, t = t0;
+		int row = 0;
+		bool live = false;
+		float na = 0.0f, tol = 0.0f, run = INFINITY;
+		// Candidates are collected per thread (a row belongs to one thread inside a segment) and appended to the row's list
+		// TC_PEND at a time: ONE atomicAdd reserves the slots, the stores do not depend on each other.
+		int n_pend = 0;
+		auto flush = [&]() {
+			if (n_pend == 0) return;
+			const int base = atomicAdd(P.cand_count + row, n_pend);
+#pragma unroll
+			for (int i = 0; i < TC_PEND; i++)
+				if (i < n_pend && base + i < TC_CAND_CAP) P.cand[(size_t)row * TC_CAND_CAP + base + i] = s_pend[i * (32 * TC_EPI_WARPS) + e];
+			n_pend = 0;
+		};
+		for (int n = 0; n < n_tiles; n++) {
+			if (t == 0 || n == 0) {
+				// ---- new row block: this thread's row goes into TMEM as a row of the A operand (lane = row, column j = k 2j | 2j+1).
+				// The MMAs that read this half of the previous block have completed: this warp waited for the last of them.
+				flush();
+				row = rp * TC_MROWS + h * TC_BM + L;
+				live = row < P.nA;
+				na = live ? P.norm_a[row] : 0.0f;
+				tol = tolerance_of(na, nb_max);
+				// A row's candidates are the columns within tol of its running minimum.  Where the caller knows a distance the row
+				// really attains — the second direction takes it from the first one's matches — the minimum starts there: the true
+				// minimum and its ties are still within tol (the estimate of a column at most bound = tol/2 above the exact value lies
+				// below start + tol; a quarter of tol is added for the float roundings of the start value itself).
+				run = INFINITY;
+				if (P.row_bound && live) {
+					const double ub = P.row_bound[row];
+					if (ub < 1e30) run = __double2float_ru(ub) - na + 0.25f * tol;
+				}
+				uint32_t ar[32];
+				const uint4* src = reinterpret_cast<const uint4*>(P.opA + (size_t)row * TC_K);     // the operand is padded to whole row blocks
+#pragma unroll
+				for (int i = 0; i < 8; i++) {
+					const uint4 v = __ldg(src + i);
+					ar[4 * i] = v.x; ar[4 * i + 1] = v.y; ar[4 * i + 2] = v.z; ar[4 * i + 3] = v.w;
+				}
+				tmem_st32(lane_base + (uint32_t)(TC_A_COL + h * (TC_K / 2)), ar);
+				tc_fence_before();
+				__syncwarp();
+				if (lane == 0) mbar_arrive(&bar->a_full);
 			}
-			// Candidates are collected per thread (a row belongs to one thread inside an item) and appended to the row's list
-			// TC_PEND at a time: ONE atomicAdd reserves the slots, the stores do not depend on each other.  ncu had 21 % of the
-			// stall samples of the 10k x 10k filter on the atomic-then-store chain of one candidate at a time.
-			int n_pend = 0;
-			auto flush = [&]() {
-				if (n_pend == 0) return;
-				const int base = atomicAdd(P.cand_count + row, n_pend);
+			const int s = n % TC_STAGES;
+			const uint32_t m = 2u * (uint32_t)n + (uint32_t)h;
+			const uint32_t slot = m % TC_SLOTS;
+			const int col0 = t * TC_BN;
+			mbar_wait(&bar->b_full[s], (n / TC_STAGES) & 1);         // the stage's norms have landed (long since: the MMAs needed its tile)
+			mbar_wait(&bar->acc_full[slot], (m / TC_SLOTS) & 1);
+			tc_fence_after();
+			// The whole accumulator row (128 columns) is fetched at once and the accumulator handed back to the MMA issuer before any
+			// arithmetic: the slot is held for one TMEM round trip, not for the reduction.
+			const uint32_t tbase = lane_base + slot * TC_BN;
+			uint32_t r0[32], r1[32], r2[32], r3[32];
+			tmem_ld32_issue(tbase, r0); tmem_ld32_issue(tbase + 32, r1); tmem_ld32_issue(tbase + 64, r2); tmem_ld32_issue(tbase + 96, r3);
+			tmem_ld_wait(r0); tmem_ld_wait(r1); tmem_ld_wait(r2); tmem_ld_wait(r3);
+			tc_fence_before();
+			__syncwarp();
+			if (lane == 0) mbar_arrive(&bar->acc_empty[slot]);
+			const uint32_t nb_addr = smem_u32(s_nb + s * TC_BN);
+			// d' = |b|^2 - 2 s for 32 columns (packed pairs, in place), two minimum chains of three-input minima
+			auto reduce = [&](uint32_t (&r)[32], int c) {
+				float m0 = INFINITY, m1 = INFINITY;
 #pragma unroll
-				for (int i = 0; i < TC_PEND; i++)
-					if (i < n_pend && base + i < TC_CAND_CAP) P.cand[(size_t)row * TC_CAND_CAP + base + i] = s_pend[i * (32 * TC_EPI_WARPS) + e];
-				n_pend = 0;
-			};
-			for (int t = t0; t < t1; t++, n_tile++) {
-				const int as = n_tile & 1;
-				const uint32_t acc_use = n_tile >> 1;
-				const int col0 = rotated_tile(t, t0, t1, rp) * TC_BN;
-				if (e < TC_BN) s_nb[as * TC_BN + e] = P.norm_b[col0 + e];
-				asm volatile("bar.sync 1, 256;" ::: "memory");        // the 256 epilogue threads only
-				mbar_wait(&bar->acc_full[as], acc_use & 1);
-				tc_fence_after();
-				const uint32_t tbase = tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * 2 * TC_BN + h * TC_BN);
-				uint32_t ra[32], rb[32];
-				// chunk c+1 is in flight while chunk c is reduced
-				auto reduce = [&](uint32_t (&r)[32], int c) {
-					const float* nb = s_nb + as * TC_BN + c * 32;
-					float v[32];
-					float cmin = INFINITY;
-#pragma unroll
-					for (int k = 0; k < 32; k++) {
-						v[k] = fmaf(-2.0f, __uint_as_float(r[k]), nb[k]);
-						cmin = fminf(cmin, v[k]);
-					}
+				for (int k = 0; k < 8; k++) {
+					const float4 b = lds128(nb_addr + (uint32_t)(c * 128 + k * 16));
+					const float2 u = ffma2(make_float2(__uint_as_float(r[4 * k]), __uint_as_float(r[4 * k + 1])), make_float2(-2.0f, -2.0f), make_float2(b.x, b.y));
+					const float2 w = ffma2(make_float2(__uint_as_float(r[4 * k + 2]), __uint_as_float(r[4 * k + 3])), make_float2(-2.0f, -2.0f), make_float2(b.z, b.w));
+					r[4 * k] = __float_as_uint(u.x); r[4 * k + 1] = __float_as_uint(u.y); r[4 * k + 2] = __float_as_uint(w.x); r[4 * k + 3] = __float_as_uint(w.y);
+					m0 = fmin3(m0, u.x, u.y);
+					m1 = fmin3(m1, w.x, w.y);
+				}
+				const float cmin = fminf(m0, m1);
+				if (DBG) {
 					if (P.dbg && live) {
 #pragma unroll
 						for (int k = 0; k < 32; k++)
-							if (col0 + c * 32 + k < P.nB) P.dbg[(size_t)row * P.nB + col0 + c * 32 + k] = v[k] + na;
+							if (col0 + c * 32 + k < P.nB) P.dbg[(size_t)row * P.nB + col0 + c * 32 + k] = __uint_as_float(r[k]) + na;
 					}
-					if (cmin <= run + tol && cmin < INFINITY && live) {
-						run = fminf(run, cmin);
-						const float thr = run + tol;
-						unsigned hits = 0;
+				}
+				if (cmin <= run + tol && cmin < INFINITY && live) {
+					run = fminf(run, cmin);
+					const float thr = run + tol;
+					unsigned hits = 0;
 #pragma unroll
-						for (int k = 0; k < 32; k++) hits |= (v[k] <= thr ? 1u : 0u) << k;
-						while (hits) {
-							const int k = __ffs(hits) - 1;
-							hits &= hits - 1;
-							s_pend[n_pend * (32 * TC_EPI_WARPS) + e] = col0 + c * 32 + k;
-							if (++n_pend == TC_PEND) flush();
-						}
+					for (int k = 0; k < 32; k++) hits |= (__uint_as_float(r[k]) <= thr ? 1u : 0u) << k;
+					while (hits) {
+						const int k = __ffs(hits) - 1;
+						hits &= hits - 1;
+						s_pend[n_pend * (32 * TC_EPI_WARPS) + e] = col0 + c * 32 + k;
+						if (++n_pend == TC_PEND) flush();
 					}
-				};
-				tmem_ld32_issue(tbase, ra);
-				tmem_ld_wait(ra); tmem_ld32_issue(tbase + 32, rb); reduce(ra, 0);
-				tmem_ld_wait(rb); tmem_ld32_issue(tbase + 64, ra); reduce(rb, 1);
-				tmem_ld_wait(ra); tmem_ld32_issue(tbase + 96, rb); reduce(ra, 2);
-				tmem_ld_wait(rb);
-				tc_fence_before();
-				__syncwarp();
-				if (lane == 0) mbar_arrive(&bar->acc_empty[as]);     // TMEM buffer free: the last chunk lives in registers now
-				reduce(rb, 3);
-			}
-			flush();
+				}
+			};
+			reduce(r0, 0); reduce(r1, 1); reduce(r2, 2); reduce(r3, 3);
+			__syncwarp();
+			if (lane == 0) mbar_arrive(&bar->b_empty[s]);            // this warp is done with the stage's norms
+			if (++t == P.b_tiles) { t = 0; rp++; }
 		}
+		flush();
 	}
 	tc_fence_before();
 	__syncthreads();
@@ -370,7 +373,7 @@ static EncodeTiledFn encode_tiled_fn() {
 	return fn;
 }
 
-// operand matrix [rows_pad][192] bf16, box = 64 elements (one 128-byte swizzle atom) x 128 rows
+// operand matrix [rows_pad][64] bf16, box = 64 elements (one 128-byte swizzle atom) x 128 rows
 static CUtensorMap operand_map(const void* base, int rows_pad) {
 	CUtensorMap m;
 	const cuuint64_t dims[2] = {(cuuint64_t)TC_K, (cuuint64_t)rows_pad};
@@ -389,11 +392,10 @@ size_t tc_operand_bytes(int n) { return (size_t)tc_pad_rows(n) * TC_K * 2; }
 int tc_cand_cap() { return TC_CAND_CAP; }
 bool tc_supported(int dof) { return dof == TC_DOF; }
 
-void launch_tc_split(const double* d_x, int n, int arrangement, void* d_operand, float* d_norm, unsigned* d_max_norm_bits, cudaStream_t st) {
+void launch_tc_split(const double* d_x, int n, void* d_operand, float* d_norm, unsigned* d_max_norm_bits, cudaStream_t st) {
 	const int n_pad = tc_pad_rows(n);
 	BS_CUDA(cudaMemsetAsync(d_max_norm_bits, 0, 4, st));
-	BS_LAUNCH(split_kernel, div_up(n_pad, 8), 256, 0, st, d_x, n, n_pad, arrangement, static_cast<__nv_bfloat16*>(d_operand), d_norm,
-	          d_max_norm_bits);
+	BS_LAUNCH(split_kernel, div_up(n_pad, 8), 256, 0, st, d_x, n, n_pad, static_cast<__nv_bfloat16*>(d_operand), d_norm, d_max_norm_bits);
 }
 
 // rows of A against all rows of B: candidate lists for the rows of A
@@ -401,33 +403,25 @@ void launch_tc_filter(const void* d_opA, const float* d_normA, int nA, const voi
                       const unsigned* d_max_norm_b_bits, int nB, int* d_cand_count, int* d_cand, float* d_dbg, int sm_count,
                       cudaStream_t st, const double* d_row_bound) {
 	if (nA <= 0 || nB <= 0) return;
-	static bool attr_set = false;
-	if (!attr_set) {
-		BS_CUDA(cudaFuncSetAttribute(filter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));
-		attr_set = true;
-	}
+	// the attribute belongs to the device: set it on every launch (a handle may live on any device of the process)
+	BS_CUDA(cudaFuncSetAttribute(filter_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));
+	BS_CUDA(cudaFuncSetAttribute(filter_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));
 	FilterArgs P{};
 	P.nA = nA; P.nB = nB;
-	P.a_tiles256 = tc_pad_rows(nA) / TC_MROWS;
-	P.b_tiles = tc_pad_rows(nB) / TC_BN;
-	// column chunks only when there are fewer 256-row items than SMs: a row's running minimum (and with it the number of
-	// candidates it emits, ~ln(columns/32)) is per item; at least 8 B tiles per item to amortise loading A
-	// — and as many chunks as keep all items in ONE wave of CTAs (a second, mostly empty wave costs a whole item time)
-	int chunks = sm_count / std::max(P.a_tiles256, 1);
-	chunks = std::max(1, std::min(chunks, P.b_tiles / 8 > 0 ? P.b_tiles / 8 : 1));
-	static const int env_chunks = getenv("BS_TC_CHUNKS") ? atoi(getenv("BS_TC_CHUNKS")) : 0;     // experiments
-	if (env_chunks > 0) chunks = std::min(env_chunks, std::max(P.b_tiles, 1));
-	P.tiles_per_chunk = div_up(P.b_tiles, chunks);
-	P.chunks = div_up(P.b_tiles, P.tiles_per_chunk);
+	P.a_blocks = tc_pad_rows(nA) / TC_MROWS;
+	P.b_tiles = div_up(nB, TC_BN);
+	P.opA = static_cast<const __nv_bfloat16*>(d_opA);
 	P.norm_a = d_normA; P.norm_b = d_normB; P.max_norm_b_bits = d_max_norm_b_bits;
 	P.cand_count = d_cand_count; P.cand = d_cand; P.dbg = d_dbg;
-	static const bool no_bound = getenv("BS_TC_NO_BOUND") != nullptr;      // experiments
-	P.row_bound = no_bound ? nullptr : d_row_bound;
-	const CUtensorMap tmA = operand_map(d_opA, tc_pad_rows(nA));
+	P.row_bound = d_row_bound;
 	const CUtensorMap tmB = operand_map(d_opB, tc_pad_rows(nB));
 	BS_CUDA(cudaMemsetAsync(d_cand_count, 0, (size_t)nA * 4, st));
-	const int grid = std::min(P.a_tiles256 * P.chunks, sm_count);
-	BS_LAUNCH(filter_kernel, grid, TC_THREADS, TC_SMEM_BYTES, st, tmA, tmB, P);
+	// one contiguous share of the (row block, tile) sequence per CTA; a CTA that takes a share loads a row block's A, so at least
+	// four tiles per CTA when the problem is small
+	const long long total = (long long)P.a_blocks * P.b_tiles;
+	const int grid = (int)std::max<long long>(1, std::min<long long>(sm_count, total / 4));
+	if (d_dbg) BS_LAUNCH(filter_kernel<true>, grid, TC_THREADS, TC_SMEM_BYTES, st, tmB, P);
+	else BS_LAUNCH(filter_kernel<false>, grid, TC_THREADS, TC_SMEM_BYTES, st, tmB, P);
 }
 
 // bound[j] = min over the rows i that chose column j of fit[i] (exact distances; non-negative doubles order like their bit patterns);

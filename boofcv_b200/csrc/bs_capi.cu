@@ -1109,8 +1109,8 @@ struct bs_assoc {
 		const size_t rows = (size_t)std::max(n, m);
 		cand_count.reserve(rows * 4); cand.reserve(rows * tc_cand_cap() * 4);
 		unsigned* sc = tc_scalars.as<unsigned>();
-		launch_tc_split(src, n, 0, op_src.p, norm_src.as<float>(), sc + 0, st);
-		launch_tc_split(dst, m, 1, op_dst.p, norm_dst.as<float>(), sc + 1, st);
+		launch_tc_split(src, n, op_src.p, norm_src.as<float>(), sc + 0, st);
+		launch_tc_split(dst, m, op_dst.p, norm_dst.as<float>(), sc + 1, st);
 		BS_CUDA(cudaMemsetAsync(sc + 2, 0, 4, st));
 	}
 	// sharded step 1 on the tensor cores: forward pass of the local rows and the column statistics over them (global row

@@ -21,25 +21,45 @@ __device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
 	asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
-// Bounded wait: a protocol bug must not hang the GPU (the box is shared), it traps instead.
+// Bounded wait: a protocol bug must not hang the GPU (the box is shared), it traps instead.  The loop is kept small on purpose
+// (no unrolling, no back-off ladder): try_wait already suspends the thread for a hardware time slice, and the first version of this
+// wait — 64 unrolled polls before a nanosleep — made the filter kernel's epilogue loop 40 KB of code (12 % of its stall samples
+// were instruction fetch).
+__device__ __forceinline__ bool mbar_try_wait(uint32_t addr, uint32_t parity) {
+	uint32_t done;
+	asm volatile(
+	    "{\n\t.reg .pred p;\n\t"
+	    "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+	    "selp.u32 %0, 1, 0, p;\n\t}"
+	    : "=r"(done)
+	    : "r"(addr), "r"(parity)
+	    : "memory");
+	return done != 0;
+}
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
 	const uint32_t addr = smem_u32(bar);
-	for (uint32_t spin = 0; spin < (1u << 26); spin++) {
-		uint32_t done;
-		asm volatile(
-		    "{\n\t.reg .pred p;\n\t"
-		    "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-		    "selp.u32 %0, 1, 0, p;\n\t}"
-		    : "=r"(done)
-		    : "r"(addr), "r"(parity)
-		    : "memory");
-		if (done) return;
-		if (spin > 64) __nanosleep(32);        // keep the issue slots for the warps that do the work
-	}
-	__trap();
+	uint32_t spin = 0;
+#pragma unroll 1
+	while (!mbar_try_wait(addr, parity))
+		if (++spin == (1u << 24)) __trap();
+}
+
+// One lane of the (converged) warp.  A branch on this predicate is the form ptxas recognises as single-thread code: tcgen05.mma /
+// commit operands then go to uniform registers directly.  Behind `if (lane == 0)` every UTCHMMA is wrapped in an ELECT / R2UR /
+// VOTEU loop instead (measured with tools/probe/tc_probe.cu: 112-124 cycles per 128x128x16 MMA against 73 behind elect.sync).
+__device__ __forceinline__ uint32_t elect_one() {
+	uint32_t pred = 0;
+	asm volatile("{\n\t.reg .b32 rx;\n\t.reg .pred px;\n\telect.sync rx|px, %1;\n\t@px mov.s32 %0, 1;\n\t}" : "+r"(pred) : "r"(0xffffffffu));
+	return pred;
 }
 
 // ---------------------------------------------------------------- TMA
+// plain 1-D bulk copy global -> shared (16-byte aligned, size a multiple of 16), completion counted in bytes on `bar`
+__device__ __forceinline__ void bulk_load_1d(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+	asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)),
+	             "l"(reinterpret_cast<uint64_t>(src)), "r"(bytes), "r"(smem_u32(bar))
+	             : "memory");
+}
 __device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* m) {
 	asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(m)) : "memory");
 }
@@ -81,6 +101,16 @@ __device__ __forceinline__ void umma_bf16(uint32_t d_tmem, uint64_t a_desc, uint
 	    "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
 	    : "memory");
 }
+// the same with the A operand in TMEM (lane = row, 32-bit column j = elements k = 2j | 2j+1 of a 16-bit type; a K = 16 step is 8
+// columns): no shared-memory traffic for A.  Measured: 73 cycles per 128x128x16 against 97 with both operands in shared memory.
+__device__ __forceinline__ void umma_bf16_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+	asm volatile(
+	    "{\n\t.reg .pred p;\n\t"
+	    "setp.ne.b32 p, %4, 0;\n\t"
+	    "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}" ::"r"(d_tmem),
+	    "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(accumulate)
+	    : "memory");
+}
 // arrive on `bar` when every tcgen05.mma issued so far by this thread has completed (implies fence::before_thread_sync)
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
 	asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
@@ -105,6 +135,41 @@ __device__ __forceinline__ void tmem_ld_wait(uint32_t (&r)[32]) {
 #define BS_INOUT(k) "+r"(r[k])
 	asm volatile("tcgen05.wait::ld.sync.aligned;" : BS_R32(BS_INOUT)::"memory");
 #undef BS_INOUT
+}
+
+// registers -> TMEM, same shape as tmem_ld32_issue; returns once the store has completed
+__device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t (&r)[32]) {
+#define BS_IN(k) "r"(r[k])
+	asm volatile(
+	    "tcgen05.st.sync.aligned.32x32b.x32.b32 [%32], "
+	    "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+	    "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31};" ::BS_R32(BS_IN),
+	    "r"(taddr)
+	    : "memory");
+#undef BS_IN
+	asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+}
+
+// packed fp32 pair arithmetic and the three-input minimum of sm_100
+__device__ __forceinline__ float2 ffma2(float2 a, float2 b, float2 c) {
+	unsigned long long ra, rb, rc, rd;
+	asm("mov.b64 %0, {%1, %2};" : "=l"(ra) : "f"(a.x), "f"(a.y));
+	asm("mov.b64 %0, {%1, %2};" : "=l"(rb) : "f"(b.x), "f"(b.y));
+	asm("mov.b64 %0, {%1, %2};" : "=l"(rc) : "f"(c.x), "f"(c.y));
+	asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(rd) : "l"(ra), "l"(rb), "l"(rc));
+	float2 d;
+	asm("mov.b64 {%0, %1}, %2;" : "=f"(d.x), "=f"(d.y) : "l"(rd));
+	return d;
+}
+__device__ __forceinline__ float4 lds128(uint32_t addr) {
+	float4 v;
+	asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
+	return v;
+}
+__device__ __forceinline__ float fmin3(float a, float b, float c) {
+	float d;
+	asm("min.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
+	return d;
 }
 
 // ---------------------------------------------------------------- UMMA descriptors

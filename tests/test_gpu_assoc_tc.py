@@ -1,4 +1,4 @@
-"""Tensor-core candidate filter (tcgen05 bf16 hi/lo split) + exact fp64 re-score — bs_assoc mode 1, through the C ABI.
+"""Tensor-core candidate filter (tcgen05, bf16 operands, K = 64) + exact fp64 re-score — bs_assoc mode 1, through the C ABI.
 
 The contract is the reference's (AssociateGreedy.java:65-118): pairs and fit must be BIT-IDENTICAL to the exact kernel and to
 the oracle, whatever the tensor cores round.  The filter only has to keep the exact minimum (and its exact ties) among the
@@ -47,10 +47,10 @@ def test_filter_estimate_stays_inside_its_error_budget(bs):
         scores, cnt, _ = g.filterScores(a, b)
         exact = _exact_scores(a, b)
         na = (a * a).sum(1)[:, None]; nb = (b * b).sum(1)[None, :]
-        budget = 6e-4 * np.sqrt(na * nb) + 1e-6 * (na + nb)     # bs_assoc_tc.cu tolerance_of() is twice this
+        budget = 8e-3 * np.sqrt(na * nb) + 1e-6 * (na + nb)     # bs_assoc_tc.cu tolerance_of() is twice this
         err = np.abs(scores.astype(np.float64) - exact)
         assert np.isfinite(scores).all()
-        assert (err <= budget / 4).all(), float((err / budget).max())
+        assert (err <= 0.75 * budget).all(), float((err / budget).max())     # the budget is a worst-case bound
         assert (cnt >= 1).all() and cnt.max() <= 64
         g.close()
 
