@@ -233,6 +233,7 @@ def run_association(torch, dev, n=100000, reps=3):
     dst = torch.randn((n, 64), generator=g, device=dev, dtype=torch.float64); dst /= dst.norm(dim=1, keepdim=True)
     perm = torch.randperm(n, generator=g, device=dev)
     src = dst[perm] + 0.02 * torch.randn((n, 64), generator=g, device=dev, dtype=torch.float64)
+    src /= src.norm(dim=1, keepdim=True)                       # SURF descriptors are unit vectors (UtilFeature.normalizeL2)
     a = bs.FactoryAssociation.greedy(bs.ScoreAssociateEuclideanSq_F64(), float(np.finfo(np.float64).max), True, device=dev.index or 0)
     a.setMode(1)
     p, _ = a.associateDevice(src, dst)                          # warm-up

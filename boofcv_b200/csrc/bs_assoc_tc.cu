@@ -41,12 +41,17 @@ constexpr int TC_BM = 128, TC_BN = 128;    // one accumulator: 128 x 128, four 1
 constexpr int TC_MROWS = 2 * TC_BM;        // rows per row block (two A halves resident in TMEM)
 constexpr int TC_STAGES = 8;               // B ring
 constexpr int TC_TILE_BYTES = TC_BN * 128; // 16 KB: 128 rows x 128 B
+constexpr int TC_NB = TC_BN + 4;           // norms of a 128-row tile: 128 floats + {all equal?, 0, 0, 0}; see norm_index()
 constexpr int TC_SLOTS = 3;                // accumulators in flight
 constexpr int TC_A_COL = TC_SLOTS * TC_BN; // TMEM columns [384, 448): the two A halves, 32 columns each
 constexpr int TC_EPI_WARPS = 8;
 constexpr int TC_THREADS = 64 + 32 * TC_EPI_WARPS;
 constexpr int TC_CAND_CAP = 64;            // candidates kept per row; more -> the caller falls back to the exact kernel
 constexpr int TC_TMEM_COLS = 512;
+
+// Norms are stored tile by tile, 132 floats per 128 rows: the 128 squared norms, then a flag (non-zero: the 128 are one and the
+// same finite float) and three zeros, so that one bulk copy brings a tile's norms and its flag into shared memory.
+__host__ __device__ __forceinline__ size_t norm_index(int row) { return (size_t)row + (size_t)(row >> 7) * 4; }
 
 // ---------------------------------------------------------------- 1. split
 // Rows >= n (padding up to a multiple of 256) are zero with norm = +inf.
@@ -62,9 +67,21 @@ __global__ void split_kernel(const double* __restrict__ x, int n, int n_pad, __n
 	for (int d = 16; d > 0; d >>= 1) sq += __shfl_xor_sync(0xffffffffu, sq, d);
 	if (lane == 0) {
 		const float f = row < n ? (float)sq : INFINITY;
-		norm[row] = f;
+		norm[norm_index(row)] = f;
 		if (row < n) atomicMax(max_norm_bits, __float_as_uint(f));      // non-negative floats order like their bit patterns
 	}
+}
+// one warp per 128-row tile: flag = the tile's norms are all the same finite value
+__global__ void norm_flags_kernel(float* __restrict__ norm, int tiles) {
+	const int tile = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+	const int lane = threadIdx.x & 31;
+	if (tile >= tiles) return;
+	float* t = norm + (size_t)tile * TC_NB;
+	const float4 v = reinterpret_cast<const float4*>(t)[lane];
+	const float first = __shfl_sync(0xffffffffu, v.x, 0);
+	const bool same = v.x == first && v.y == first && v.z == first && v.w == first && first < INFINITY;
+	const bool all = __all_sync(0xffffffffu, same);
+	if (lane == 0) reinterpret_cast<float4*>(t)[32] = make_float4(all ? 1.0f : 0.0f, 0.0f, 0.0f, 0.0f);
 }
 
 // Bound on |d'_computed - d'_exact| for one pair, d' = |b|^2 - 2 a.b, s = fp32 sum of the 64 products a~_k b~_k:
@@ -104,7 +121,7 @@ struct __align__(8) FilterBarriers {
 };
 
 constexpr int TC_PEND = 8;                // candidates an epilogue thread collects before it reserves slots in its row's list
-constexpr int TC_SMEM_BYTES = 1024 /*alignment slack*/ + TC_STAGES * TC_TILE_BYTES + TC_STAGES * TC_BN * 4 + (int)sizeof(FilterBarriers) +
+constexpr int TC_SMEM_BYTES = 1024 /*alignment slack*/ + TC_STAGES * TC_TILE_BYTES + TC_STAGES * TC_NB * 4 + (int)sizeof(FilterBarriers) +
                               TC_PEND * 32 * TC_EPI_WARPS * 4;
 
 template <bool DBG>
@@ -114,7 +131,7 @@ filter_kernel(const __grid_constant__ CUtensorMap tmB, FilterArgs P) {
 	unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
 	unsigned char* sB = smem;                                                       // [stages][128 rows][128 B]
 	float* s_nb = reinterpret_cast<float*>(sB + TC_STAGES * TC_TILE_BYTES);         // [stages][128]: column norms of the stage's tile
-	FilterBarriers* bar = reinterpret_cast<FilterBarriers*>(s_nb + TC_STAGES * TC_BN);
+	FilterBarriers* bar = reinterpret_cast<FilterBarriers*>(s_nb + TC_STAGES * TC_NB);
 	int* s_pend = reinterpret_cast<int*>(bar + 1);                   // [TC_PEND][256]: pending candidates, one column per epilogue thread
 
 	const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -146,9 +163,9 @@ filter_kernel(const __grid_constant__ CUtensorMap tmB, FilterArgs P) {
 				const int s = n % TC_STAGES;
 				const uint32_t use = n / TC_STAGES;
 				mbar_wait(&bar->b_empty[s], (use & 1) ^ 1);          // the epilogue warps are done with the stage's norms (and the MMAs with its tile)
-				mbar_expect_tx(&bar->b_full[s], TC_TILE_BYTES + TC_BN * 4);
+				mbar_expect_tx(&bar->b_full[s], TC_TILE_BYTES + TC_NB * 4);
 				tma_load_2d(sB + s * TC_TILE_BYTES, &tmB, 0, t * TC_BN, &bar->b_full[s]);
-				bulk_load_1d(s_nb + s * TC_BN, P.norm_b + (size_t)t * TC_BN, TC_BN * 4, &bar->b_full[s]);
+				bulk_load_1d(s_nb + s * TC_NB, P.norm_b + (size_t)t * TC_NB, TC_NB * 4, &bar->b_full[s]);
 				if (++t == P.b_tiles) t = 0;
 			}
 		}
@@ -212,7 +229,7 @@ filter_kernel(const __grid_constant__ CUtensorMap tmB, FilterArgs P) {
 				flush();
 				row = rp * TC_MROWS + h * TC_BM + L;
 				live = row < P.nA;
-				na = live ? P.norm_a[row] : 0.0f;
+				na = live ? P.norm_a[norm_index(row)] : 0.0f;
 				tol = tolerance_of(na, nb_max);
 				// A row's candidates are the columns within tol of its running minimum.  Where the caller knows a distance the row
 				// really attains — the second direction takes it from the first one's matches — the minimum starts there: the true
@@ -251,33 +268,17 @@ filter_kernel(const __grid_constant__ CUtensorMap tmB, FilterArgs P) {
 			tc_fence_before();
 			__syncwarp();
 			if (lane == 0) mbar_arrive(&bar->acc_empty[slot]);
-			const uint32_t nb_addr = smem_u32(s_nb + s * TC_BN);
-			// d' = |b|^2 - 2 s for 32 columns (packed pairs, in place), two minimum chains of three-input minima
-			auto reduce = [&](uint32_t (&r)[32], int c) {
-				float m0 = INFINITY, m1 = INFINITY;
-#pragma unroll
-				for (int k = 0; k < 8; k++) {
-					const float4 b = lds128(nb_addr + (uint32_t)(c * 128 + k * 16));
-					const float2 u = ffma2(make_float2(__uint_as_float(r[4 * k]), __uint_as_float(r[4 * k + 1])), make_float2(-2.0f, -2.0f), make_float2(b.x, b.y));
-					const float2 w = ffma2(make_float2(__uint_as_float(r[4 * k + 2]), __uint_as_float(r[4 * k + 3])), make_float2(-2.0f, -2.0f), make_float2(b.z, b.w));
-					r[4 * k] = __float_as_uint(u.x); r[4 * k + 1] = __float_as_uint(u.y); r[4 * k + 2] = __float_as_uint(w.x); r[4 * k + 3] = __float_as_uint(w.y);
-					m0 = fmin3(m0, u.x, u.y);
-					m1 = fmin3(m1, w.x, w.y);
-				}
-				const float cmin = fminf(m0, m1);
-				if (DBG) {
-					if (P.dbg && live) {
-#pragma unroll
-						for (int k = 0; k < 32; k++)
-							if (col0 + c * 32 + k < P.nB) P.dbg[(size_t)row * P.nB + col0 + c * 32 + k] = __uint_as_float(r[k]) + na;
-					}
-				}
+			const float* nb_tile = s_nb + s * TC_NB;
+			const uint32_t nb_addr = smem_u32(nb_tile);
+			// Candidate path of one 32-column chunk whose minimum came within tol of the row's running minimum (rare once the minimum
+			// has settled: ~1.3 / columns-seen per column).  val(k) = d' of column k of the chunk.
+			auto emit = [&](float cmin, int c, auto val) {
 				if (cmin <= run + tol && cmin < INFINITY && live) {
 					run = fminf(run, cmin);
 					const float thr = run + tol;
 					unsigned hits = 0;
 #pragma unroll
-					for (int k = 0; k < 32; k++) hits |= (__uint_as_float(r[k]) <= thr ? 1u : 0u) << k;
+					for (int k = 0; k < 32; k++) hits |= (val(k) <= thr ? 1u : 0u) << k;
 					while (hits) {
 						const int k = __ffs(hits) - 1;
 						hits &= hits - 1;
@@ -286,7 +287,54 @@ filter_kernel(const __grid_constant__ CUtensorMap tmB, FilterArgs P) {
 					}
 				}
 			};
-			reduce(r0, 0); reduce(r1, 1); reduce(r2, 2); reduce(r3, 3);
+			// SURF descriptors are unit vectors: where the 128 column norms of a tile are one and the same float (flagged by
+			// norm_flags_kernel) min_j (nb - 2 s_j) = nb - 2 max_j s_j (fma is monotonic), and the row maximum of the raw accumulators
+			// is all the fast path needs: half an instruction per element, nothing read from shared memory.
+			if (!DBG && nb_tile[TC_BN] != 0.0f) {
+				const float nbc = nb_tile[0];
+				auto row_max = [&](const uint32_t (&r)[32]) {
+					float a[11];
+#pragma unroll
+					for (int i = 0; i < 10; i++) a[i] = fmax3(__uint_as_float(r[3 * i]), __uint_as_float(r[3 * i + 1]), __uint_as_float(r[3 * i + 2]));
+					a[10] = fmaxf(__uint_as_float(r[30]), __uint_as_float(r[31]));
+					const float b0 = fmax3(a[0], a[1], a[2]), b1 = fmax3(a[3], a[4], a[5]), b2 = fmax3(a[6], a[7], a[8]), b3 = fmaxf(a[9], a[10]);
+					return fmaf(-2.0f, fmaxf(fmax3(b0, b1, b2), b3), nbc);
+				};
+				const float c0 = row_max(r0), c1 = row_max(r1), c2 = row_max(r2), c3 = row_max(r3);
+				emit(c0, 0, [&](int k) { return fmaf(-2.0f, __uint_as_float(r0[k]), nbc); });
+				emit(c1, 1, [&](int k) { return fmaf(-2.0f, __uint_as_float(r1[k]), nbc); });
+				emit(c2, 2, [&](int k) { return fmaf(-2.0f, __uint_as_float(r2[k]), nbc); });
+				emit(c3, 3, [&](int k) { return fmaf(-2.0f, __uint_as_float(r3[k]), nbc); });
+			} else {
+				// general norms: d' = |b_j|^2 - 2 s_j in place (packed pairs), then the same tree of three-input minima
+				auto row_min = [&](uint32_t (&r)[32], int c) {
+#pragma unroll
+					for (int k = 0; k < 8; k++) {
+						const float4 b = lds128(nb_addr + (uint32_t)(c * 128 + k * 16));
+						const float2 u = ffma2(make_float2(__uint_as_float(r[4 * k]), __uint_as_float(r[4 * k + 1])), make_float2(-2.0f, -2.0f), make_float2(b.x, b.y));
+						const float2 w = ffma2(make_float2(__uint_as_float(r[4 * k + 2]), __uint_as_float(r[4 * k + 3])), make_float2(-2.0f, -2.0f), make_float2(b.z, b.w));
+						r[4 * k] = __float_as_uint(u.x); r[4 * k + 1] = __float_as_uint(u.y); r[4 * k + 2] = __float_as_uint(w.x); r[4 * k + 3] = __float_as_uint(w.y);
+					}
+					float a[11];
+#pragma unroll
+					for (int i = 0; i < 10; i++) a[i] = fmin3(__uint_as_float(r[3 * i]), __uint_as_float(r[3 * i + 1]), __uint_as_float(r[3 * i + 2]));
+					a[10] = fminf(__uint_as_float(r[30]), __uint_as_float(r[31]));
+					const float b0 = fmin3(a[0], a[1], a[2]), b1 = fmin3(a[3], a[4], a[5]), b2 = fmin3(a[6], a[7], a[8]), b3 = fminf(a[9], a[10]);
+					if (DBG) {
+						if (P.dbg && live) {
+#pragma unroll
+							for (int k = 0; k < 32; k++)
+								if (col0 + c * 32 + k < P.nB) P.dbg[(size_t)row * P.nB + col0 + c * 32 + k] = __uint_as_float(r[k]) + na;
+						}
+					}
+					return fminf(fmin3(b0, b1, b2), b3);
+				};
+				const float c0 = row_min(r0, 0), c1 = row_min(r1, 1), c2 = row_min(r2, 2), c3 = row_min(r3, 3);
+				emit(c0, 0, [&](int k) { return __uint_as_float(r0[k]); });
+				emit(c1, 1, [&](int k) { return __uint_as_float(r1[k]); });
+				emit(c2, 2, [&](int k) { return __uint_as_float(r2[k]); });
+				emit(c3, 3, [&](int k) { return __uint_as_float(r3[k]); });
+			}
 			__syncwarp();
 			if (lane == 0) mbar_arrive(&bar->b_empty[s]);            // this warp is done with the stage's norms
 			if (++t == P.b_tiles) { t = 0; rp++; }
@@ -389,6 +437,7 @@ static CUtensorMap operand_map(const void* base, int rows_pad) {
 
 int tc_pad_rows(int n) { return ((n + TC_MROWS - 1) / TC_MROWS) * TC_MROWS; }
 size_t tc_operand_bytes(int n) { return (size_t)tc_pad_rows(n) * TC_K * 2; }
+size_t tc_norm_bytes(int n) { return (size_t)(tc_pad_rows(n) / TC_BN) * TC_NB * 4; }
 int tc_cand_cap() { return TC_CAND_CAP; }
 bool tc_supported(int dof) { return dof == TC_DOF; }
 
@@ -396,6 +445,7 @@ void launch_tc_split(const double* d_x, int n, void* d_operand, float* d_norm, u
 	const int n_pad = tc_pad_rows(n);
 	BS_CUDA(cudaMemsetAsync(d_max_norm_bits, 0, 4, st));
 	BS_LAUNCH(split_kernel, div_up(n_pad, 8), 256, 0, st, d_x, n, n_pad, static_cast<__nv_bfloat16*>(d_operand), d_norm, d_max_norm_bits);
+	BS_LAUNCH(norm_flags_kernel, div_up(n_pad / TC_BN, 8), 256, 0, st, d_norm, n_pad / TC_BN);
 }
 
 // rows of A against all rows of B: candidate lists for the rows of A

@@ -1104,7 +1104,7 @@ struct bs_assoc {
 	}
 	void tc_prepare(const double* src, int n, const double* dst, int m, cudaStream_t st) {
 		op_src.reserve(tc_operand_bytes(n)); op_dst.reserve(tc_operand_bytes(m));
-		norm_src.reserve((size_t)tc_pad_rows(n) * 4); norm_dst.reserve((size_t)tc_pad_rows(m) * 4);
+		norm_src.reserve(tc_norm_bytes(n)); norm_dst.reserve(tc_norm_bytes(m));
 		tc_scalars.reserve(16);
 		const size_t rows = (size_t)std::max(n, m);
 		cand_count.reserve(rows * 4); cand.reserve(rows * tc_cand_cap() * 4);
@@ -1137,7 +1137,7 @@ struct bs_assoc {
 	// workspace of the tensor-core path for problems up to n x m (so that queued runs never reallocate under a running kernel)
 	void tc_reserve(int n, int m) {
 		op_src.reserve(tc_operand_bytes(n)); op_dst.reserve(tc_operand_bytes(m));
-		norm_src.reserve((size_t)tc_pad_rows(n) * 4); norm_dst.reserve((size_t)tc_pad_rows(m) * 4);
+		norm_src.reserve(tc_norm_bytes(n)); norm_dst.reserve(tc_norm_bytes(m));
 		tc_scalars.reserve(16);
 		const size_t rows = (size_t)std::max(n, m);
 		cand_count.reserve(rows * 4); cand.reserve(rows * tc_cand_cap() * 4);

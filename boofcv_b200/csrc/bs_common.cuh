@@ -194,6 +194,7 @@ struct RowminScratch { double* p_min; int* p_first; int* p_last; long cap; };
 bool tc_supported(int dof);
 int tc_pad_rows(int n);
 size_t tc_operand_bytes(int n);
+size_t tc_norm_bytes(int n);
 int tc_cand_cap();
 void launch_tc_split(const double* d_x, int n, void* d_operand, float* d_norm, unsigned* d_max_norm_bits, cudaStream_t st);
 void launch_tc_filter(const void* d_opA, const float* d_normA, int nA, const void* d_opB, const float* d_normB,

@@ -166,6 +166,11 @@ __device__ __forceinline__ float4 lds128(uint32_t addr) {
 	asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
 	return v;
 }
+__device__ __forceinline__ float fmax3(float a, float b, float c) {
+	float d;
+	asm("max.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
+	return d;
+}
 __device__ __forceinline__ float fmin3(float a, float b, float c) {
 	float d;
 	asm("min.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
