@@ -84,6 +84,7 @@ SIGNATURES = {
     "bs_assoc_filter_scores": (_i, [_vp, _vp, _i, _vp, _i, _i, _vp, _vp, _vp]),
     "bs_assoc_run": (_i, [_vp, _vp, _i, _vp, _i, _i, _vp, _vp]),
     "bs_assoc_run_device": (_i, [_vp, _vp, _i, _vp, _i, _i, _vp, _vp, _vp]),
+    "bs_assoc_forward_static": (_i, [_i, _vp, _i, _vp, _i, _i, _d, _vp, _vp, _vp]),
     "bs_assoc_forward_device": (_i, [_vp, _vp, _i, _i, _vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp]),
     "bs_assoc_merge_columns_device": (_i, [_vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "bs_assoc_validate_device": (_i, [_vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp]),

@@ -223,3 +223,103 @@ void launch_merge_columns(int ranks, int m, const double* a_min, const int32_t* 
 }
 
 }  // namespace bs
+
+// ====================================================================================================================
+// bs_assoc_forward_static — forward greedy association that allocates NOTHING.  No counterpart in the reference: added
+// for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
+// serving loops, harnesses that forbid it).  Same kernels and the same results as the exact path of bs_assoc_run_device
+// without backward validation; the split partials live in a file-scope device array instead of the handle's workspace.
+//
+// The array exists once per GPU that loads the library (4 MiB, held until exit).  Its NAME is a host-side stand-in in
+// host code, not a device address: the address is resolved once per device with cudaGetSymbolAddress (that device
+// current) and passed to the kernels.  Every call shares the array: calls that overlap on the GPU (two streams, two host
+// threads, two processes' worth of handles on one context) race on it — serialise them.  Nothing in it has to start at
+// zero: every entry the finalize pass reads is written by the tile pass of the same call, so the previous call's contents
+// are never observed.
+// ====================================================================================================================
+#include <mutex>
+
+namespace {
+
+constexpr long kStaticEntries = 2L * BS_ASSOC_STATIC_MAX_ROWS;           // split partials: (min, first, last) per (split, row)
+constexpr size_t kStaticBytes = (size_t)kStaticEntries * 16;            // 8 + 4 + 4 bytes per entry = 4 MiB
+
+}  // namespace
+
+static __device__ __align__(256) unsigned char g_assoc_static_scratch[kStaticBytes];
+
+namespace {
+
+constexpr int kMaxDevices = 64;
+std::mutex g_static_mu;
+unsigned char* g_static_ptr[kMaxDevices];     // device address of g_assoc_static_scratch on each device (nullptr: not set up yet)
+int g_static_sms[kMaxDevices];
+
+struct CurrentDevice {                         // make `dev` current for the scope of the call
+	int prev = -1;
+	explicit CurrentDevice(int dev) {
+		BS_CUDA(cudaGetDevice(&prev));
+		if (prev != dev) BS_CUDA(cudaSetDevice(dev)); else prev = -1;
+	}
+	~CurrentDevice() { if (prev >= 0) cudaSetDevice(prev); }
+};
+
+// once per device, with that device current: the array's device address, the kernel's shared-memory opt-in, the SM count
+unsigned char* static_scratch_of(int device, int* sms) {
+	std::lock_guard<std::mutex> lock(g_static_mu);
+	if (!g_static_ptr[device]) {
+		unsigned char* p = nullptr;
+		const cudaError_t e = cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_assoc_static_scratch);
+		if (e != cudaSuccess || !p) bs::fail(BS_ERR_CUDA, std::string("cudaGetSymbolAddress(static association scratch): ") + cudaGetErrorString(e));
+		BS_CUDA(cudaFuncSetAttribute(bs::rowmin_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+		                             (int)(((size_t)bs::AMAX_DOF * bs::APAD + (size_t)bs::AK * bs::APAD) * sizeof(double))));
+		BS_CUDA(cudaDeviceGetAttribute(&g_static_sms[device], cudaDevAttrMultiProcessorCount, device));
+		g_static_ptr[device] = p;
+	}
+	*sms = g_static_sms[device];
+	return g_static_ptr[device];
+}
+
+}  // namespace
+
+extern "C" int bs_assoc_forward_static(int device, const double* d_src, int n, const double* d_dst, int m, int dof, double max_fit_error,
+                                       int32_t* d_pairs, double* d_fit, void* stream) {
+	using namespace bs;
+	try {
+		if (n < 0 || m < 0) fail(BS_ERR_ARG, "bad sizes");
+		if (dof < 1 || dof > AMAX_DOF) fail(BS_ERR_ARG, "descriptor length must be in [1,256]");
+		if (n > BS_ASSOC_STATIC_MAX_ROWS)
+			fail(BS_ERR_ARG, "bs_assoc_forward_static: " + std::to_string(n) + " source rows exceed the static scratch (BS_ASSOC_STATIC_MAX_ROWS = " +
+			                          std::to_string(BS_ASSOC_STATIC_MAX_ROWS) + "); use bs_assoc_run_device");
+		if (n == 0) return BS_OK;
+		if (!d_src || !d_pairs || !d_fit || (m > 0 && !d_dst)) fail(BS_ERR_ARG, "null argument");
+		int ndev = 0;
+		BS_CUDA(cudaGetDeviceCount(&ndev));
+		if (device < 0 || device >= ndev || device >= kMaxDevices) fail(BS_ERR_ARG, "no such CUDA device");
+		CurrentDevice cur(device);
+		int sms = 0;
+		unsigned char* scratch = static_scratch_of(device, &sms);
+		RowminScratch s{reinterpret_cast<double*>(scratch), reinterpret_cast<int*>(scratch + (size_t)kStaticEntries * 8),
+		                reinterpret_cast<int*>(scratch + (size_t)kStaticEntries * 12), kStaticEntries};
+		cudaStream_t st = static_cast<cudaStream_t>(stream);
+		int splits = 0;                               // m == 0: nothing to score, finalize alone writes -1 / max_fit_error
+		if (m > 0) {
+			splits = rowmin_splits(n, m, sms);
+			if ((long)splits * n > kStaticEntries) splits = (int)(kStaticEntries / n);      // >= 2: n <= kStaticEntries / 2
+			int per = div_up(div_up(m, splits), AT) * AT;
+			if (per < AT) per = AT;
+			splits = div_up(m, per);                  // no empty trailing split
+			const size_t smem = ((size_t)dof * APAD + (size_t)AK * APAD) * sizeof(double);
+			BS_LAUNCH(rowmin_tile_kernel, dim3(div_up(n, AT), splits), ATHREADS, smem, st, d_src, n, d_dst, m, dof, per, s.p_min, s.p_first, s.p_last);
+		}
+		BS_LAUNCH(rowmin_finalize_kernel, div_up(n, 256), 256, 0, st, s.p_min, s.p_first, s.p_last, n, splits, 0, max_fit_error, 0, d_pairs, d_fit,
+		          (double*)nullptr, (int32_t*)nullptr, (int32_t*)nullptr);
+		return BS_OK;
+	} catch (const bs::Error& e) {
+		bs::set_last_error(e.what());
+		return e.code;
+	} catch (const std::exception& e) {
+		bs::set_last_error(e.what());
+		return BS_ERR_CUDA;
+	}
+}

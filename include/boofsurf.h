@@ -254,6 +254,22 @@ int bs_assoc_run(bs_assoc* a, const double* src, int n, const double* dst, int m
 int bs_assoc_run_device(bs_assoc* a, const double* d_src, int n, const double* d_dst, int m, int dof,
                         int32_t* d_pairs, double* d_fit, void* stream);
 
+/* Forward greedy association on device pointers that ALLOCATES NOTHING (no cudaMalloc / cudaFree, no handle): for callers
+ * that cannot allocate — code under CUDA graph capture, tight serving loops, harnesses that forbid it.  This entry point
+ * has no counterpart in the reference.
+ * Results: exactly those of bs_assoc_run_device on a handle in exact mode without backward validation
+ * (d_pairs[i] = the LAST index of d_dst attaining row i's minimum exact fp64 score if that score <= max_fit_error, else
+ * -1; d_fit[i] = that score, else max_fit_error).  Asynchronous on `stream` (NULL = the legacy default stream).
+ * The split partials of the tile kernel live in a file-scope device array of 4 MiB that every GPU loading the library
+ * holds until exit; hence the limits: n <= BS_ASSOC_STATIC_MAX_ROWS source rows (any m, 1 <= dof <= 256), BS_ERR_ARG with
+ * a message naming the limit beyond it.  Every call shares that array and it keeps the last call's contents (nothing in it
+ * needs clearing: each call overwrites what it reads): calls that OVERLAP on the GPU race on it — issue them on one
+ * stream or order them with events.  The first call on a device resolves the array's address and opts the kernel into its
+ * shared-memory size (no allocation either); make it outside a graph capture. */
+#define BS_ASSOC_STATIC_MAX_ROWS 131072
+int bs_assoc_forward_static(int device, const double* d_src, int n, const double* d_dst, int m, int dof,
+                            double max_fit_error, int32_t* d_pairs, double* d_fit, void* stream);
+
 /* detect -> associate on the device: source = the features of frame_src, destination = those of frame_dst of the last
  * batch `s` detected (same device as `a`), i.e. the frame-to-frame use of the pair of interfaces by the reference's callers
  * (ExampleAssociatePoints.java:125-160, DetectDescribeAssociate): no descriptor leaves the GPU.  surf_basic != 0 splits by
