@@ -56,6 +56,7 @@ SIGNATURES = {
     "bs_surf_destroy": (_i, [_vp]),
     "bs_surf_set_workspace": (_i, [_vp, _i, _l]),
     "bs_surf_set_ways": (_i, [_vp, _i]),
+    "bs_surf_set_walk_scratch": (_i, [_vp, _l]),
     "bs_surf_detect": (_i, [_vp, _vp, _i, _i, _i, _i]),
     "bs_surf_create_planar": (_i, [_i, C.POINTER(FhCfg), C.POINTER(OriCfg), C.POINTER(DescCfg), _i, _i, C.POINTER(_vp)]),
     "bs_surf_detect_planar": (_i, [_vp, C.POINTER(_vp), _i, _i, _i, _i, _i]),

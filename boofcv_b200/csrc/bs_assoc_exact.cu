@@ -194,12 +194,9 @@ void launch_rowmin(const double* A, int nA, const double* B, int nB, int dof, in
 	int per = div_up(div_up(nB, splits), AT) * AT;
 	if (per < AT) per = AT;
 	const size_t smem = ((size_t)dof * APAD + (size_t)AK * APAD) * sizeof(double);
-	static bool attr_set = false;
-	if (!attr_set) {
-		BS_CUDA(cudaFuncSetAttribute(rowmin_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-		                             (int)(((size_t)AMAX_DOF * APAD + (size_t)AK * APAD) * sizeof(double))));
-		attr_set = true;
-	}
+	// per-device attribute: set on every launch (a handle may live on any device of the process)
+	BS_CUDA(cudaFuncSetAttribute(rowmin_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+	                             (int)(((size_t)AMAX_DOF * APAD + (size_t)AK * APAD) * sizeof(double))));
 	BS_LAUNCH(rowmin_tile_kernel, dim3(div_up(nA, AT), splits), ATHREADS, smem, st, A, nA, B, nB, dof, per, s.p_min, s.p_first,
 	          s.p_last);
 }

@@ -19,9 +19,13 @@
 // accumulator back costs far less than producing it (tcgen05.ld: ~880 B/cycle/SM).  So: the 256 rows of a row block live in
 // TMEM as the A operand (written there by the epilogue threads with tcgen05.st), B tiles stream through an 8-stage TMA ring
 // together with their column norms, three 128-column accumulators rotate between the MMA issuer and two epilogue groups.
-// Roles inside the CTA (320 threads): warp 0 = TMA producer, warp 1 = MMA issuer (one elected thread), warps 2-5 / 6-9 =
-// epilogue of the first / second 128 rows (one TMEM lane = one row per thread).  The work of a launch is the sequence of
-// (row block, B tile) pairs in row-block-major order, cut into one contiguous range per CTA: equal shares whatever the shape.
+// Roles inside the CTA (576 threads): warp 0 = TMA producer, warp 1 = MMA issuer (one elected thread), warps 2-17 = epilogue in
+// four groups of four warps (a group covers the four TMEM lane quarters): group g takes the accumulators of A half g >> 1 and
+// the 64 columns g & 1 of each — one TMEM lane = one row per thread, two threads per row.  An epilogue warp's serial chain per
+// accumulator (barrier wake-up, tcgen05.ld round trip, the reduction) was longer than the two MMAs it has to keep up with when
+// eight warps shared the work (650 vs 584 cycles: the filter ran at 45 % of the MMA rate); sixteen warps halve the chain.
+// The two threads of a row exchange their running minima through shared memory once per tile.  The work of a launch is the
+// sequence of (row block, B tile) pairs in row-block-major order, cut into one contiguous range per CTA.
 #include "bs_common.cuh"
 #include <cstdlib>
 #include "bs_sm100.cuh"
@@ -44,7 +48,8 @@ constexpr int TC_TILE_BYTES = TC_BN * 128; // 16 KB: 128 rows x 128 B
 constexpr int TC_NB = TC_BN + 4;           // norms of a 128-row tile: 128 floats + {all equal?, 0, 0, 0}; see norm_index()
 constexpr int TC_SLOTS = 3;                // accumulators in flight
 constexpr int TC_A_COL = TC_SLOTS * TC_BN; // TMEM columns [384, 448): the two A halves, 32 columns each
-constexpr int TC_EPI_WARPS = 8;
+constexpr int TC_EPI_WARPS = 16;           // four groups: (A half) x (column half)
+constexpr int TC_EC = TC_BN / 2;           // columns of an accumulator one epilogue thread reduces
 constexpr int TC_THREADS = 64 + 32 * TC_EPI_WARPS;
 constexpr int TC_CAND_CAP = 64;            // candidates kept per row; more -> the caller falls back to the exact kernel
 constexpr int TC_TMEM_COLS = 512;
@@ -55,8 +60,7 @@ __host__ __device__ __forceinline__ size_t norm_index(int row) { return (size_t)
 
 // ---------------------------------------------------------------- 1. split
 // Rows >= n (padding up to a multiple of 256) are zero with norm = +inf.
-__global__ void split_kernel(const double* __restrict__ x, int n, int n_pad, __nv_bfloat16* __restrict__ out, float* __restrict__ norm,
-                             unsigned* __restrict__ max_norm_bits) {
+__global__ void split_kernel(const double* __restrict__ x, int n, int n_pad, __nv_bfloat16* __restrict__ out, float* __restrict__ norm) {
 	const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
 	const int lane = threadIdx.x & 31;
 	if (row >= n_pad) return;
@@ -65,14 +69,11 @@ __global__ void split_kernel(const double* __restrict__ x, int n, int n_pad, __n
 	reinterpret_cast<__nv_bfloat162*>(out + (size_t)row * TC_K)[lane] = __nv_bfloat162(__double2bfloat16(v.x), __double2bfloat16(v.y));
 	double sq = v.x * v.x + v.y * v.y;
 	for (int d = 16; d > 0; d >>= 1) sq += __shfl_xor_sync(0xffffffffu, sq, d);
-	if (lane == 0) {
-		const float f = row < n ? (float)sq : INFINITY;
-		norm[norm_index(row)] = f;
-		if (row < n) atomicMax(max_norm_bits, __float_as_uint(f));      // non-negative floats order like their bit patterns
-	}
+	if (lane == 0) norm[norm_index(row)] = row < n ? (float)sq : INFINITY;
 }
-// one warp per 128-row tile: flag = the tile's norms are all the same finite value
-__global__ void norm_flags_kernel(float* __restrict__ norm, int tiles) {
+// one warp per 128-row tile: flag = the tile's norms are all the same finite value; the largest norm of the real rows (one atomic
+// per tile: one per row in split_kernel was 100 k atomics on one address, 60 of that kernel's 70 us at 100 k rows)
+__global__ void norm_flags_kernel(float* __restrict__ norm, int tiles, int n, unsigned* __restrict__ max_norm_bits) {
 	const int tile = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
 	const int lane = threadIdx.x & 31;
 	if (tile >= tiles) return;
@@ -82,6 +83,14 @@ __global__ void norm_flags_kernel(float* __restrict__ norm, int tiles) {
 	const bool same = v.x == first && v.y == first && v.z == first && v.w == first && first < INFINITY;
 	const bool all = __all_sync(0xffffffffu, same);
 	if (lane == 0) reinterpret_cast<float4*>(t)[32] = make_float4(all ? 1.0f : 0.0f, 0.0f, 0.0f, 0.0f);
+	const int r0 = tile * TC_BN + lane * 4;
+	unsigned mx = 0;                                                 // non-negative floats order like their bit patterns
+	if (r0 < n) mx = __float_as_uint(v.x);
+	if (r0 + 1 < n) mx = max(mx, __float_as_uint(v.y));
+	if (r0 + 2 < n) mx = max(mx, __float_as_uint(v.z));
+	if (r0 + 3 < n) mx = max(mx, __float_as_uint(v.w));
+	mx = __reduce_max_sync(0xffffffffu, mx);
+	if (lane == 0 && mx) atomicMax(max_norm_bits, mx);
 }
 
 // Bound on |d'_computed - d'_exact| for one pair, d' = |b|^2 - 2 a.b, s = fp32 sum of the 64 products a~_k b~_k:
@@ -122,7 +131,7 @@ struct __align__(8) FilterBarriers {
 
 constexpr int TC_PEND = 8;                // candidates an epilogue thread collects before it reserves slots in its row's list
 constexpr int TC_SMEM_BYTES = 1024 /*alignment slack*/ + TC_STAGES * TC_TILE_BYTES + TC_STAGES * TC_NB * 4 + (int)sizeof(FilterBarriers) +
-                              TC_PEND * 32 * TC_EPI_WARPS * 4;
+                              TC_PEND * 32 * TC_EPI_WARPS * 4 + TC_MROWS * 2 * 8;
 
 template <bool DBG>
 __global__ void __launch_bounds__(TC_THREADS, 1)
@@ -132,15 +141,18 @@ filter_kernel(const __grid_constant__ CUtensorMap tmB, FilterArgs P) {
 	unsigned char* sB = smem;                                                       // [stages][128 rows][128 B]
 	float* s_nb = reinterpret_cast<float*>(sB + TC_STAGES * TC_TILE_BYTES);         // [stages][128]: column norms of the stage's tile
 	FilterBarriers* bar = reinterpret_cast<FilterBarriers*>(s_nb + TC_STAGES * TC_NB);
-	int* s_pend = reinterpret_cast<int*>(bar + 1);                   // [TC_PEND][256]: pending candidates, one column per epilogue thread
+	int* s_pend = reinterpret_cast<int*>(bar + 1);                   // [TC_PEND][512]: pending candidates, one column per epilogue thread
+	unsigned long long* s_run = reinterpret_cast<unsigned long long*>(s_pend + TC_PEND * 32 * TC_EPI_WARPS);   // [256 rows][2]: {running minimum, row block}
 
 	const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 	if (threadIdx.x == 0) {
-		mbar_init(&bar->a_full, TC_EPI_WARPS);
+		mbar_init(&bar->a_full, TC_EPI_WARPS / 2);                   // the warps that write A: column half 0 of both A halves
 		for (int s = 0; s < TC_STAGES; s++) { mbar_init(&bar->b_full[s], 1); mbar_init(&bar->b_empty[s], TC_EPI_WARPS); }
 		for (int s = 0; s < TC_SLOTS; s++) { mbar_init(&bar->acc_full[s], 1); mbar_init(&bar->acc_empty[s], TC_EPI_WARPS / 2); }
 		mbar_fence_init();
 	}
+	// no row block yet in the running-minimum exchange (shared memory keeps what the previous kernel left there)
+	for (int i = threadIdx.x; i < TC_MROWS * 2; i += TC_THREADS) s_run[i] = ~0ull;
 	__syncwarp();
 	if (warp == 0) tmem_alloc<TC_TMEM_COLS>(&bar->tmem_base);
 	tc_fence_before();
@@ -200,18 +212,21 @@ filter_kernel(const __grid_constant__ CUtensorMap tmB, FilterArgs P) {
 			}
 		}
 	} else {
-		// ===== epilogue: warps 2..9.  TMEM lane quarter = warp % 4 (hardware rule); warps 2-5 take A half 0, 6-9 A half 1 =====
+		// ===== epilogue: warps 2..17.  TMEM lane quarter = warp % 4 (hardware rule); group = (warp - 2) / 4 =====
 		const int q = warp & 3;
-		const int h = (warp - 2) >> 2;
-		const int e = (warp - 2) * 32 + lane;                        // 0..255 among the epilogue threads
+		const int g = (warp - 2) >> 2;
+		const int h = g >> 1;                                        // A half (rows h*128 .. h*128+127 of the row block)
+		const int ch = g & 1;                                        // column half of every accumulator
+		const int e = (warp - 2) * 32 + lane;                        // 0..511 among the epilogue threads
 		const int L = q * 32 + lane;                                 // TMEM lane = row inside the 128-row half
 		const uint32_t lane_base = tmem + ((uint32_t)(q * 32) << 16);
+		const uint32_t run_mine = smem_u32(s_run + (h * TC_BM + L) * 2 + ch), run_other = smem_u32(s_run + (h * TC_BM + L) * 2 + (ch ^ 1));
 		const float nb_max = __uint_as_float(*P.max_norm_b_bits);
 		int rp = rp0, t = t0;
 		int row = 0;
 		bool live = false;
 		float na = 0.0f, tol = 0.0f, run = INFINITY;
-		// Candidates are collected per thread (a row belongs to one thread inside a segment) and appended to the row's list
+		// Candidates are collected per thread (a row belongs to two threads inside a segment) and appended to the row's list
 		// TC_PEND at a time: ONE atomicAdd reserves the slots, the stores do not depend on each other.
 		int n_pend = 0;
 		auto flush = [&]() {
@@ -224,8 +239,7 @@ filter_kernel(const __grid_constant__ CUtensorMap tmB, FilterArgs P) {
 		};
 		for (int n = 0; n < n_tiles; n++) {
 			if (t == 0 || n == 0) {
-				// ---- new row block: this thread's row goes into TMEM as a row of the A operand (lane = row, column j = k 2j | 2j+1).
-				// The MMAs that read this half of the previous block have completed: this warp waited for the last of them.
+				// ---- new row block
 				flush();
 				row = rp * TC_MROWS + h * TC_BM + L;
 				live = row < P.nA;
@@ -240,36 +254,49 @@ filter_kernel(const __grid_constant__ CUtensorMap tmB, FilterArgs P) {
 					const double ub = P.row_bound[row];
 					if (ub < 1e30) run = __double2float_ru(ub) - na + 0.25f * tol;
 				}
-				uint32_t ar[32];
-				const uint4* src = reinterpret_cast<const uint4*>(P.opA + (size_t)row * TC_K);     // the operand is padded to whole row blocks
+				if (ch == 0) {
+					// this thread's row goes into TMEM as a row of the A operand (lane = row, column j = k 2j | 2j+1).  The MMAs that
+					// read this half of the previous block have completed: this warp waited for the last of them.
+					uint32_t ar[32];
+					const uint4* src = reinterpret_cast<const uint4*>(P.opA + (size_t)row * TC_K);     // the operand is padded to whole row blocks
 #pragma unroll
-				for (int i = 0; i < 8; i++) {
-					const uint4 v = __ldg(src + i);
-					ar[4 * i] = v.x; ar[4 * i + 1] = v.y; ar[4 * i + 2] = v.z; ar[4 * i + 3] = v.w;
+					for (int i = 0; i < 8; i++) {
+						const uint4 v = __ldg(src + i);
+						ar[4 * i] = v.x; ar[4 * i + 1] = v.y; ar[4 * i + 2] = v.z; ar[4 * i + 3] = v.w;
+					}
+					tmem_st32(lane_base + (uint32_t)(TC_A_COL + h * (TC_K / 2)), ar);
+					tc_fence_before();
+					__syncwarp();
+					if (lane == 0) mbar_arrive(&bar->a_full);
 				}
-				tmem_st32(lane_base + (uint32_t)(TC_A_COL + h * (TC_K / 2)), ar);
-				tc_fence_before();
-				__syncwarp();
-				if (lane == 0) mbar_arrive(&bar->a_full);
 			}
 			const int s = n % TC_STAGES;
 			const uint32_t m = 2u * (uint32_t)n + (uint32_t)h;
 			const uint32_t slot = m % TC_SLOTS;
-			const int col0 = t * TC_BN;
+			const int col0 = t * TC_BN + ch * TC_EC;
+			// The row's other thread (the other 64 columns of every tile) shares its running minimum: a value tagged with the row block
+			// it belongs to, one 64-bit shared-memory word per thread.  A stale value is still a valid (looser) bound.
+			{
+				const unsigned long long mine = ((unsigned long long)(uint32_t)rp << 32) | __float_as_uint(run);
+				unsigned long long other;
+				asm volatile("st.shared.b64 [%0], %1;" ::"r"(run_mine), "l"(mine) : "memory");
+				asm volatile("ld.shared.b64 %0, [%1];" : "=l"(other) : "r"(run_other) : "memory");
+				if ((int)(other >> 32) == rp) run = fminf(run, __uint_as_float((uint32_t)other));
+			}
 			mbar_wait(&bar->b_full[s], (n / TC_STAGES) & 1);         // the stage's norms have landed (long since: the MMAs needed its tile)
 			mbar_wait(&bar->acc_full[slot], (m / TC_SLOTS) & 1);
 			tc_fence_after();
-			// The whole accumulator row (128 columns) is fetched at once and the accumulator handed back to the MMA issuer before any
+			// This thread's 64 columns are fetched at once and the accumulator handed back to the MMA issuer before any
 			// arithmetic: the slot is held for one TMEM round trip, not for the reduction.
-			const uint32_t tbase = lane_base + slot * TC_BN;
-			uint32_t r0[32], r1[32], r2[32], r3[32];
-			tmem_ld32_issue(tbase, r0); tmem_ld32_issue(tbase + 32, r1); tmem_ld32_issue(tbase + 64, r2); tmem_ld32_issue(tbase + 96, r3);
-			tmem_ld_wait(r0); tmem_ld_wait(r1); tmem_ld_wait(r2); tmem_ld_wait(r3);
+			const uint32_t tbase = lane_base + slot * TC_BN + ch * TC_EC;
+			uint32_t r0[32], r1[32];
+			tmem_ld32_issue(tbase, r0); tmem_ld32_issue(tbase + 32, r1);
+			tmem_ld_wait(r0); tmem_ld_wait(r1);
 			tc_fence_before();
 			__syncwarp();
 			if (lane == 0) mbar_arrive(&bar->acc_empty[slot]);
 			const float* nb_tile = s_nb + s * TC_NB;
-			const uint32_t nb_addr = smem_u32(nb_tile);
+			const uint32_t nb_addr = smem_u32(nb_tile + ch * TC_EC);
 			// Candidate path of one 32-column chunk whose minimum came within tol of the row's running minimum (rare once the minimum
 			// has settled: ~1.3 / columns-seen per column).  val(k) = d' of column k of the chunk.
 			auto emit = [&](float cmin, int c, auto val) {
@@ -300,11 +327,9 @@ filter_kernel(const __grid_constant__ CUtensorMap tmB, FilterArgs P) {
 					const float b0 = fmax3(a[0], a[1], a[2]), b1 = fmax3(a[3], a[4], a[5]), b2 = fmax3(a[6], a[7], a[8]), b3 = fmaxf(a[9], a[10]);
 					return fmaf(-2.0f, fmaxf(fmax3(b0, b1, b2), b3), nbc);
 				};
-				const float c0 = row_max(r0), c1 = row_max(r1), c2 = row_max(r2), c3 = row_max(r3);
+				const float c0 = row_max(r0), c1 = row_max(r1);
 				emit(c0, 0, [&](int k) { return fmaf(-2.0f, __uint_as_float(r0[k]), nbc); });
 				emit(c1, 1, [&](int k) { return fmaf(-2.0f, __uint_as_float(r1[k]), nbc); });
-				emit(c2, 2, [&](int k) { return fmaf(-2.0f, __uint_as_float(r2[k]), nbc); });
-				emit(c3, 3, [&](int k) { return fmaf(-2.0f, __uint_as_float(r3[k]), nbc); });
 			} else {
 				// general norms: d' = |b_j|^2 - 2 s_j in place (packed pairs), then the same tree of three-input minima
 				auto row_min = [&](uint32_t (&r)[32], int c) {
@@ -329,11 +354,9 @@ filter_kernel(const __grid_constant__ CUtensorMap tmB, FilterArgs P) {
 					}
 					return fminf(fmin3(b0, b1, b2), b3);
 				};
-				const float c0 = row_min(r0, 0), c1 = row_min(r1, 1), c2 = row_min(r2, 2), c3 = row_min(r3, 3);
+				const float c0 = row_min(r0, 0), c1 = row_min(r1, 1);
 				emit(c0, 0, [&](int k) { return __uint_as_float(r0[k]); });
 				emit(c1, 1, [&](int k) { return __uint_as_float(r1[k]); });
-				emit(c2, 2, [&](int k) { return __uint_as_float(r2[k]); });
-				emit(c3, 3, [&](int k) { return __uint_as_float(r3[k]); });
 			}
 			__syncwarp();
 			if (lane == 0) mbar_arrive(&bar->b_empty[s]);            // this warp is done with the stage's norms
@@ -444,8 +467,8 @@ bool tc_supported(int dof) { return dof == TC_DOF; }
 void launch_tc_split(const double* d_x, int n, void* d_operand, float* d_norm, unsigned* d_max_norm_bits, cudaStream_t st) {
 	const int n_pad = tc_pad_rows(n);
 	BS_CUDA(cudaMemsetAsync(d_max_norm_bits, 0, 4, st));
-	BS_LAUNCH(split_kernel, div_up(n_pad, 8), 256, 0, st, d_x, n, n_pad, static_cast<__nv_bfloat16*>(d_operand), d_norm, d_max_norm_bits);
-	BS_LAUNCH(norm_flags_kernel, div_up(n_pad / TC_BN, 8), 256, 0, st, d_norm, n_pad / TC_BN);
+	BS_LAUNCH(split_kernel, div_up(n_pad, 8), 256, 0, st, d_x, n, n_pad, static_cast<__nv_bfloat16*>(d_operand), d_norm);
+	BS_LAUNCH(norm_flags_kernel, div_up(n_pad / TC_BN, 8), 256, 0, st, d_norm, n_pad / TC_BN, n, d_max_norm_bits);
 }
 
 // rows of A against all rows of B: candidate lists for the rows of A

@@ -138,13 +138,17 @@ struct DescribeSetup {
 		tables.d_walk = nullptr; tables.walk_cap = 0;
 	}
 	// scratch of the sliding-window walks (DescribeTables::d_walk) for up to `features` features per launch, at most 6 GB
-	void reserve_walk(long features) {
+	// limit > 0 (bs_surf_set_walk_scratch): never more than that many features, also when the scratch is already larger
+	void reserve_walk(long features, long limit = 0) {
 		if (p.ori_variant != 1) return;
 		const size_t per = ori_w.size() * 32;
-		const long cap = std::max<long>(1, std::min<long>(features, (long)((6UL << 30) / per)));
+		long cap = std::max<long>(1, std::min<long>(features, (long)((6UL << 30) / per)));
+		if (limit > 0) cap = std::min(cap, limit);
 		if (cap > tables.walk_cap) {
 			d_walk.reserve((size_t)cap * per);
 			tables.d_walk = d_walk.as<double>(); tables.walk_cap = cap;
+		} else if (limit > 0 && tables.d_walk) {
+			tables.walk_cap = cap;
 		}
 	}
 	void release() { d_ori_w.release(); d_w.release(); d_wgrid.release(); d_perm.release(); d_walk.release(); }
@@ -195,7 +199,7 @@ struct bs_surf {
 	cudaEvent_t ev_in = nullptr;
 	DescribeSetup ds;
 	// workspace
-	int chunk_req = 0; long pool_req = 0;
+	int chunk_req = 0; long pool_req = 0; long walk_req = 0;
 	int W = 0, H = 0, chunk = 0;
 	Plan plan{};
 	DevBuf d_plan, d_in, d_frame_offset;
@@ -290,7 +294,7 @@ void bs_surf::ensure(int w, int h, int nbatch) {
 	d_frame_offset.reserve((size_t)(nbatch + 1) * sizeof(int));
 	long cap = pool_req > 0 ? pool_req : (long)nbatch * std::max<long>((long)px / 64, 256);
 	pool.reserve(cap, out_dof());
-	ds.reserve_walk(std::min<long>(cap, (long)chunk * std::max<long>((long)px / 96, 256)));   // a chunk's features (~3x the synthetic density)
+	ds.reserve_walk(std::min<long>(cap, (long)chunk * std::max<long>((long)px / 96, 256)), walk_req);   // a chunk's features (~3x the synthetic density)
 	if (bands > 0) {
 		d_gray.reserve(px * elem_size(pixel_type) * group);
 		d_ii_bands.reserve(px * 4 * group * bands);
@@ -575,6 +579,15 @@ int bs_surf_set_workspace(bs_surf* s, int chunk_frames, long pool_features) {
 	});
 }
 
+int bs_surf_set_walk_scratch(bs_surf* s, long max_features) {
+	return guarded([&] {
+		if (!s) fail(BS_ERR_ARG, "handle is null");
+		if (max_features < 0) fail(BS_ERR_ARG, "max_features must be >= 0");
+		s->finish();
+		s->walk_req = max_features;
+	});
+}
+
 int bs_surf_set_ways(bs_surf* s, int ways) {
 	return guarded([&] {
 		if (!s) fail(BS_ERR_ARG, "handle is null");
@@ -637,6 +650,8 @@ int bs_surf_detect_host_batch(bs_surf* s, const void* pixels, long frame_stride,
 		if (width <= 0 || height <= 0) fail(BS_ERR_ARG, "image width and height must be positive");
 		if (batch < 0 || cap < 0 || stride < width) fail(BS_ERR_ARG, "bad batch/cap/stride");
 		if (frame_stride < (long)stride * (height - 1) + width) fail(BS_ERR_ARG, "frames overlap");
+		// the worker lanes are grey handles: a planar handle's bands and 64*bands descriptor rows do not fit them
+		if (s->bands > 0) fail(BS_ERR_STATE, "bs_surf_detect_host_batch is not available on a planar (colour) handle");
 		DeviceGuard g(s->device);
 		s->finish();
 		const int NL = s->n_lanes;
@@ -682,7 +697,9 @@ int bs_surf_detect_host_batch(bs_surf* s, const void* pixels, long frame_stride,
 		for (int f0 = 0; f0 < batch; f0 += sub, k = (k + 1) % NL) {
 			drain(k);                              // normally a no-op: this lane was drained right after the previous one started
 			bs_surf* h = s->lane[k];
-			h->chunk_req = s->chunk_req; h->pool_req = s->pool_req;
+			// the caller sized pool_features for the whole batch; a lane holds one turn of `sub` frames (twice its share: frames differ)
+			h->chunk_req = s->chunk_req; h->walk_req = s->walk_req;
+			h->pool_req = s->pool_req > 0 ? std::min<long>(s->pool_req, std::max<long>(1024, 2 * ((s->pool_req * sub + batch - 1) / batch))) : 0;
 			const int n = std::min(sub, batch - f0);
 			const size_t dense = (size_t)width * height * es;
 			h->d_in.reserve(dense * sub);

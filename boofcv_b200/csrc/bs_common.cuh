@@ -38,6 +38,19 @@ void count_launch(int n = 1);
 	} while (0)
 
 inline int div_up(int a, int b) { return (a + b - 1) / b; }
+// SM count of the CURRENT device, cached per device: a process may hold handles on several GPUs (the C ABI takes a device on
+// every create call), so nothing about a device may live in a process-wide static keyed to whichever device came first.
+// Function attributes (opt-in shared memory sizes) are per device too and are simply set before every launch that needs one.
+inline int device_sm_count() {
+	static int cache[64] = {0};
+	int dev = 0;
+	BS_CUDA(cudaGetDevice(&dev));
+	if (dev >= 0 && dev < 64 && cache[dev] > 0) return cache[dev];
+	int n = 0;
+	BS_CUDA(cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev));
+	if (dev >= 0 && dev < 64) cache[dev] = n;
+	return n;
+}
 inline long div_up_l(long a, long b) { return (a + b - 1) / b; }
 
 // ---------------------------------------------------------------- scale-space plan

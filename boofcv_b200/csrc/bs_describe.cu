@@ -546,12 +546,7 @@ __global__ void __launch_bounds__(128, 10) sliding_walk_kernel(const double2* __
 template <typename T>
 void launch_describe(const T* d_ii, int W, int H, const DescribeParams& p, const DescribeTables& t, const Pool& pool,
                      const int* d_begin, const int* d_end, int frame0, bool do_orientation, bool do_describe, cudaStream_t st) {
-	static int sm_count = 0;
-	if (sm_count == 0) {
-		int dev = 0;
-		BS_CUDA(cudaGetDevice(&dev));
-		BS_CUDA(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev));
-	}
+	const int sm_count = device_sm_count();
 	const DescribeSmem S = describe_smem(p);
 	if (S.total > 220 * 1024) fail(BS_ERR_ARG, "orientation/descriptor configuration needs too much shared memory");
 	BS_CUDA(cudaFuncSetAttribute(describe_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, S.total));

@@ -362,17 +362,10 @@ bool launch_hessian_tma(const float* d_ii, const Plan& plan, int first_layer, fl
 	if (encode(&tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<float*>(d_ii), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
 	           CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
 		return false;
-	static int sm_count = 0;
-	static bool attr = false;
 	constexpr int smem = 2 * G::BUF * 4 + 16 + 128;
 	auto kern = hessian_tma_kernel<SKIP, S0, STEP, NS, TX, TY, THREADS>;
-	if (!attr) {
-		int dev = 0;
-		BS_CUDA(cudaGetDevice(&dev));
-		BS_CUDA(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev));
-		BS_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-		attr = true;
-	}
+	const int sm_count = device_sm_count();
+	BS_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));   // per device: set on every launch
 	int per_sm = (200 * 1024) / (smem + 1024);
 	static const int per_sm_cap = getenv("BS_HT_PER_SM") ? atoi(getenv("BS_HT_PER_SM")) : 4;
 	per_sm = per_sm > per_sm_cap ? per_sm_cap : (per_sm < 1 ? 1 : per_sm);

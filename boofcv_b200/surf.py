@@ -177,6 +177,10 @@ class DetectDescribeSurf:
     def setWorkspace(self, chunkFrames=0, poolFeatures=0):
         N.check(N.lib().bs_surf_set_workspace(self._h, chunkFrames, poolFeatures))
 
+    def setWalkScratch(self, maxFeatures=0):
+        """surfStable: cap the sliding-window walk scratch (features); the rest is walked inside describe_kernel."""
+        N.check(N.lib().bs_surf_set_walk_scratch(self._h, maxFeatures))
+
     def setWays(self, ways):
         N.check(N.lib().bs_surf_set_ways(self._h, ways))
 

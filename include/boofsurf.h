@@ -115,6 +115,10 @@ int bs_surf_destroy(bs_surf* s);
  * intensity workspace: 4*sum(layers) bytes per frame); pool_features = capacity of the feature pool of one detect call
  * (0 = batch * width*height/64). */
 int bs_surf_set_workspace(bs_surf* s, int chunk_frames, long pool_features);
+/* surfStable only: cap the sliding-window walk scratch (32 bytes x 289 samples per feature, default one chunk's features, at
+ * most 6 GB) at max_features features; features beyond it are walked inside describe_kernel (same results, slower).  0 = default.
+ * ImplOrientationSlidingWindowIntegral.java:139-188 is the walk either way; tests use this to run the in-kernel branch. */
+int bs_surf_set_walk_scratch(bs_surf* s, long max_features);
 /* Streams ("ways", 1..4, default 3) a device-resident batch is spread over, integral group by integral group; 1 = every
  * kernel on the caller's stream (what the per-stage timing of bs_surf_set_timing wants).  Results do not depend on it. */
 int bs_surf_set_ways(bs_surf* s, int ways);
