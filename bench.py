@@ -10,7 +10,10 @@ timing barrier.
 
   value      frames/s with the batch already resident in HBM (CUDA events, max over ranks)
   e2e        frames/s with HOST (pinned) frames in and HOST feature lists out, copies inside the timed region
-  roofline   the Fast-Hessian kernel (dominant): algorithmic bytes per launch / its CUDA-event time, vs measured HBM peak
+  roofline   the largest stage by CUDA-event time (today orientation + descriptor): algorithmic bytes per launch / its
+             event time vs the measured HBM peak, with every other stage's figures beside it (roofline.stages)
+  association / config3 / config5   the other BASELINE configs, short legs; under torchrun the 100k x 100k association shards
+             its source rows over the ranks (one NCCL all-gather of the column partials)
   cpu_baseline  the CPU oracle (C++ restatement of the reference Java; no JVM on this box) on a bounded sample
 --impl reference times that CPU path alone, with all host threads, and prints the same JSON shape.
 """
@@ -196,12 +199,12 @@ def det_total_of_first(g, B):
 def run_e2e(g, steps, world=1):
     """Same metric through the host-facing call (bs_surf_detect_host_batch): the step's frames live in pinned HOST memory,
     the feature lists (frame offsets, xy, scale, angle, desc, white) land in pinned HOST memory; the library overlaps the
-    copies of one 32-frame sub-batch with the kernels of the other.  Returns (frames/s, h2d, d2h bytes per step)."""
+    copies of one sub-batch with the kernels of the others.  Returns (frames/s, h2d, d2h bytes per step, parity probe)."""
     torch, det, dev = g["torch"], g["det"], g["dev"]
     from boofcv_b200 import HostFeatureBuffers
     # host memory is bounded when several ranks share one box: 1024 frames are 8.5 GB of pinned input + 6 GB of pinned output per
-    # rank, so the ranks of a box share 2048 frames between them
-    B = min(g["B"], max(2048 // world, 64))
+    # rank, so the ranks of a box share 4096 frames between them
+    B = min(g["B"], max(4096 // world, 64))
     host = torch.empty((B, H, W), dtype=torch.float32, pin_memory=True)      # the step's input lives on the host
     host.copy_(g["frames"][:B])
     cap = int(g["total_features"] * 1.1 * B / g["B"]) + 4096
@@ -220,38 +223,178 @@ def run_e2e(g, steps, world=1):
     dt = time.perf_counter() - t0
     if out.total != expect:
         raise RuntimeError("host path found %d features, device path %d" % (out.total, expect))
+    # Parity probe (outside the timed region): three frames of what the timed call just returned, against the CPU oracle, bit for bit
+    probe = "skipped"
+    if g.get("rank", 0) == 0:
+        from oracle import bsoracle as orc
+        orc.build()
+        bad = []
+        for f in sorted({0, B // 2, B - 1}):
+            o = orc.surf_fast(host[f].numpy(), nthreads=os.cpu_count() or 1)
+            b, e = int(out.frame_offset[f]), int(out.frame_offset[f + 1])
+            ok = (e - b == len(o["x"]) and np.array_equal(out.xy[b:e, 0], o["x"]) and np.array_equal(out.xy[b:e, 1], o["y"])
+                  and np.array_equal(out.scale[b:e], o["scale"]) and np.array_equal(out.angle[b:e], o["angle"])
+                  and np.array_equal(out.desc[b:e], o["desc"]) and np.array_equal(out.white[b:e].astype(bool), o["white"]))
+            if not ok:
+                bad.append(f)
+        probe = "ok" if not bad else "MISMATCH in frames %s" % bad
     out.close()
-    return B * steps / dt, h2d, d2h
+    return B * steps / dt, h2d, d2h, probe, B
 
 
-def run_association(torch, dev, n=100000, reps=3):
-    """Second headline of the path (BASELINE north_star): greedy association of n x n SURF-64 descriptors with backward
-    validation, descriptors resident in HBM.  Tensor-core filter + exact fp64 re-score (bs_assoc mode 1)."""
-    import numpy as np
+def _exact_sq(a, b):
+    """DescriptorDistance.euclideanSq of every row of a against every row of b: sequential over k, no FMA (numpy, fp64)."""
+    s = np.zeros((len(a), len(b)))
+    for k in range(a.shape[1]):
+        d = a[:, k][:, None] - b[:, k][None, :]
+        s = s + d * d
+    return s
+
+
+def association_probe(src, dst, pairs, fit, rows):
+    """Exactness of sampled rows of a 100k x 100k result against the reference's rule, evaluated on the CPU in fp64:
+    forward = the LAST column with the smallest distance (AssociateGreedy.java:80-91), kept only if no OTHER source row is as
+    close or closer to that column (:98-117); fit = that distance bit for bit."""
+    a = src[rows]
+    w = _exact_sq(a, dst)                                        # [rows][m]
+    best = w.min(axis=1)
+    jstar = w.shape[1] - 1 - np.argmin(w[:, ::-1], axis=1)       # last index of the minimum
+    col = _exact_sq(dst[jstar], src)                             # [rows][n]: distances of the chosen column to every source row
+    bad = 0
+    for r, i in enumerate(rows):
+        c = col[r]
+        alone = (c <= best[r]).sum() == 1                        # only row i itself attains (or beats) it
+        want_pair, want_fit = (int(jstar[r]), best[r]) if alone else (-1, np.finfo(np.float64).max)
+        if int(pairs[i]) != want_pair or float(fit[i]) != want_fit:
+            bad += 1
+    return bad
+
+
+def run_association(torch, dist, dev, rank, world, n=100000, reps=5):
+    """Second headline of the path (BASELINE north_star, configs[3]): greedy association of n x n SURF-64 descriptors with backward
+    validation, descriptors resident in HBM.  Tensor-core filter + exact fp64 re-score (bs_assoc mode 1).  With several ranks
+    the SOURCE ROWS are sharded (boofcv_b200.parallel.ShardedAssociate: one all-gather of the column partials over NCCL)."""
     import boofcv_b200 as bs
-    g = torch.Generator(device=dev); g.manual_seed(99)
+    from boofcv_b200 import parallel
+    g = torch.Generator(device=dev); g.manual_seed(99)              # the same descriptors on every rank
     dst = torch.randn((n, 64), generator=g, device=dev, dtype=torch.float64); dst /= dst.norm(dim=1, keepdim=True)
     perm = torch.randperm(n, generator=g, device=dev)
     src = dst[perm] + 0.02 * torch.randn((n, 64), generator=g, device=dev, dtype=torch.float64)
     src /= src.norm(dim=1, keepdim=True)                       # SURF descriptors are unit vectors (UtilFeature.normalizeL2)
     a = bs.FactoryAssociation.greedy(bs.ScoreAssociateEuclideanSq_F64(), float(np.finfo(np.float64).max), True, device=dev.index or 0)
     a.setMode(1)
-    p, _ = a.associateDevice(src, dst)                          # warm-up
+    b0, e0 = parallel.shard_range(n, rank, world)
+    mine = src[b0:e0].contiguous()
+    sa = parallel.ShardedAssociate(parallel.GpuAssocBackend(a), True)
+    call = (lambda: sa.associate(mine, dst, row_offset=b0)) if world > 1 else (lambda: a.associateDevice(src, dst))
+    p, f = call()                                               # warm-up
     torch.cuda.synchronize(dev)
+    if world > 1:
+        dist.barrier()
+    e_0, e_1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e_0.record()
+    for _ in range(reps):
+        p, f = call()
+    e_1.record(); torch.cuda.synchronize(dev)
+    t = torch.tensor([e_0.elapsed_time(e_1) / reps], device=dev, dtype=torch.float64)
+    ok = torch.tensor([1 if torch.equal(p.long(), perm[b0:e0]) else 0], device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+    ms = float(t.item())
+    _, _, (runs, fallbacks) = a.filterScores(src[:1].cpu().numpy(), dst[:1].cpu().numpy(), want_scores=False)
+    out = None
+    if rank == 0:
+        pk, _ = peaks()
+        alg = 2.0 * n * n * 64 / (ms / 1e3) / 1e12               # SURVEY 8(d): the -2 A B^T term, once
+        probe_rows = np.random.default_rng(5).choice(e0 - b0, 48, replace=False)
+        bad = association_probe(src.cpu().numpy(), dst.cpu().numpy(), p.cpu().numpy(), f.cpu().numpy(), probe_rows) if world == 1 else None
+        out = {"workload": "%d x %d SURF-64 descriptors, greedy + backward validation, HBM resident%s" % (
+                   n, n, ", source rows sharded over %d ranks" % world if world > 1 else ""),
+               "ms": ms, "pairs_per_s": n * float(n) / (ms / 1e3),
+               "algorithmic_tflops": alg, "frac_of_bf16_peak": alg / pk["bf16_tflops"],
+               "frac_of_bf16_peak_sustained": alg / pk.get("bf16_tflops_sustained", pk["bf16_tflops"]),
+               "target_ms_for_half_of_peak": 2.0 * n * n * 64 / (0.5 * pk["bf16_tflops"] * 1e12) * 1e3,
+               "tensor_pipe_tflops_executed": 2 * alg,            # two K = 64 GEMM passes (forward, backward) are issued
+               "planted_permutation_recovered": bool(ok.item() == 1), "exact_fallbacks": fallbacks,
+               "parity_probe": None if bad is None else ("ok: 48 sampled rows exact vs fp64 CPU rule" if bad == 0 else "%d of 48 sampled rows differ" % bad)}
+    a.close()
+    del src, dst
+    torch.cuda.empty_cache()
+    return out
+
+
+def run_config3(torch, dist, dev, rank, world, local_rank, frames_per_rank=32):
+    """BASELINE configs[2]: surfStable (4 octaves, sliding-window orientation, SurfMod descriptor) on 3840x2160 frames, frames
+    sharded over the ranks, no collective (a bounded sample: frames_per_rank per GPU)."""
+    import boofcv_b200 as bs
+    from boofcv_b200.synth import blob_images_torch
+    B = frames_per_rank
+    frames = blob_images_torch(3840, 2160, B, seed=234 + rank * B, device=dev)
+    det = bs.FactoryDetectDescribe.surfStable(None, None, None, np.float32, device=local_rank)
+    det.detectBatch(frames); det.totalFeatures()                # warm-up
+    torch.cuda.synchronize(dev)
+    if world > 1:
+        dist.barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
-    for _ in range(reps):
-        p, _ = a.associateDevice(src, dst)
+    det.detectBatch(frames)
+    feats = det.totalFeatures()
     e1.record(); torch.cuda.synchronize(dev)
-    ms = e0.elapsed_time(e1) / reps
-    pk, _ = peaks()
-    tflops = 2 * 2.0 * n * n * 192 / (ms / 1e3) / 1e12           # two GEMM passes (forward, backward), K = 192
-    _, _, (runs, fallbacks) = a.filterScores(src[:1].cpu().numpy(), dst[:1].cpu().numpy(), want_scores=False)
-    out = {"workload": "%d x %d SURF-64 descriptors, greedy + backward validation, HBM resident" % (n, n), "ms": ms,
-           "pairs_per_s": n * n / (ms / 1e3), "tensor_tflops_whole_call": tflops, "frac_of_bf16_peak": tflops / pk["bf16_tflops"],
-           "planted_permutation_recovered": bool(torch.equal(p.long(), perm)), "exact_fallbacks": fallbacks}
-    a.close()
-    return out
+    t = torch.tensor([e0.elapsed_time(e1)], device=dev, dtype=torch.float64)
+    fs = torch.tensor([float(feats)], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX); dist.all_reduce(fs)
+    det.close(); del frames
+    torch.cuda.empty_cache()
+    ms = float(t.item())
+    return {"workload": "surfStable detect+describe, %d x 3840x2160 GrayF32 per GPU (sample of BASELINE configs[2]), frames sharded" % B,
+            "frames_per_s": world * B / (ms / 1e3), "ms": ms, "features_per_frame": float(fs.item()) / (world * B), "scaling": "weak"}
+
+
+def run_config5(torch, dist, dev, rank, world, local_rank, pairs_total=8192, pairs_cap=256):
+    """BASELINE configs[4]: stereo-pair stream — per pair detect+describe both 1080p frames and associate left -> right with backward
+    validation, everything on the device; pairs sharded over the ranks (8192 / world per rank, capped to a stated sample)."""
+    import boofcv_b200 as bs
+    from boofcv_b200.synth import blob_images_torch
+    P = min(pairs_total // world, pairs_cap)
+    left = blob_images_torch(1920 + 16, 1080, P, seed=5000 + rank * P, device=dev)
+    frames = torch.empty((2 * P, 1080, 1920), device=dev, dtype=torch.float32)
+    frames[0::2] = left[:, :, :1920]                            # right = left shifted by a disparity of 16 px
+    frames[1::2] = left[:, :, 16:]
+    del left
+    det = bs.FactoryDetectDescribe.surfFast(None, None, None, np.float32, device=local_rank)
+    assoc = bs.FactoryAssociation.greedy(bs.ScoreAssociateEuclideanSq_F64(), 0.1, True, device=local_rank)
+    sub = 32
+
+    def stream():
+        matched = 0
+        for p0 in range(0, P, sub):
+            det.detectBatch(frames[2 * p0:2 * min(p0 + sub, P)])
+            k = min(sub, P - p0)
+            pairs, _, off = assoc.associateFramesBatch(det, np.arange(0, 2 * k, 2), np.arange(1, 2 * k, 2))
+            if p0 == 0:
+                matched = int((pairs[:off[1]] >= 0).sum().item())
+        return matched
+
+    stream()                                                    # warm-up
+    torch.cuda.synchronize(dev)
+    if world > 1:
+        dist.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    matched = stream()
+    e1.record(); torch.cuda.synchronize(dev)
+    t = torch.tensor([e0.elapsed_time(e1)], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    det.close(); assoc.close(); del frames
+    torch.cuda.empty_cache()
+    ms = float(t.item())
+    return {"workload": "stereo stream: %d x (2 x 1920x1080) per GPU (sample of BASELINE configs[4]: 8192 pairs over the ranks), surfFast x2 + "
+                        "greedy(backward, maxFit 0.1) per pair, device resident" % P,
+            "pairs_per_s": world * P / (ms / 1e3), "frames_per_s": 2 * world * P / (ms / 1e3), "ms": ms, "matches_first_pair": matched,
+            "scaling": "weak"}
 
 
 def main():
@@ -264,7 +407,8 @@ def main():
     ap.add_argument("--chunk", type=int, default=0, help="frames per kernel wave (0 = library default)")
     ap.add_argument("--ways", type=int, default=3, help="streams a device-resident batch is spread over (1..4)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
-    ap.add_argument("--no-assoc", action="store_true", help="skip the association leg (100k x 100k, rank 0)")
+    ap.add_argument("--no-assoc", action="store_true", help="skip the association leg (100k x 100k, rows sharded over the ranks)")
+    ap.add_argument("--no-configs", action="store_true", help="skip the short config-3 / config-5 legs")
     ap.add_argument("--no-e2e", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "native" else args.warmup
@@ -288,6 +432,7 @@ def main():
         os.dup2(2, 1)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     g = run_gpu(args, rank, world, local_rank)
+    g["rank"] = rank
     dev = g["dev"]
     ms = torch.tensor([g["ms"]], device=dev, dtype=torch.float64)
     feats = torch.tensor([float(g["total_features"])], device=dev, dtype=torch.float64)
@@ -300,34 +445,66 @@ def main():
 
     e2e = None
     if not args.no_e2e:
-        fps, h2d, d2h = run_e2e(g, max(1, min(args.steps, 2)), world)
+        fps, h2d, d2h, probe, eb = run_e2e(g, max(1, args.steps), world)
         t = torch.tensor([fps], device=dev, dtype=torch.float64)
         if world > 1:
             dist.all_reduce(t, op=dist.ReduceOp.MIN)          # slowest rank bounds the job
-        e2e = {"value": float(t.item()) * world, "unit": UNIT, "h2d_bytes_per_step": int(h2d) * world,
-               "d2h_bytes_per_step": int(d2h) * world, "batch_per_gpu": min(B, max(2048 // world, 64))}
+        rate = float(t.item())
+        e2e = {"value": rate * world, "unit": UNIT, "h2d_bytes_per_step": int(h2d) * world,
+               "d2h_bytes_per_step": int(d2h) * world, "batch_per_gpu": eb, "steps": max(1, args.steps),
+               "h2d_gbs_per_gpu": rate * h2d / eb / 1e9, "d2h_gbs_per_gpu": rate * d2h / eb / 1e9, "parity_probe": probe}
+    # the device batch of the headline is no longer needed: free it before the other legs allocate theirs
+    det = g["det"]
+    timing, ms_single, clocks, launches = g["timing"], g["ms_single"], g["clocks"], g["launches"]
+    det.close()
+    g.clear()
+    torch.cuda.empty_cache()
+
+    extra = {}
+    if not args.no_assoc:
+        try:
+            extra["association"] = run_association(torch, dist, dev, rank, world)
+        except Exception as ex:                                  # never lose the headline line over an extra leg
+            extra["association"] = {"error": str(ex)[:300]}
+    if not args.no_configs:
+        for name, fn in (("config3", run_config3), ("config5", run_config5)):
+            try:
+                extra[name] = fn(torch, dist, dev, rank, world, local_rank)
+            except Exception as ex:
+                extra[name] = {"error": str(ex)[:300]}
 
     if rank == 0:
         pk, pk_kind = peaks()
-        tm = g["timing"]
-        stage_ms = {k: v[0] for k, v in tm.items()}
-        total_stage = sum(stage_ms.values()) or 1.0
-        hess_ms, hess_calls = tm["fast_hessian"]
-        chunk_frames = B * args.steps / max(hess_calls, 1)
-        # algorithmic bytes of one Fast-Hessian launch: the integral image of its frames, read once (the
-        # intensity layers are avoidable traffic and are not counted)
-        alg_bytes = chunk_frames * 4.0 * W * H
-        achieved = alg_bytes / (hess_ms / max(hess_calls, 1) / 1000.0) / 1e9 if hess_ms > 0 else 0.0
+        tm = timing
+        steps = args.steps
+        frames_timed = float(B * steps)
         nfeat = float(feats.item()) / (world * B)
-        pipeline_bytes = 3 * 4.0 * W * H + 545.0 * nfeat
-        # DRAM bytes of the dominant kernel from the committed ncu --set full capture (profiles/traffic.json), per launch
-        traffic, kernel_name = None, "hessian_tile_kernel<1,9,6,4,64,16>"
+        # Algorithmic bytes per frame of each stage: integral = read input + write integral; Fast-Hessian + NMS = the
+        # integral read once (the intensity layers are avoidable traffic, NMS adds nothing when fused); descriptors = 545 B per feature
+        alg = {"integral": 8.0 * W * H, "fast_hessian": 4.0 * W * H, "nms_refine": 0.0, "compaction": 0.0, "orient_describe": 545.0 * nfeat}
+        kernels = {"integral": "integral_rows_kernel + integral_cols_kernel", "fast_hessian": "hessian_tma_kernel<1,..> + hessian_tma_kernel<2,..> + hessian_generic_kernel",
+                   "nms_refine": "nms_kernel", "compaction": "scan_counts + frame_offsets + gather_points", "orient_describe": "describe_kernel<float>"}
+        traffic_per_frame = {}
         try:
-            tj = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "traffic.json")))
-            traffic = float(tj["fast_hessian_dram_bytes_per_frame"]) * chunk_frames
-            kernel_name = tj.get("kernel", kernel_name)
+            tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+            traffic_per_frame = tj.get("dram_bytes_per_frame", {})
         except Exception:
             pass
+        stage_ms = {k: v[0] for k, v in tm.items()}
+        total_stage = sum(stage_ms.values()) or 1.0
+        stages = {}
+        for k, (msk, calls) in tm.items():
+            us_frame = msk * 1000.0 / frames_timed
+            gbs = alg[k] / (us_frame * 1e-6) / 1e9 if us_frame > 0 else 0.0
+            stages[k] = {"us_per_frame": us_frame, "share_of_step": msk / total_stage, "algorithmic_bytes_per_frame": alg[k],
+                         "achieved_gbs": gbs, "frac": gbs / pk["hbm_gbs"], "dram_bytes_per_frame_ncu": traffic_per_frame.get(k)}
+        dom = max(stage_ms, key=lambda k: stage_ms[k])
+        dom_ms, dom_calls = tm[dom]
+        frames_per_launch = frames_timed / max(dom_calls, 1)
+        alg_launch = alg[dom] * frames_per_launch
+        achieved = alg_launch / (dom_ms / max(dom_calls, 1) / 1000.0) / 1e9 if dom_ms > 0 else 0.0
+        pipeline_bytes = 3 * 4.0 * W * H + 545.0 * nfeat
+        tr = traffic_per_frame.get(dom)
         out = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -336,33 +513,37 @@ def main():
                        "batch_per_gpu": B, "features_per_frame": nfeat,
                        "ways": args.ways,
                        "l2": "inputs larger than L2 (%.1f GB batch per step)" % (B * W * H * 4 / 1e9)},
-            "roofline": {"bound": "hbm", "kernel": kernel_name, "achieved": achieved, "peak": pk["hbm_gbs"],
-                         "unit": "GB/s", "frac": achieved / pk["hbm_gbs"], "traffic": traffic, "peak_kind": pk_kind,
-                         "frames_per_launch": chunk_frames, "algorithmic_bytes_per_launch": alg_bytes,
-                         "share_of_step": hess_ms / total_stage,
+            "roofline": {"bound": "hbm", "kernel": kernels[dom], "stage": dom, "achieved": achieved, "peak": pk["hbm_gbs"],
+                         "unit": "GB/s", "frac": achieved / pk["hbm_gbs"], "traffic": (tr * frames_per_launch) if tr else None,
+                         "peak_kind": pk_kind, "frames_per_launch": frames_per_launch, "algorithmic_bytes_per_launch": alg_launch,
+                         "share_of_step": dom_ms / total_stage,
+                         "note": "the largest stage by CUDA-event time; no stage of this path is HBM-bound (L1 / shared-memory load issue "
+                                 "limits them, see profiles/): the fractions say how far each is from the bytes it has to move",
+                         "stages": stages,
                          "timed": "event pair per stage launch over the same %d steps run on one stream (%.1f ms per step); "
-                                  "the timed region of `value` overlaps %d streams" % (args.steps, g["ms_single"] / args.steps, args.ways),
+                                  "the timed region of `value` overlaps %d streams" % (args.steps, ms_single / args.steps, args.ways),
                          "pipeline_achieved_gbs": value / world * pipeline_bytes / 1e9,
                          "pipeline_frac": value / world * pipeline_bytes / 1e9 / pk["hbm_gbs"]},
             "stage_ms_per_step": {k: v / args.steps for k, v in stage_ms.items()},
-            "gpu_launches": int(g["launches"]),
-            "clocks": g["clocks"],
+            "gpu_launches": int(launches),
+            "clocks": clocks,
         }
         if e2e:
             out["e2e"] = e2e
-        if not args.no_assoc:
-            try:
-                out["association"] = run_association(g["torch"], dev)
-            except Exception as ex:                              # never lose the headline line over the extra leg
-                out["association"] = {"error": str(ex)[:200]}
+            out["parity_probe"] = e2e["parity_probe"]
+        out.update(extra)
         if not args.no_cpu and world == 1:
             from boofcv_b200.synth import blob_image
             cores = os.cpu_count() or 1
             frames = [blob_image(W, H, 234 + i) for i in range(2)]
-            fps, n, _ = cpu_surf_fps(frames, cores, min_seconds=12.0, max_frames=4096)
-            out["cpu_baseline"] = {"value": fps, "unit": UNIT, "cores": cores, "kind": "port",
-                                   "sample": "%d x 1080p frames (same generator, seeds 234..235 cycled), surfFast, %d threads; "
-                                             "C++ restatement of the reference Java (no JVM on this box)" % (n, cores)}
+            fps1, n1, _ = cpu_surf_fps(frames, 1, min_seconds=3.0, max_frames=64)
+            fps, n, _ = cpu_surf_fps(frames, cores, min_seconds=10.0, max_frames=4096)
+            out["cpu_baseline"] = {"value": fps, "unit": UNIT, "cores": cores, "kind": "port", "single_thread_value": fps1,
+                                   "sample": "%d x 1080p frames on %d threads (+ %d frames on one thread; same generator, seeds 234..235 cycled), "
+                                             "surfFast; C++ restatement of the reference Java (no JVM on this box), persistent thread pool with "
+                                             "contiguous blocks like BoofConcurrency's ForkJoinPool; the integral image, the scale-space "
+                                             "maximum search and the list handling are serial in the reference too, which bounds the scaling "
+                                             "with threads" % (n, cores, n1)}
         if saved_stdout is not None:
             sys.stdout.flush()
             os.dup2(saved_stdout, 1)

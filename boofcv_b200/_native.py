@@ -88,6 +88,8 @@ SIGNATURES = {
     "bs_assoc_forward_static": (_i, [_i, _vp, _i, _vp, _i, _i, _d, _vp, _vp, _vp]),
     "bs_assoc_forward_device": (_i, [_vp, _vp, _i, _i, _vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp]),
     "bs_assoc_merge_columns_device": (_i, [_vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "bs_assoc_forward_only_device": (_i, [_vp, _vp, _i, _vp, _i, _i, _vp, _vp, _vp]),
+    "bs_assoc_merge_packed_device": (_i, [_vp, _i, _i, _vp, _vp, _vp, _vp, _vp]),
     "bs_assoc_validate_device": (_i, [_vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp]),
     "bs_assoc_matches": (_i, [_vp, _vp, _i, _i, _vp, _vp, _vp, _pi, _vp, _pi, _vp, _pi]),
     "bs_assoc_frames_device": (_i, [_vp, _vp, _i, _i, _i, _vp, _vp, _vp]),

@@ -48,6 +48,7 @@ class AssociateGreedyGPU:
         if not isinstance(score, ScoreAssociateEuclideanSq_F64):
             raise ValueError("only ScoreAssociateEuclideanSq_F64 is supported by the GPU associator")
         self._score = score
+        self._max_fit = float(maxError)
         self._backwards = bool(backwardsValidation)
         self._h = C.c_void_p()
         N.check(N.lib().bs_assoc_create(device, float(maxError), int(self._backwards), C.byref(self._h)))
@@ -112,6 +113,10 @@ class AssociateGreedyGPU:
 
     def setMaxScoreThreshold(self, score):
         N.check(N.lib().bs_assoc_set_max_fit_error(self._h, float(score)))
+        self._max_fit = float(score)
+
+    def maxFitError(self):         # AssociateGreedyBase.maxFitError
+        return self._max_fit
 
     def setMode(self, mode):
         N.check(N.lib().bs_assoc_set_mode(self._h, int(mode)))

@@ -161,17 +161,18 @@ __global__ void validate_kernel(int n, int row_offset, int32_t* __restrict__ pai
 }
 
 // merge the column partials of `ranks` shards (all-gathered): min score; first = min, last = max over the shards attaining it
-__global__ void merge_columns_kernel(int ranks, int m, const double* __restrict__ a_min, const int32_t* __restrict__ a_first,
-                                     const int32_t* __restrict__ a_last, double* __restrict__ o_min, int32_t* __restrict__ o_first,
-                                     int32_t* __restrict__ o_last) {
+// (rank r's arrays start r * stride_min doubles / r * stride_idx ints after rank 0's: [ranks][m] arrays or one packed record per rank)
+__global__ void merge_columns_kernel(int ranks, int m, long stride_min, long stride_idx, const double* __restrict__ a_min,
+                                     const int32_t* __restrict__ a_first, const int32_t* __restrict__ a_last, double* __restrict__ o_min,
+                                     int32_t* __restrict__ o_first, int32_t* __restrict__ o_last) {
 	const int j = blockIdx.x * blockDim.x + threadIdx.x;
 	if (j >= m) return;
 	double best = CUDART_INF; int fi = -1, la = -1;
 	for (int r = 0; r < ranks; r++) {
-		const long o = (long)r * m + j;
-		const int a = a_first[o], b = a_last[o];
+		const long oi = (long)r * stride_idx + j;
+		const int a = a_first[oi], b = a_last[oi];
 		if (a < 0) continue;
-		const double f = a_min[o];
+		const double f = a_min[(long)r * stride_min + j];
 		if (fi < 0 || f < best) { best = f; fi = a; la = b; }
 		else if (f == best) { fi = min(fi, a); la = max(la, b); }
 	}
@@ -214,9 +215,11 @@ void launch_validate(int n, int row_offset, int32_t* pairs, double* fit, const d
 }
 
 void launch_merge_columns(int ranks, int m, const double* a_min, const int32_t* a_first, const int32_t* a_last, double* o_min,
-                          int32_t* o_first, int32_t* o_last, cudaStream_t st) {
+                          int32_t* o_first, int32_t* o_last, cudaStream_t st, long stride_min, long stride_idx) {
 	if (m <= 0) return;
-	BS_LAUNCH(merge_columns_kernel, div_up(m, 256), 256, 0, st, ranks, m, a_min, a_first, a_last, o_min, o_first, o_last);
+	if (stride_min <= 0) stride_min = m;
+	if (stride_idx <= 0) stride_idx = m;
+	BS_LAUNCH(merge_columns_kernel, div_up(m, 256), 256, 0, st, ranks, m, stride_min, stride_idx, a_min, a_first, a_last, o_min, o_first, o_last);
 }
 
 }  // namespace bs

@@ -19,7 +19,8 @@
 // accumulator back costs far less than producing it (tcgen05.ld: ~880 B/cycle/SM).  So: the 256 rows of a row block live in
 // TMEM as the A operand (written there by the epilogue threads with tcgen05.st), B tiles stream through an 8-stage TMA ring
 // together with their column norms, three 128-column accumulators rotate between the MMA issuer and two epilogue groups.
-// Roles inside the CTA (576 threads): warp 0 = TMA producer, warp 1 = MMA issuer (one elected thread), warps 2-17 = epilogue in
+// Roles inside the CTA (608 threads): warp 0 = TMA producer, warps 1 and 18 = MMA issuers (one elected thread each, one per A
+// half), warps 2-17 = epilogue in
 // four groups of four warps (a group covers the four TMEM lane quarters): group g takes the accumulators of A half g >> 1 and
 // the 64 columns g & 1 of each — one TMEM lane = one row per thread, two threads per row.  An epilogue warp's serial chain per
 // accumulator (barrier wake-up, tcgen05.ld round trip, the reduction) was longer than the two MMAs it has to keep up with when
@@ -34,6 +35,7 @@
 #include <math_constants.h>
 #include <cfloat>
 #include <cmath>
+#include <type_traits>
 
 namespace bs {
 
@@ -50,7 +52,8 @@ constexpr int TC_SLOTS = 3;                // accumulators in flight
 constexpr int TC_A_COL = TC_SLOTS * TC_BN; // TMEM columns [384, 448): the two A halves, 32 columns each
 constexpr int TC_EPI_WARPS = 16;           // four groups: (A half) x (column half)
 constexpr int TC_EC = TC_BN / 2;           // columns of an accumulator one epilogue thread reduces
-constexpr int TC_THREADS = 64 + 32 * TC_EPI_WARPS;
+constexpr int TC_ISSUER2 = 2 + TC_EPI_WARPS;  // warp index of the second MMA issuer (after the epilogue warps)
+constexpr int TC_THREADS = 96 + 32 * TC_EPI_WARPS;
 constexpr int TC_CAND_CAP = 64;            // candidates kept per row; more -> the caller falls back to the exact kernel
 constexpr int TC_TMEM_COLS = 512;
 
@@ -116,7 +119,7 @@ struct FilterArgs {
 	const float* norm_b;        // [nB_pad] (+inf in the padding)
 	const unsigned* max_norm_b_bits;
 	int* cand_count;            // [nA]
-	int* cand;                  // [nA][TC_CAND_CAP]
+	int* cand;                  // [nA][TC_CAND_CAP][2]: column, estimate d' (float bits)
 	float* dbg;                 // optional [nA][nB] dump of d' + |a|^2 (tests)
 	const double* row_bound;    // optional [nA]: an exact |a-b_j|^2 of some column j per row (an upper bound of the row's minimum), else huge
 };
@@ -124,14 +127,14 @@ struct FilterArgs {
 struct __align__(8) FilterBarriers {
 	uint64_t a_full;
 	uint64_t b_full[TC_STAGES], b_empty[TC_STAGES];
-	uint64_t acc_full[TC_SLOTS], acc_empty[TC_SLOTS];
+	uint64_t acc_full[TC_SLOTS][2], acc_empty[TC_SLOTS][2];  // [slot][use & 1], see the MMA issuers
 	uint32_t tmem_base;
 	uint32_t pad;
 };
 
 constexpr int TC_PEND = 8;                // candidates an epilogue thread collects before it reserves slots in its row's list
 constexpr int TC_SMEM_BYTES = 1024 /*alignment slack*/ + TC_STAGES * TC_TILE_BYTES + TC_STAGES * TC_NB * 4 + (int)sizeof(FilterBarriers) +
-                              TC_PEND * 32 * TC_EPI_WARPS * 4 + TC_MROWS * 2 * 8;
+                              2 * TC_PEND * 32 * TC_EPI_WARPS * 4 + TC_MROWS * 2 * 8;
 
 template <bool DBG>
 __global__ void __launch_bounds__(TC_THREADS, 1)
@@ -142,13 +145,13 @@ filter_kernel(const __grid_constant__ CUtensorMap tmB, FilterArgs P) {
 	float* s_nb = reinterpret_cast<float*>(sB + TC_STAGES * TC_TILE_BYTES);         // [stages][128]: column norms of the stage's tile
 	FilterBarriers* bar = reinterpret_cast<FilterBarriers*>(s_nb + TC_STAGES * TC_NB);
 	int* s_pend = reinterpret_cast<int*>(bar + 1);                   // [TC_PEND][512]: pending candidates, one column per epilogue thread
-	unsigned long long* s_run = reinterpret_cast<unsigned long long*>(s_pend + TC_PEND * 32 * TC_EPI_WARPS);   // [256 rows][2]: {running minimum, row block}
+	unsigned long long* s_run = reinterpret_cast<unsigned long long*>(s_pend + 2 * TC_PEND * 32 * TC_EPI_WARPS);   // [256 rows][2]: {running minimum, row block}
 
 	const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 	if (threadIdx.x == 0) {
 		mbar_init(&bar->a_full, TC_EPI_WARPS / 2);                   // the warps that write A: column half 0 of both A halves
 		for (int s = 0; s < TC_STAGES; s++) { mbar_init(&bar->b_full[s], 1); mbar_init(&bar->b_empty[s], TC_EPI_WARPS); }
-		for (int s = 0; s < TC_SLOTS; s++) { mbar_init(&bar->acc_full[s], 1); mbar_init(&bar->acc_empty[s], TC_EPI_WARPS / 2); }
+		for (int s = 0; s < TC_SLOTS; s++) { mbar_init(&bar->acc_full[s][0], 1); mbar_init(&bar->acc_full[s][1], 1); mbar_init(&bar->acc_empty[s][0], TC_EPI_WARPS / 2); mbar_init(&bar->acc_empty[s][1], TC_EPI_WARPS / 2); }
 		mbar_fence_init();
 	}
 	// no row block yet in the running-minimum exchange (shared memory keeps what the previous kernel left there)
@@ -181,33 +184,40 @@ filter_kernel(const __grid_constant__ CUtensorMap tmB, FilterArgs P) {
 				if (++t == P.b_tiles) t = 0;
 			}
 		}
-	} else if (warp == 1) {
-		// ===== MMA issuer =====
+	} else if (warp == 1 || warp == TC_ISSUER2) {
+		// ===== MMA issuers: warp 1 takes A half 0, warp 18 A half 1 (one elected thread each).  An accumulator is four MMAs
+		// (K = 64) between a wait and a commit: one thread's instruction stream for both halves (~45 dependent instructions per
+		// accumulator, sharing its scheduler with four epilogue warps) took longer than the MMAs themselves (measured with
+		// tools/probe/hs_probe.cu: 513 cycles per accumulator whatever the number of slots, 292 without the hand-off). =====
 		if (elect_one()) {
 			constexpr uint32_t idesc = umma_idesc_bf16(TC_BM, TC_BN);
+			const uint32_t h = warp == 1 ? 0u : 1u;
+			const uint32_t a = tmem + (uint32_t)(TC_A_COL) + h * (TC_K / 2);
 			int t = t0;
-			uint32_t seg = 0, m = 0;                                 // row-block segments started, accumulators produced
+			uint32_t seg = 0;                                        // row-block segments started
 			for (int n = 0; n < n_tiles; n++) {
 				if (t == 0 || n == 0) {                              // the epilogue threads have written this row block's A into TMEM
 					mbar_wait(&bar->a_full, seg & 1);
 					seg++;
 				}
 				const int s = n % TC_STAGES;
+				const uint32_t m = 2u * (uint32_t)n + h;
+				const uint32_t slot = m % TC_SLOTS;
 				mbar_wait(&bar->b_full[s], (n / TC_STAGES) & 1);
+				// The epilogue drained the slot's previous accumulator (use u - 1).  A parity wait is only sound if the waiter knows that
+				// the phase before the one it waits for has completed (otherwise "previous phase still open" reads as "my phase done").
+				// The uses of a slot alternate between the two issuers (and between the two epilogue halves), so with ONE barrier per
+				// slot nobody would know that.  With one barrier per use parity, [slot][u & 1], the phase before is the one this same
+				// thread (warp) waited for two uses earlier.  The same holds for acc_full.
+				const uint32_t u = m / TC_SLOTS;
+				if (u > 0) mbar_wait(&bar->acc_empty[slot][(u - 1) & 1], ((u - 1) >> 1) & 1);
 				tc_fence_after();
 				const uint64_t db = umma_desc_sw128(smem_u32(sB + s * TC_TILE_BYTES));
+				const uint32_t d = tmem + slot * TC_BN;
 #pragma unroll
-				for (int h = 0; h < 2; h++, m++) {
-					const uint32_t slot = m % TC_SLOTS;
-					mbar_wait(&bar->acc_empty[slot], ((m / TC_SLOTS) & 1) ^ 1);   // the epilogue drained this accumulator
-					tc_fence_after();
-					const uint32_t d = tmem + slot * TC_BN;
-					const uint32_t a = tmem + (uint32_t)(TC_A_COL + h * (TC_K / 2));
-#pragma unroll
-					for (int kk = 0; kk < TC_K / 16; kk++)               // 16 bf16 = 8 TMEM columns of A = 32 bytes = 2 descriptor units of B
-						umma_bf16_ts(d, a + 8 * kk, db + 2 * kk, idesc, kk != 0 ? 1u : 0u);
-					umma_commit(&bar->acc_full[slot]);
-				}
+				for (int kk = 0; kk < TC_K / 16; kk++)               // 16 bf16 = 8 TMEM columns of A = 32 bytes = 2 descriptor units of B
+					umma_bf16_ts(d, a + 8 * kk, db + 2 * kk, idesc, kk != 0 ? 1u : 0u);
+				umma_commit(&bar->acc_full[slot][u & 1]);
 				if (++t == P.b_tiles) t = 0;
 			}
 		}
@@ -234,9 +244,17 @@ filter_kernel(const __grid_constant__ CUtensorMap tmB, FilterArgs P) {
 			const int base = atomicAdd(P.cand_count + row, n_pend);
 #pragma unroll
 			for (int i = 0; i < TC_PEND; i++)
-				if (i < n_pend && base + i < TC_CAND_CAP) P.cand[(size_t)row * TC_CAND_CAP + base + i] = s_pend[i * (32 * TC_EPI_WARPS) + e];
+				if (i < n_pend && base + i < TC_CAND_CAP)
+					reinterpret_cast<int2*>(P.cand)[(size_t)row * TC_CAND_CAP + base + i] =
+					    make_int2(s_pend[i * (32 * TC_EPI_WARPS) + e], s_pend[(TC_PEND + i) * (32 * TC_EPI_WARPS) + e]);
 			n_pend = 0;
 		};
+		static_assert(TC_SLOTS == 3, "the slot / use-count stepping below is written for three slots");
+		const uint32_t bfull_addr = smem_u32(&bar->b_full[0]), bempty_addr = smem_u32(&bar->b_empty[0]);
+		const uint32_t accfull_addr = smem_u32(&bar->acc_full[0][0]), accempty_addr = smem_u32(&bar->acc_empty[0][0]);
+		const uint32_t snb_addr = smem_u32(s_nb);
+		uint32_t st = 0, sph = 0;                                    // B stage of tile n and the parity of its use
+		uint32_t slot = (uint32_t)h, use = 0;                        // accumulator m = 2 n + h: slot m % 3, use count m / 3
 		for (int n = 0; n < n_tiles; n++) {
 			if (t == 0 || n == 0) {
 				// ---- new row block
@@ -249,7 +267,7 @@ filter_kernel(const __grid_constant__ CUtensorMap tmB, FilterArgs P) {
 				// really attains — the second direction takes it from the first one's matches — the minimum starts there: the true
 				// minimum and its ties are still within tol (the estimate of a column at most bound = tol/2 above the exact value lies
 				// below start + tol; a quarter of tol is added for the float roundings of the start value itself).
-				run = INFINITY;
+				run = live ? INFINITY : -INFINITY;                   // padding rows never pass the candidate test
 				if (P.row_bound && live) {
 					const double ub = P.row_bound[row];
 					if (ub < 1e30) run = __double2float_ru(ub) - na + 0.25f * tol;
@@ -270,21 +288,19 @@ filter_kernel(const __grid_constant__ CUtensorMap tmB, FilterArgs P) {
 					if (lane == 0) mbar_arrive(&bar->a_full);
 				}
 			}
-			const int s = n % TC_STAGES;
-			const uint32_t m = 2u * (uint32_t)n + (uint32_t)h;
-			const uint32_t slot = m % TC_SLOTS;
 			const int col0 = t * TC_BN + ch * TC_EC;
 			// The row's other thread (the other 64 columns of every tile) shares its running minimum: a value tagged with the row block
-			// it belongs to, one 64-bit shared-memory word per thread.  A stale value is still a valid (looser) bound.
-			{
+			// it belongs to, one 64-bit shared-memory word per thread.  A stale value is still a valid (looser) bound, so once every
+			// four tiles is enough after the first eight (where the minimum still moves fast and short shares of a CTA end).
+			if (n < 8 || (n & 3) == 0) {
 				const unsigned long long mine = ((unsigned long long)(uint32_t)rp << 32) | __float_as_uint(run);
 				unsigned long long other;
 				asm volatile("st.shared.b64 [%0], %1;" ::"r"(run_mine), "l"(mine) : "memory");
 				asm volatile("ld.shared.b64 %0, [%1];" : "=l"(other) : "r"(run_other) : "memory");
 				if ((int)(other >> 32) == rp) run = fminf(run, __uint_as_float((uint32_t)other));
 			}
-			mbar_wait(&bar->b_full[s], (n / TC_STAGES) & 1);         // the stage's norms have landed (long since: the MMAs needed its tile)
-			mbar_wait(&bar->acc_full[slot], (m / TC_SLOTS) & 1);
+			mbar_wait_addr(bfull_addr + 8u * st, sph);               // the stage's norms have landed (long since: the MMAs needed its tile)
+			mbar_wait_addr(accfull_addr + 8u * (2u * slot + (use & 1u)), (use >> 1) & 1u);
 			tc_fence_after();
 			// This thread's 64 columns are fetched at once and the accumulator handed back to the MMA issuer before any
 			// arithmetic: the slot is held for one TMEM round trip, not for the reduction.
@@ -294,42 +310,64 @@ filter_kernel(const __grid_constant__ CUtensorMap tmB, FilterArgs P) {
 			tmem_ld_wait(r0); tmem_ld_wait(r1);
 			tc_fence_before();
 			__syncwarp();
-			if (lane == 0) mbar_arrive(&bar->acc_empty[slot]);
-			const float* nb_tile = s_nb + s * TC_NB;
-			const uint32_t nb_addr = smem_u32(nb_tile + ch * TC_EC);
+			if (lane == 0) mbar_arrive_addr(accempty_addr + 8u * (2u * slot + (use & 1u)));
+			const uint32_t nb_addr = snb_addr + (uint32_t)(TC_NB * 4) * st + (uint32_t)(ch * TC_EC * 4);     // this thread's 64 column norms
+			const uint32_t flag_addr = snb_addr + (uint32_t)(TC_NB * 4) * st + (uint32_t)(TC_BN * 4);
 			// Candidate path of one 32-column chunk whose minimum came within tol of the row's running minimum (rare once the minimum
-			// has settled: ~1.3 / columns-seen per column).  val(k) = d' of column k of the chunk.
-			auto emit = [&](float cmin, int c, auto val) {
-				if (cmin <= run + tol && cmin < INFINITY && live) {
-					run = fminf(run, cmin);
-					const float thr = run + tol;
+			// has settled: ~1.3 / columns-seen per column).  val(k) = d' of column k of the chunk.  Dead rows (padding) carry
+			// run = -inf and never get here.
+			// Candidate path of one 32-column chunk whose best column came within tol of the row's running minimum (per row ~1.3 /
+			// columns-seen per column; a 32-lane warp takes it whenever ONE of its rows does: about a third of the tiles of a first
+			// direction at 100k columns).  Kept small on purpose — two larger variants (an unrolled walk with 32 store sites: 4096
+			// instructions of kernel code; a warp-cooperative scan through shared memory) lost more to instruction fetch and
+			// serialisation than they saved: 1.56 -> 2.3 / 1.9 ms per 100k x 100k pass.  A hit goes to the thread's pending list as
+			// (column, cmin): the chunk's best estimate stands in for the estimate of each of its hits — never above the hit's own,
+			// and the estimate of a column that is in the list, which is all the re-score's pruning rule needs.
+			// val(k): k-th value of the chunk; hits are val <= lim (LE) or val >= lim (!LE)
+			auto scan = [&](bool want, float cmin, int c, float lim, auto val, auto le) {
+				constexpr bool LE = decltype(le)::value;
+				if (want) {
 					unsigned hits = 0;
 #pragma unroll
-					for (int k = 0; k < 32; k++) hits |= (val(k) <= thr ? 1u : 0u) << k;
+					for (int k = 0; k < 32; k++) hits |= ((LE ? val(k) <= lim : val(k) >= lim) ? 1u : 0u) << k;
 					while (hits) {
 						const int k = __ffs(hits) - 1;
 						hits &= hits - 1;
 						s_pend[n_pend * (32 * TC_EPI_WARPS) + e] = col0 + c * 32 + k;
+						s_pend[(TC_PEND + n_pend) * (32 * TC_EPI_WARPS) + e] = __float_as_int(cmin);
 						if (++n_pend == TC_PEND) flush();
 					}
 				}
 			};
 			// SURF descriptors are unit vectors: where the 128 column norms of a tile are one and the same float (flagged by
 			// norm_flags_kernel) min_j (nb - 2 s_j) = nb - 2 max_j s_j (fma is monotonic), and the row maximum of the raw accumulators
-			// is all the fast path needs: half an instruction per element, nothing read from shared memory.
-			if (!DBG && nb_tile[TC_BN] != 0.0f) {
-				const float nbc = nb_tile[0];
+			// is all the fast path needs: half an instruction per element, nothing but two words read from shared memory.
+			if (!DBG && lds32(flag_addr) != 0u) {
+				const float nbc = __uint_as_float(lds32(nb_addr));
 				auto row_max = [&](const uint32_t (&r)[32]) {
 					float a[11];
 #pragma unroll
 					for (int i = 0; i < 10; i++) a[i] = fmax3(__uint_as_float(r[3 * i]), __uint_as_float(r[3 * i + 1]), __uint_as_float(r[3 * i + 2]));
 					a[10] = fmaxf(__uint_as_float(r[30]), __uint_as_float(r[31]));
 					const float b0 = fmax3(a[0], a[1], a[2]), b1 = fmax3(a[3], a[4], a[5]), b2 = fmax3(a[6], a[7], a[8]), b3 = fmaxf(a[9], a[10]);
-					return fmaf(-2.0f, fmaxf(fmax3(b0, b1, b2), b3), nbc);
+					return fmaxf(fmax3(b0, b1, b2), b3);
 				};
-				const float c0 = row_max(r0), c1 = row_max(r1);
-				emit(c0, 0, [&](int k) { return fmaf(-2.0f, __uint_as_float(r0[k]), nbc); });
-				emit(c1, 1, [&](int k) { return fmaf(-2.0f, __uint_as_float(r1[k]), nbc); });
+				const float m0 = row_max(r0), m1 = row_max(r1);
+				// one test for both chunks: nothing to do while the tile's best column stays more than tol above the running minimum
+				// one test for both chunks: nothing to do while the tile's best column stays more than tol above the running minimum
+				if (fmaf(-2.0f, fmaxf(m0, m1), nbc) <= run + tol) {
+					// s >= lim is implied by nb - 2 s <= thr: half the difference, less a margin for the roundings of both sides
+					auto chunk = [&](float mx, int c, const uint32_t (&r)[32]) {
+						const float cmin = fmaf(-2.0f, mx, nbc);
+						const bool want = cmin <= run + tol && cmin < INFINITY;
+						if (want) run = fminf(run, cmin);
+						const float thr = run + tol;
+						const float lim = 0.5f * (nbc - thr) - 1e-6f * (fabsf(nbc) + fabsf(thr));
+						scan(want, cmin, c, lim, [&](int k) { return __uint_as_float(r[k]); }, std::false_type());
+					};
+					chunk(m0, 0, r0);
+					chunk(m1, 1, r1);
+				}
 			} else {
 				// general norms: d' = |b_j|^2 - 2 s_j in place (packed pairs), then the same tree of three-input minima
 				auto row_min = [&](uint32_t (&r)[32], int c) {
@@ -355,11 +393,22 @@ filter_kernel(const __grid_constant__ CUtensorMap tmB, FilterArgs P) {
 					return fminf(fmin3(b0, b1, b2), b3);
 				};
 				const float c0 = row_min(r0, 0), c1 = row_min(r1, 1);
-				emit(c0, 0, [&](int k) { return __uint_as_float(r0[k]); });
-				emit(c1, 1, [&](int k) { return __uint_as_float(r1[k]); });
+				if (fminf(c0, c1) <= run + tol) {
+					auto chunk = [&](float cmin, int c, const uint32_t (&r)[32]) {
+						const bool want = cmin <= run + tol && cmin < INFINITY;
+						if (want) run = fminf(run, cmin);
+						scan(want, cmin, c, run + tol, [&](int k) { return __uint_as_float(r[k]); }, std::true_type());
+					};
+					chunk(c0, 0, r0);
+					chunk(c1, 1, r1);
+				}
 			}
 			__syncwarp();
-			if (lane == 0) mbar_arrive(&bar->b_empty[s]);            // this warp is done with the stage's norms
+			if (lane == 0) mbar_arrive_addr(bempty_addr + 8u * st);  // this warp is done with the stage's norms
+			// next tile: stage and its phase, accumulator slot and its use count (m advances by two: slot (m % 3) steps back by one,
+			// the use count m / 3 goes up whenever the slot does not wrap), column tile and row block
+			if (++st == (uint32_t)TC_STAGES) { st = 0; sph ^= 1u; }
+			if (slot == 0) slot = TC_SLOTS - 1; else { slot--; use++; }
 			if (++t == P.b_tiles) { t = 0; rp++; }
 		}
 		flush();
@@ -371,8 +420,12 @@ filter_kernel(const __grid_constant__ CUtensorMap tmB, FilterArgs P) {
 
 // ---------------------------------------------------------------- 3. exact re-score
 // one warp per row of A: exact distance to every candidate column of B; mode 0 -> pairs/fit, mode 1 -> column statistics
+// A candidate carries the filter's estimate d' of its column: only those within tol of the smallest estimate of the list can be the
+// exact minimum or tie with it (each estimate is within tol / 2 of the exact value), so the early entries of a list — emitted while the
+// row's running minimum was still loose — are dropped without touching their descriptors: ~17 -> ~1.5 exact distances per row.
 __global__ void rescore_kernel(const double* __restrict__ A, int nA, const double* __restrict__ B, const int* __restrict__ cand_count,
-                               const int* __restrict__ cand, int mode, double max_fit, int index_offset, int32_t* __restrict__ pairs,
+                               const int* __restrict__ cand, const float* __restrict__ norm_a, const unsigned* __restrict__ max_norm_b_bits,
+                               int mode, double max_fit, int index_offset, int32_t* __restrict__ pairs,
                                double* __restrict__ fit, double* __restrict__ o_min, int32_t* __restrict__ o_first,
                                int32_t* __restrict__ o_last, int* __restrict__ overflow) {
 	const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
@@ -383,8 +436,15 @@ __global__ void rescore_kernel(const double* __restrict__ A, int nA, const doubl
 	const double* a = A + (size_t)row * TC_DOF;
 	double best = CUDART_INF;
 	int first = -1, last = -1;
+	const int2* list = reinterpret_cast<const int2*>(cand) + (size_t)row * TC_CAND_CAP;
+	const int2 c0 = lane < cnt ? list[lane] : make_int2(-1, 0x7f800000), c1 = lane + 32 < cnt ? list[lane + 32] : make_int2(-1, 0x7f800000);
+	float est_min = fminf(__int_as_float(c0.y), __int_as_float(c1.y));
+	for (int d = 16; d > 0; d >>= 1) est_min = fminf(est_min, __shfl_xor_sync(0xffffffffu, est_min, d));
+	const float keep = est_min + tolerance_of(norm_a[norm_index(row)], __uint_as_float(*max_norm_b_bits));
 	for (int c = lane; c < cnt; c += 32) {
-		const int j = cand[(size_t)row * TC_CAND_CAP + c];
+		const int2 cj = c < 32 ? c0 : c1;
+		if (!(__int_as_float(cj.y) <= keep)) continue;
+		const int j = cj.x;
 		const double* b = B + (size_t)j * TC_DOF;
 		double s = 0.0;
 		// DescriptorDistance.euclideanSq :55-64, same order, no FMA.  The candidate's row is fetched 16 values at a time
@@ -462,6 +522,7 @@ int tc_pad_rows(int n) { return ((n + TC_MROWS - 1) / TC_MROWS) * TC_MROWS; }
 size_t tc_operand_bytes(int n) { return (size_t)tc_pad_rows(n) * TC_K * 2; }
 size_t tc_norm_bytes(int n) { return (size_t)(tc_pad_rows(n) / TC_BN) * TC_NB * 4; }
 int tc_cand_cap() { return TC_CAND_CAP; }
+size_t tc_cand_bytes(size_t rows) { return rows * TC_CAND_CAP * 8; }   // (column, estimate) per candidate
 bool tc_supported(int dof) { return dof == TC_DOF; }
 
 void launch_tc_split(const double* d_x, int n, void* d_operand, float* d_norm, unsigned* d_max_norm_bits, cudaStream_t st) {
@@ -513,11 +574,12 @@ void launch_tc_row_bounds(const int32_t* d_pairs, const double* d_fit, int n, in
 	BS_LAUNCH(row_bounds_kernel, div_up(n, 256), 256, 0, st, d_pairs, d_fit, n, m, reinterpret_cast<unsigned long long*>(d_bound));
 }
 
-void launch_tc_rescore(const double* d_A, int nA, const double* d_B, const int* d_cand_count, const int* d_cand, int mode, double max_fit,
+void launch_tc_rescore(const double* d_A, int nA, const double* d_B, const int* d_cand_count, const int* d_cand, const float* d_norm_a,
+                       const unsigned* d_max_norm_b_bits, int mode, double max_fit,
                        int index_offset, int32_t* pairs, double* fit, double* o_min, int32_t* o_first, int32_t* o_last, int* d_overflow,
                        cudaStream_t st) {
 	if (nA <= 0) return;
-	BS_LAUNCH(rescore_kernel, div_up(nA, 8), 256, 0, st, d_A, nA, d_B, d_cand_count, d_cand, mode, max_fit, index_offset, pairs, fit, o_min,
+	BS_LAUNCH(rescore_kernel, div_up(nA, 8), 256, 0, st, d_A, nA, d_B, d_cand_count, d_cand, d_norm_a, d_max_norm_b_bits, mode, max_fit, index_offset, pairs, fit, o_min,
 	          o_first, o_last, d_overflow);
 }
 

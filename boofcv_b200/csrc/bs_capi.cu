@@ -1124,7 +1124,7 @@ struct bs_assoc {
 		norm_src.reserve(tc_norm_bytes(n)); norm_dst.reserve(tc_norm_bytes(m));
 		tc_scalars.reserve(16);
 		const size_t rows = (size_t)std::max(n, m);
-		cand_count.reserve(rows * 4); cand.reserve(rows * tc_cand_cap() * 4);
+		cand_count.reserve(rows * 4); cand.reserve(tc_cand_bytes(rows));
 		unsigned* sc = tc_scalars.as<unsigned>();
 		launch_tc_split(src, n, op_src.p, norm_src.as<float>(), sc + 0, st);
 		launch_tc_split(dst, m, op_dst.p, norm_dst.as<float>(), sc + 1, st);
@@ -1139,12 +1139,12 @@ struct bs_assoc {
 		int* overflow = reinterpret_cast<int*>(sc + 2);
 		launch_tc_filter(op_src.p, norm_src.as<float>(), n, op_dst.p, norm_dst.as<float>(), sc + 1, m, cand_count.as<int>(), cand.as<int>(),
 		                 nullptr, sm_count, st);
-		launch_tc_rescore(src, n, dst, cand_count.as<int>(), cand.as<int>(), 0, max_fit, 0, pairs, fit, nullptr, nullptr, nullptr, overflow, st);
+		launch_tc_rescore(src, n, dst, cand_count.as<int>(), cand.as<int>(), norm_src.as<float>(), sc + 1, 0, max_fit, 0, pairs, fit, nullptr, nullptr, nullptr, overflow, st);
 		tc_bound.reserve((size_t)m * 8);
 		launch_tc_row_bounds(pairs, fit, n, m, tc_bound.as<double>(), st);
 		launch_tc_filter(op_dst.p, norm_dst.as<float>(), m, op_src.p, norm_src.as<float>(), sc + 0, n, cand_count.as<int>(), cand.as<int>(),
 		                 nullptr, sm_count, st, tc_bound.as<double>());
-		launch_tc_rescore(dst, m, src, cand_count.as<int>(), cand.as<int>(), 1, 0.0, row_offset, nullptr, nullptr, cmin, cfirst, clast, overflow, st);
+		launch_tc_rescore(dst, m, src, cand_count.as<int>(), cand.as<int>(), norm_dst.as<float>(), sc + 0, 1, 0.0, row_offset, nullptr, nullptr, cmin, cfirst, clast, overflow, st);
 		int h_overflow = 0;
 		BS_CUDA(cudaMemcpyAsync(&h_overflow, overflow, 4, cudaMemcpyDeviceToHost, st));
 		BS_CUDA(cudaStreamSynchronize(st));
@@ -1157,7 +1157,7 @@ struct bs_assoc {
 		norm_src.reserve(tc_norm_bytes(n)); norm_dst.reserve(tc_norm_bytes(m));
 		tc_scalars.reserve(16);
 		const size_t rows = (size_t)std::max(n, m);
-		cand_count.reserve(rows * 4); cand.reserve(rows * tc_cand_cap() * 4);
+		cand_count.reserve(rows * 4); cand.reserve(tc_cand_bytes(rows));
 		col_min.reserve((size_t)m * 8); col_first.reserve((size_t)m * 4); col_last.reserve((size_t)m * 4);
 		tc_bound.reserve((size_t)m * 8);
 	}
@@ -1168,7 +1168,7 @@ struct bs_assoc {
 		unsigned* sc = tc_scalars.as<unsigned>();
 		launch_tc_filter(op_src.p, norm_src.as<float>(), n, op_dst.p, norm_dst.as<float>(), sc + 1, m, cand_count.as<int>(), cand.as<int>(),
 		                 nullptr, sm_count, st);
-		launch_tc_rescore(src, n, dst, cand_count.as<int>(), cand.as<int>(), 0, max_fit, 0, pairs, fit, nullptr, nullptr, nullptr, overflow, st);
+		launch_tc_rescore(src, n, dst, cand_count.as<int>(), cand.as<int>(), norm_src.as<float>(), sc + 1, 0, max_fit, 0, pairs, fit, nullptr, nullptr, nullptr, overflow, st);
 		if (backwards) {
 			col_min.reserve((size_t)m * 8); col_first.reserve((size_t)m * 4); col_last.reserve((size_t)m * 4);
 			// the column minimum of j is at most the fit of any row that chose j: the second direction starts from it
@@ -1176,7 +1176,7 @@ struct bs_assoc {
 			launch_tc_row_bounds(pairs, fit, n, m, tc_bound.as<double>(), st);
 			launch_tc_filter(op_dst.p, norm_dst.as<float>(), m, op_src.p, norm_src.as<float>(), sc + 0, n, cand_count.as<int>(), cand.as<int>(),
 			                 nullptr, sm_count, st, tc_bound.as<double>());
-			launch_tc_rescore(dst, m, src, cand_count.as<int>(), cand.as<int>(), 1, 0.0, 0, nullptr, nullptr, col_min.as<double>(),
+			launch_tc_rescore(dst, m, src, cand_count.as<int>(), cand.as<int>(), norm_dst.as<float>(), sc + 0, 1, 0.0, 0, nullptr, nullptr, col_min.as<double>(),
 			                  col_first.as<int32_t>(), col_last.as<int32_t>(), overflow, st);
 			launch_validate(n, 0, pairs, fit, col_min.as<double>(), col_first.as<int32_t>(), col_last.as<int32_t>(), st);
 		}
@@ -1468,6 +1468,18 @@ int bs_assoc_forward_device(bs_assoc* a, const double* d_src, int n, int row_off
 	});
 }
 
+int bs_assoc_forward_only_device(bs_assoc* a, const double* d_src, int n, const double* d_dst, int m, int dof, int32_t* d_pairs,
+                                 double* d_fit, void* stream) {
+	return guarded([&] {
+		if (!a) fail(BS_ERR_ARG, "handle is null");
+		if ((n > 0 && (!d_src || !d_pairs || !d_fit)) || (m > 0 && !d_dst)) fail(BS_ERR_ARG, "null argument");
+		DeviceGuard g(a->device);
+		struct Restore { bs_assoc* a; int b; ~Restore() { a->backwards = b; } } restore{a, a->backwards};
+		a->backwards = 0;
+		a->run(d_src, n, d_dst, m, dof, d_pairs, d_fit, stream ? static_cast<cudaStream_t>(stream) : a->stream);
+	});
+}
+
 int bs_assoc_merge_columns_device(bs_assoc* a, int ranks, int m, const double* d_all_min, const int32_t* d_all_first,
                                   const int32_t* d_all_last, double* d_col_min, int32_t* d_col_first, int32_t* d_col_last,
                                   void* stream) {
@@ -1477,6 +1489,20 @@ int bs_assoc_merge_columns_device(bs_assoc* a, int ranks, int m, const double* d
 		DeviceGuard g(a->device);
 		launch_merge_columns(ranks, m, d_all_min, d_all_first, d_all_last, d_col_min, d_col_first, d_col_last,
 		                     stream ? static_cast<cudaStream_t>(stream) : a->stream);
+	});
+}
+
+int bs_assoc_merge_packed_device(bs_assoc* a, int ranks, int m, const void* d_packed, double* d_col_min, int32_t* d_col_first,
+                                 int32_t* d_col_last, void* stream) {
+	return guarded([&] {
+		if (!a) fail(BS_ERR_ARG, "handle is null");
+		if (ranks < 1 || m < 0) fail(BS_ERR_ARG, "bad sizes");
+		if (m > 0 && (!d_packed || !d_col_min || !d_col_first || !d_col_last)) fail(BS_ERR_ARG, "null argument");
+		DeviceGuard g(a->device);
+		const char* base = static_cast<const char*>(d_packed);
+		launch_merge_columns(ranks, m, reinterpret_cast<const double*>(base), reinterpret_cast<const int32_t*>(base + (size_t)m * 8),
+		                     reinterpret_cast<const int32_t*>(base + (size_t)m * 12), d_col_min, d_col_first, d_col_last,
+		                     stream ? static_cast<cudaStream_t>(stream) : a->stream, 2L * m, 4L * m);
 	});
 }
 

@@ -214,7 +214,9 @@ void launch_tc_filter(const void* d_opA, const float* d_normA, int nA, const voi
                       const unsigned* d_max_norm_b_bits, int nB, int* d_cand_count, int* d_cand, float* d_dbg, int sm_count,
                       cudaStream_t st, const double* d_row_bound = nullptr);
 void launch_tc_row_bounds(const int32_t* d_pairs, const double* d_fit, int n, int m, double* d_bound, cudaStream_t st);
-void launch_tc_rescore(const double* d_A, int nA, const double* d_B, const int* d_cand_count, const int* d_cand, int mode, double max_fit,
+size_t tc_cand_bytes(size_t rows);
+void launch_tc_rescore(const double* d_A, int nA, const double* d_B, const int* d_cand_count, const int* d_cand, const float* d_norm_a,
+                       const unsigned* d_max_norm_b_bits, int mode, double max_fit,
                        int index_offset, int32_t* pairs, double* fit, double* o_min, int32_t* o_first, int32_t* o_last, int* d_overflow,
                        cudaStream_t st);
 int rowmin_splits(int nA, int nB, int sm_count);
@@ -224,7 +226,7 @@ void launch_rowmin_finalize(const RowminScratch& s, int nA, int splits, int mode
 void launch_validate(int n, int row_offset, int32_t* pairs, double* fit, const double* col_min, const int32_t* col_first,
                      const int32_t* col_last, cudaStream_t st);
 void launch_merge_columns(int ranks, int m, const double* a_min, const int32_t* a_first, const int32_t* a_last, double* o_min,
-                          int32_t* o_first, int32_t* o_last, cudaStream_t st);
+                          int32_t* o_first, int32_t* o_last, cudaStream_t st, long stride_min = 0, long stride_idx = 0);
 
 // AssociateSurfBasic helpers (bs_assoc_surf.cu)
 void launch_partition_white(const uint8_t* d_white, int n, int32_t* d_idx, int32_t* d_count, cudaStream_t st);

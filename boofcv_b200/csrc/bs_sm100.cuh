@@ -36,6 +36,20 @@ __device__ __forceinline__ bool mbar_try_wait(uint32_t addr, uint32_t parity) {
 	    : "memory");
 	return done != 0;
 }
+__device__ __forceinline__ void mbar_wait_addr(uint32_t addr, uint32_t parity) {
+	uint32_t spin = 0;
+#pragma unroll 1
+	while (!mbar_try_wait(addr, parity))
+		if (++spin == (1u << 24)) __trap();
+}
+__device__ __forceinline__ void mbar_arrive_addr(uint32_t addr) {
+	asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(addr) : "memory");
+}
+__device__ __forceinline__ uint32_t lds32(uint32_t addr) {
+	uint32_t v;
+	asm volatile("ld.shared.b32 %0, [%1];" : "=r"(v) : "r"(addr));
+	return v;
+}
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
 	const uint32_t addr = smem_u32(bar);
 	uint32_t spin = 0;

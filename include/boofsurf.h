@@ -299,9 +299,18 @@ int bs_assoc_frames_batch_device(bs_assoc* a, bs_surf* s, int n_pairs, const int
 int bs_assoc_forward_device(bs_assoc* a, const double* d_src, int n, int row_offset, const double* d_dst, int m,
                             int dof, int32_t* d_pairs, double* d_fit, double* d_col_min, int32_t* d_col_first,
                             int32_t* d_col_last, void* stream);
+/* The forward pass alone (AssociateGreedy.java:76-96, no backward validation whatever the handle was created with): what a
+ * rank of a sharded association runs when backwardsValidation is off — no column statistics, no exchange step. */
+int bs_assoc_forward_only_device(bs_assoc* a, const double* d_src, int n, const double* d_dst, int m, int dof,
+                                 int32_t* d_pairs, double* d_fit, void* stream);
 int bs_assoc_merge_columns_device(bs_assoc* a, int ranks, int m, const double* d_all_min, const int32_t* d_all_first,
                                   const int32_t* d_all_last, double* d_col_min, int32_t* d_col_first,
                                   int32_t* d_col_last, void* stream);
+/* The same merge for ONE packed record per rank, which is what a single all-gather moves: rank r's record starts at
+ * d_packed + r*16*m bytes and holds col_min[m] (double), then col_first[m], then col_last[m] (int32) — i.e. the three outputs
+ * of bs_assoc_forward_device written into one 16*m-byte buffer. */
+int bs_assoc_merge_packed_device(bs_assoc* a, int ranks, int m, const void* d_packed, double* d_col_min,
+                                 int32_t* d_col_first, int32_t* d_col_last, void* stream);
 int bs_assoc_validate_device(bs_assoc* a, int n, int row_offset, int32_t* d_pairs, double* d_fit,
                              const double* d_col_min, const int32_t* d_col_first, const int32_t* d_col_last,
                              void* stream);

@@ -7,18 +7,92 @@
 #include <functional>
 #include <numeric>
 #include <stdexcept>
+#include <atomic>
+#include <condition_variable>
+#include <mutex>
 #include <thread>
 
 namespace orc {
 
-// BoofConcurrency.loopFor (TY/concurrency/BoofConcurrency.java:82-88) stand-in: static interleaved split.
+// BoofConcurrency.loopFor (TY/concurrency/BoofConcurrency.java:82-88, :158-177) stand-in.  The reference hands the index range to
+// a persistent ForkJoinPool, which splits it into contiguous sub-ranges that idle workers steal; here a persistent pool of
+// worker threads (created once, parked on a condition variable between loops) takes contiguous chunks of the range off an
+// atomic counter.  Spawning and joining fresh std::threads for each of the ~30 loops of a frame — what this file did before —
+// cost more than the loops themselves beyond 16 threads.  Every body(i) writes its own outputs, so results do not depend on
+// which thread runs which chunk.
+namespace {
+class Pool {
+public:
+	static Pool& get() { static Pool p; return p; }
+	void run(int begin, int end, int nthreads, const std::function<void(int)>& body) {
+		const int n = end - begin;
+		const int nt = std::min(nthreads, n);
+		std::unique_lock<std::mutex> job_lock(job_mutex_);              // one loop at a time (nested or concurrent callers queue up)
+		grow(nt - 1);
+		{
+			std::lock_guard<std::mutex> lk(m_);
+			body_ = &body; begin_ = begin; end_ = end;
+			chunk_ = std::max(1, n / (nt * 4));                         // ~4 chunks per thread: contiguous blocks, balanced tails
+			next_.store(begin, std::memory_order_relaxed);
+			want_ = nt - 1; active_ = nt - 1;
+			epoch_++;
+		}
+		cv_.notify_all();
+		work();
+		std::unique_lock<std::mutex> lk(m_);
+		done_cv_.wait(lk, [&] { return active_ == 0; });
+		body_ = nullptr;
+	}
+private:
+	Pool() {}
+	~Pool() {
+		{ std::lock_guard<std::mutex> lk(m_); stop_ = true; epoch_++; }
+		cv_.notify_all();
+		for (auto& t : threads_) t.join();
+	}
+	void grow(int n) {
+		while ((int)threads_.size() < n) {
+			const int id = (int)threads_.size();
+			threads_.emplace_back([this, id] { loop(id); });
+		}
+	}
+	void work() {
+		for (;;) {
+			const int i0 = next_.fetch_add(chunk_, std::memory_order_relaxed);
+			if (i0 >= end_) break;
+			const int i1 = std::min(end_, i0 + chunk_);
+			for (int i = i0; i < i1; i++) (*body_)(i);
+		}
+	}
+	void loop(int id) {
+		unsigned long seen = 0;
+		for (;;) {
+			{
+				std::unique_lock<std::mutex> lk(m_);
+				cv_.wait(lk, [&] { return epoch_ != seen; });
+				seen = epoch_;
+				if (stop_) return;
+				if (id >= want_) continue;                                  // this loop uses fewer threads than the pool holds
+			}
+			work();
+			std::lock_guard<std::mutex> lk(m_);
+			if (--active_ == 0) done_cv_.notify_one();
+		}
+	}
+	std::mutex job_mutex_, m_;
+	std::condition_variable cv_, done_cv_;
+	std::vector<std::thread> threads_;
+	const std::function<void(int)>* body_ = nullptr;
+	std::atomic<int> next_{0};
+	int begin_ = 0, end_ = 0, chunk_ = 1, want_ = 0, active_ = 0;
+	unsigned long epoch_ = 0;
+	bool stop_ = false;
+};
+}  // namespace
+
 static void parallel_for(int begin, int end, int nthreads, const std::function<void(int)>& body) {
 	if (nthreads <= 1 || end - begin <= 1) { for (int i = begin; i < end; i++) body(i); return; }
-	std::vector<std::thread> pool;
-	int nt = std::min(nthreads, end - begin);
-	for (int t = 0; t < nt; t++)
-		pool.emplace_back([=, &body] { for (int i = begin + t; i < end; i += nt) body(i); });
-	for (auto& th : pool) th.join();
+	Pool::get().run(begin, end, nthreads, body);
 }
 
 // ===================================================================== integral image

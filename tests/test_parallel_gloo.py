@@ -111,7 +111,8 @@ def _worker(rank, world, port, cases, out):
             src, dst = _case(seed, n, m)
             b, e = parallel.shard_range(n, rank, world)
             sa = parallel.ShardedAssociate(NumpyBackend(max_fit), backwards)
-            pairs, fit = sa.associate(torch.from_numpy(src[b:e].copy()), torch.from_numpy(dst))
+            # the caller may pass the global index of its first row (shard_range knows it) and save the all-gather of the shard sizes
+            pairs, fit = sa.associate(torch.from_numpy(src[b:e].copy()), torch.from_numpy(dst), row_offset=b if seed % 2 else None)
             gp, gf = parallel.gather_matches(pairs, fit)
             res.append((gp, gf))
         if rank == 0:

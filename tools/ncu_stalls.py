@@ -1,5 +1,5 @@
 """Stall / instruction-mix digest of one kernel out of an ncu --set full --import-source on report.
-usage: python tools/ncu_stalls.py report.ncu-rep [top_n]"""
+usage: python tools/ncu_stalls.py report.ncu-rep [top_n] [launch_index]   (launch_index: which launch of a multi-kernel report)"""
 import csv
 import subprocess
 import sys
@@ -7,6 +7,10 @@ from collections import Counter
 
 out = subprocess.run(["ncu", "-i", sys.argv[1], "--page", "source", "--csv", "--print-source", "sass"], capture_output=True, text=True).stdout
 rows = list(csv.reader(out.splitlines()))
+starts = [i for i, r in enumerate(rows) if r and r[0] == "Kernel Name"] + [len(rows)]
+k = int(sys.argv[3]) if len(sys.argv) > 3 else 0
+rows = rows[starts[k]:starts[k + 1]]
+print("launch", k, "of", len(starts) - 1, ":", rows[0][1][:100])
 h = rows[1]; c = {n: i for i, n in enumerate(h)}
 data = rows[2:]
 I = lambda r, n: int(r[c[n]] or 0)
