@@ -419,63 +419,82 @@ filter_kernel(const __grid_constant__ CUtensorMap tmB, FilterArgs P) {
 }
 
 // ---------------------------------------------------------------- 3. exact re-score
-// one warp per row of A: exact distance to every candidate column of B; mode 0 -> pairs/fit, mode 1 -> column statistics
+// one THREAD per row of A: exact distance to the candidate columns of B that survive the pruning; mode 0 -> pairs/fit, mode 1 ->
+// column statistics.
 // A candidate carries the filter's estimate d' of its column: only those within tol of the smallest estimate of the list can be the
 // exact minimum or tie with it (each estimate is within tol / 2 of the exact value), so the early entries of a list — emitted while the
 // row's running minimum was still loose — are dropped without touching their descriptors: ~17 -> ~1.5 exact distances per row.
-__global__ void rescore_kernel(const double* __restrict__ A, int nA, const double* __restrict__ B, const int* __restrict__ cand_count,
-                               const int* __restrict__ cand, const float* __restrict__ norm_a, const unsigned* __restrict__ max_norm_b_bits,
-                               int mode, double max_fit, int index_offset, int32_t* __restrict__ pairs,
-                               double* __restrict__ fit, double* __restrict__ o_min, int32_t* __restrict__ o_first,
-                               int32_t* __restrict__ o_last, int* __restrict__ overflow) {
-	const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-	const int lane = threadIdx.x & 31;
-	if (row >= nA) return;
-	int cnt = cand_count[row];
-	if (cnt > TC_CAND_CAP) { if (lane == 0) atomicExch(overflow, 1); cnt = TC_CAND_CAP; }
-	const double* a = A + (size_t)row * TC_DOF;
+// With so few survivors a warp per row left 30 of 32 lanes idle through 192 fp64 instructions per candidate (the fp64 pipe was the
+// limit: 116 us per 100k rows); with a row per lane the lanes walk their survivors in lockstep (first survivor of every row, then
+// the second, ...), so a warp's fp64 instructions serve 32 rows.
+constexpr int RS_KEEP = 4;                 // survivors held in registers; a row with more takes the slow loop below
+__device__ __forceinline__ double exact_sq64(const double* __restrict__ a, const double* __restrict__ b) {
+	// DescriptorDistance.euclideanSq :55-64, same order, no FMA; 16 values of each row in flight ahead of the serial sum
+	const double2* a2 = reinterpret_cast<const double2*>(a);
+	const double2* b2 = reinterpret_cast<const double2*>(b);
+	double s = 0.0;
+#pragma unroll 1
+	for (int k0 = 0; k0 < TC_DOF / 2; k0 += 8) {
+		double2 bv[8], av[8];
+#pragma unroll
+		for (int u = 0; u < 8; u++) { bv[u] = __ldg(b2 + k0 + u); av[u] = __ldg(a2 + k0 + u); }
+#pragma unroll
+		for (int u = 0; u < 8; u++) {
+			const double d0 = av[u].x - bv[u].x;
+			s += d0 * d0;
+			const double d1 = av[u].y - bv[u].y;
+			s += d1 * d1;
+		}
+	}
+	return s;
+}
+__global__ void __launch_bounds__(128)
+rescore_kernel(const double* __restrict__ A, int nA, const double* __restrict__ B, const int* __restrict__ cand_count,
+               const int* __restrict__ cand, const float* __restrict__ norm_a, const unsigned* __restrict__ max_norm_b_bits,
+               int mode, double max_fit, int index_offset, int32_t* __restrict__ pairs,
+               double* __restrict__ fit, double* __restrict__ o_min, int32_t* __restrict__ o_first,
+               int32_t* __restrict__ o_last, int* __restrict__ overflow) {
+	const int row = blockIdx.x * blockDim.x + threadIdx.x;
+	const bool live = row < nA;
+	int cnt = live ? cand_count[row] : 0;
+	if (cnt > TC_CAND_CAP) { atomicExch(overflow, 1); cnt = TC_CAND_CAP; }
+	const int2* list = reinterpret_cast<const int2*>(cand) + (size_t)(live ? row : 0) * TC_CAND_CAP;
+	float est_min = INFINITY;
+	for (int c = 0; c < cnt; c++) est_min = fminf(est_min, __int_as_float(list[c].y));
+	const float keep = live ? est_min + tolerance_of(norm_a[norm_index(row)], __uint_as_float(*max_norm_b_bits)) : 0.0f;
+	int kept[RS_KEEP];
+	int nk = 0;
+	for (int c = 0; c < cnt; c++) {
+		const int2 cj = list[c];
+		if (__int_as_float(cj.y) <= keep) {
+#pragma unroll
+			for (int t = 0; t < RS_KEEP; t++) if (nk == t) kept[t] = cj.x;
+			nk++;
+		}
+	}
+	const double* a = A + (size_t)(live ? row : 0) * TC_DOF;
 	double best = CUDART_INF;
 	int first = -1, last = -1;
-	const int2* list = reinterpret_cast<const int2*>(cand) + (size_t)row * TC_CAND_CAP;
-	const int2 c0 = lane < cnt ? list[lane] : make_int2(-1, 0x7f800000), c1 = lane + 32 < cnt ? list[lane + 32] : make_int2(-1, 0x7f800000);
-	float est_min = fminf(__int_as_float(c0.y), __int_as_float(c1.y));
-	for (int d = 16; d > 0; d >>= 1) est_min = fminf(est_min, __shfl_xor_sync(0xffffffffu, est_min, d));
-	const float keep = est_min + tolerance_of(norm_a[norm_index(row)], __uint_as_float(*max_norm_b_bits));
-	for (int c = lane; c < cnt; c += 32) {
-		const int2 cj = c < 32 ? c0 : c1;
-		if (!(__int_as_float(cj.y) <= keep)) continue;
-		const int j = cj.x;
-		const double* b = B + (size_t)j * TC_DOF;
-		double s = 0.0;
-		// DescriptorDistance.euclideanSq :55-64, same order, no FMA.  The candidate's row is fetched 16 values at a time
-		// (eight 16-byte loads in flight per lane) ahead of the serial sum; the a row is a broadcast load
-		const double2* b2 = reinterpret_cast<const double2*>(b);
-		const double2* a2 = reinterpret_cast<const double2*>(a);
-#pragma unroll 1
-		for (int k0 = 0; k0 < TC_DOF / 2; k0 += 8) {
-			double2 bv[8], av[8];
-#pragma unroll
-			for (int u = 0; u < 8; u++) { bv[u] = __ldg(b2 + k0 + u); av[u] = __ldg(a2 + k0 + u); }
-#pragma unroll
-			for (int u = 0; u < 8; u++) {
-				const double d0 = av[u].x - bv[u].x;
-				s += d0 * d0;
-				const double d1 = av[u].y - bv[u].y;
-				s += d1 * d1;
-			}
-		}
+	auto take = [&](int j) {
+		const double s = exact_sq64(a, B + (size_t)j * TC_DOF);
 		if (first < 0 || s < best) { best = s; first = j; last = j; }
 		else if (s == best) { first = min(first, j); last = max(last, j); }
+	};
+	const int rounds = __reduce_max_sync(0xffffffffu, min(nk, RS_KEEP));
+	for (int t = 0; t < rounds; t++) {
+		int j = -1;
+#pragma unroll
+		for (int u = 0; u < RS_KEEP; u++) if (t == u && u < nk) j = kept[u];
+		if (j >= 0) take(j);
 	}
-	for (int d = 16; d > 0; d >>= 1) {
-		const double ob = __shfl_xor_sync(0xffffffffu, best, d);
-		const int of = __shfl_xor_sync(0xffffffffu, first, d), ol = __shfl_xor_sync(0xffffffffu, last, d);
-		if (of >= 0) {
-			if (first < 0 || ob < best) { best = ob; first = of; last = ol; }
-			else if (ob == best) { first = min(first, of); last = max(last, ol); }
+	if (nk > RS_KEEP) {                     // many near-ties (duplicates): the remaining survivors, one by one
+		int seen = 0;
+		for (int c = 0; c < cnt; c++) {
+			const int2 cj = list[c];
+			if (__int_as_float(cj.y) <= keep) { if (seen >= RS_KEEP) take(cj.x); seen++; }
 		}
 	}
-	if (lane != 0) return;
+	if (!live) return;
 	if (mode == 0) {
 		const bool hit = first >= 0 && best <= max_fit;      // AssociateGreedy.java:80-91
 		pairs[row] = hit ? last : -1;
@@ -579,7 +598,7 @@ void launch_tc_rescore(const double* d_A, int nA, const double* d_B, const int* 
                        int index_offset, int32_t* pairs, double* fit, double* o_min, int32_t* o_first, int32_t* o_last, int* d_overflow,
                        cudaStream_t st) {
 	if (nA <= 0) return;
-	BS_LAUNCH(rescore_kernel, div_up(nA, 8), 256, 0, st, d_A, nA, d_B, d_cand_count, d_cand, d_norm_a, d_max_norm_b_bits, mode, max_fit, index_offset, pairs, fit, o_min,
+	BS_LAUNCH(rescore_kernel, div_up(nA, 128), 128, 0, st, d_A, nA, d_B, d_cand_count, d_cand, d_norm_a, d_max_norm_b_bits, mode, max_fit, index_offset, pairs, fit, o_min,
 	          o_first, o_last, d_overflow);
 }
 
