@@ -171,6 +171,18 @@ class AssociateGreedyGPU:
                                                      offsets.ctypes.data_as(C.c_void_p), C.c_void_p(st)))
         return pairs, fit, offsets
 
+    def associateRetained(self, src, dst, surfBasic=False, stream=None):
+        """AssociateDescription.associate on two retained feature sets (DetectDescribeSurf.retainFrame): previous frame ->
+        current frame without leaving the device (bs_assoc_features_device).  Returns (pairs, fit) torch tensors."""
+        import torch
+        n, _ = src.count()
+        dev = torch.device("cuda", self.device)
+        pairs = torch.empty(max(n, 1), dtype=torch.int32, device=dev)[:n]; fit = torch.empty(max(n, 1), dtype=torch.float64, device=dev)[:n]
+        st = (stream if stream is not None else torch.cuda.current_stream(dev).cuda_stream) or 1
+        N.check(N.lib().bs_assoc_features_device(self._h, src._h, dst._h, int(bool(surfBasic)), C.c_void_p(pairs.data_ptr()),
+                                                 C.c_void_p(fit.data_ptr()), C.c_void_p(st)))
+        return pairs, fit
+
     # device-resident variant (torch float64 tensors [n,dof], [m,dof]); returns (pairs int32[n], fit float64[n]) tensors
     def associateDevice(self, src, dst, stream=None):
         import torch

@@ -66,6 +66,25 @@ __device__ __forceinline__ void sparse_gradient(const T* __restrict__ ii, int W,
 	dy = Arith<T>::sub(bottom, top);
 }
 
+// The Haar wavelet of ConfigSurfDescribe.useHaar (SparseIntegralHaar_NoBorder_F32.java:37-73, _I32): radius r, width 2r, eight
+// integral reads; bounds x0 = y0 = -r, x1 = y1 = r (SparseScaleGradient.isInBounds); (0,0) outside, like SparseGradientSafe.
+template <typename T>
+__device__ __forceinline__ void sparse_haar(const T* __restrict__ ii, int W, int H, int r, int x, int y, T& dx, T& dy) {
+	const int x0 = x - r, y0 = y - r;
+	if ((x0 | y0) < 0 || x + r >= W || y + r >= H) { dx = 0; dy = 0; return; }
+	const int w = 2 * r;
+	const int a = y0 * W + x0, b = y * W + x0, c = (y + r) * W + x0;
+	const T p0 = __ldg(ii + a), p1 = __ldg(ii + (a + r)), p2 = __ldg(ii + (a + w));
+	const T p3 = __ldg(ii + b), p5 = __ldg(ii + (b + w));
+	const T p6 = __ldg(ii + c), p7 = __ldg(ii + (c + r)), p8 = __ldg(ii + (c + w));
+	const T left = Arith<T>::sum4(p7, p1, p6, p0);
+	const T right = Arith<T>::sum4(p8, p2, p7, p1);
+	const T top = Arith<T>::sum4(p5, p2, p3, p0);
+	const T bottom = Arith<T>::sum4(p8, p5, p6, p3);
+	dx = Arith<T>::sub(right, left);
+	dy = Arith<T>::sub(bottom, top);
+}
+
 // SparseIntegralGradient_NoBorder.setWidth (IP/alg/transform/ii/SparseIntegralGradient_NoBorder.java:41-47)
 __device__ __forceinline__ int gradient_radius(double width) {
 	int r = ((int)(width + 0.5)) / 2;

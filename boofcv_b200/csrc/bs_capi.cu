@@ -91,6 +91,7 @@ struct DescribeSetup {
 		if (p.ori_weighted) gaussian2d_odd(o.weight_sigma, o.radius, ori_w.data());
 
 		p.variant = d.variant; p.grid = d.width_large_grid; p.sub = d.width_sub_region; p.sample_width = d.width_sample;
+		p.use_haar = d.use_haar ? 1 : 0;
 		p.overlap = d.variant == 1 ? d.overlap : 0;
 		p.dof = d.width_large_grid * d.width_large_grid * 4;
 		const int region = d.width_large_grid * d.width_sub_region;
@@ -174,6 +175,12 @@ struct PoolBufs {
 }  // namespace
 
 // ====================================================================================================== bs_surf
+// bs_surf_retain: one frame's features, copied out of the pool so that they survive the next detect (include/boofsurf.h)
+struct bs_features {
+	int device = 0, n = 0, dof = 64;
+	DevBuf xy, scale, angle, desc, white, offsets;
+};
+
 struct bs_surf {
 	int device = 0;
 	bs_fh_cfg fh{}; bs_ori_cfg ori{}; bs_desc_cfg desc{};
@@ -789,6 +796,62 @@ int bs_surf_read(bs_surf* s, int frame, double* xy, double* scale, double* angle
 	});
 }
 
+int bs_surf_retain(bs_surf* s, int frame, void* stream, bs_features** out) {
+	return guarded([&] {
+		if (!out) fail(BS_ERR_ARG, "out is null");
+		*out = nullptr;
+		DeviceGuard g(s ? s->device : 0);
+		check_ready(s);
+		if (frame < 0 || frame >= s->batch) fail(BS_ERR_ARG, "frame out of range");
+		const std::vector<int>& fo = s->h_frame_offset;
+		if (fo[s->batch] > s->pool.view.cap) fail(BS_ERR_CAPACITY, "feature pool too small for this batch");
+		std::unique_ptr<bs_features> f(new bs_features());
+		f->device = s->device; f->dof = s->out_dof();
+		const long b = fo[frame];
+		const int n = fo[frame + 1] - fo[frame];
+		f->n = n;
+		const size_t m = (size_t)std::max(n, 1);
+		f->xy.reserve(m * 16); f->scale.reserve(m * 8); f->angle.reserve(m * 8); f->desc.reserve(m * f->dof * 8); f->white.reserve(m);
+		f->offsets.reserve(8);
+		cudaStream_t st = stream ? static_cast<cudaStream_t>(stream) : s->stream;
+		const Pool& p = s->pool.view;
+		if (n > 0) {
+			BS_CUDA(cudaMemcpyAsync(f->xy.p, p.xy + 2 * b, (size_t)n * 16, cudaMemcpyDeviceToDevice, st));
+			BS_CUDA(cudaMemcpyAsync(f->scale.p, p.scale + b, (size_t)n * 8, cudaMemcpyDeviceToDevice, st));
+			BS_CUDA(cudaMemcpyAsync(f->angle.p, p.angle + b, (size_t)n * 8, cudaMemcpyDeviceToDevice, st));
+			BS_CUDA(cudaMemcpyAsync(f->desc.p, p.desc + b * f->dof, (size_t)n * f->dof * 8, cudaMemcpyDeviceToDevice, st));
+			BS_CUDA(cudaMemcpyAsync(f->white.p, p.white + b, (size_t)n, cudaMemcpyDeviceToDevice, st));
+		}
+		const int32_t h_off[2] = {0, n};
+		BS_CUDA(cudaMemcpyAsync(f->offsets.p, h_off, 8, cudaMemcpyHostToDevice, st));
+		BS_CUDA(cudaStreamSynchronize(st));        // the next detect may overwrite the pool on another stream
+		*out = f.release();
+	});
+}
+int bs_features_count(const bs_features* f, int* n, int* dof) {
+	return guarded([&] {
+		if (!f) fail(BS_ERR_ARG, "handle is null");
+		if (n) *n = f->n;
+		if (dof) *dof = f->dof;
+	});
+}
+int bs_features_view(const bs_features* f, bs_surf_device_view* v) {
+	return guarded([&] {
+		if (!f || !v) fail(BS_ERR_ARG, "null argument");
+		v->d_xy = f->xy.as<double>(); v->d_scale = f->scale.as<double>(); v->d_angle = f->angle.as<double>();
+		v->d_desc = f->desc.as<double>(); v->d_white = f->white.as<uint8_t>(); v->d_frame_offset = f->offsets.as<int32_t>();
+		v->total = f->n; v->batch = 1; v->dof = f->dof;
+	});
+}
+int bs_features_destroy(bs_features* f) {
+	return guarded([&] {
+		if (!f) return;
+		DeviceGuard g(f->device);
+		f->xy.release(); f->scale.release(); f->angle.release(); f->desc.release(); f->white.release(); f->offsets.release();
+		delete f;
+	});
+}
+
 int bs_surf_view(bs_surf* s, bs_surf_device_view* v) {
 	return guarded([&] {
 		if (!v) fail(BS_ERR_ARG, "view is null");
@@ -1391,6 +1454,21 @@ int bs_assoc_frames_device(bs_assoc* a, bs_surf* s, int frame_src, int frame_dst
 		const double* dst = p.desc + (long)fo[frame_dst] * dof;
 		if (surf_basic) a->run_surf_basic(src, p.white + fo[frame_src], n, dst, p.white + fo[frame_dst], m, dof, d_pairs, d_fit, st);
 		else a->run(src, n, dst, m, dof, d_pairs, d_fit, st);
+	});
+}
+
+int bs_assoc_features_device(bs_assoc* a, const bs_features* src, const bs_features* dst, int surf_basic, int32_t* d_pairs, double* d_fit,
+                             void* stream) {
+	return guarded([&] {
+		if (!a || !src || !dst) fail(BS_ERR_ARG, "handle is null");
+		if (a->device != src->device || a->device != dst->device) fail(BS_ERR_ARG, "feature sets and associator live on different devices");
+		if (src->dof != dst->dof) fail(BS_ERR_ARG, "source and destination descriptors differ in length");
+		if (src->n > 0 && (!d_pairs || !d_fit)) fail(BS_ERR_ARG, "null argument");
+		DeviceGuard g(a->device);
+		cudaStream_t st = stream ? static_cast<cudaStream_t>(stream) : a->stream;
+		if (surf_basic) a->run_surf_basic(src->desc.as<double>(), src->white.as<uint8_t>(), src->n, dst->desc.as<double>(), dst->white.as<uint8_t>(),
+		                                  dst->n, src->dof, d_pairs, d_fit, st);
+		else a->run(src->desc.as<double>(), src->n, dst->desc.as<double>(), dst->n, src->dof, d_pairs, d_fit, st);
 	});
 }
 

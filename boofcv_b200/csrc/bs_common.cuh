@@ -129,6 +129,7 @@ struct DescribeParams {
 	// descriptor
 	int variant, grid, sub, sample_width, overlap, dof;
 	int radius_descriptor;
+	int use_haar;      // ConfigSurfDescribe.useHaar: the descriptor samples the Haar wavelet instead of the gradient kernel
 	// WrapDetectDescribeSurf sets the orientation's object radius to scale*SURF_SCALE_TO_RADIUS (2.0),
 	// DetectDescribeSurfPlanar (F/alg/feature/detdesc/DetectDescribeSurfPlanar.java:108) to the scale itself (1.0)
 	double ori_object_radius_mult;

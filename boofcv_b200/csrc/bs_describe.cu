@@ -218,13 +218,14 @@ __device__ __forceinline__ bool laplace_sign(const T* __restrict__ ii, int W, in
 
 // sample grid of the descriptor (DescribePointSurfMod samples the overlap once)
 struct DescGeo {
-	int r, regionR, ov, G;
+	int r, regionR, ov, G, haar;
 	float inv_G;                   // (k + 0.5f) * inv_G truncates to k / G
 	double c_x, c_y;
 };
 __device__ __forceinline__ DescGeo desc_geometry(const DescribeParams& P, double x, double y, double scale) {
 	DescGeo g;
 	g.r = gradient_radius(P.sample_width * scale);
+	g.haar = P.use_haar;
 	const int regionSize = P.grid * P.sub;
 	g.regionR = regionSize / 2;
 	g.ov = P.variant == 1 ? P.overlap : 0;
@@ -247,7 +248,8 @@ __device__ __forceinline__ void describe_sample(const T* __restrict__ ii, int W,
 	int pixelX, pixelY;
 	desc_pixel(g, c, s, scale, gxi, gyi, pixelX, pixelY);
 	T dx, dy;
-	sparse_gradient(ii, W, H, g.r, pixelX, pixelY, dx, dy);
+	if (g.haar) sparse_haar(ii, W, H, g.r, pixelX, pixelY, dx, dy);
+	else sparse_gradient(ii, W, H, g.r, pixelX, pixelY, dx, dy);
 	gx[k] = dx; gy[k] = dy;
 }
 

@@ -39,7 +39,6 @@ void check_ori_cfg(const bs_ori_cfg& c) {
 }
 void check_desc_cfg(const bs_desc_cfg& c) {
 	if (c.variant != 0 && c.variant != 1) fail(BS_ERR_ARG, "descriptor variant must be 0 (Speed) or 1 (Stability)");
-	if (c.use_haar) fail(BS_ERR_ARG, "useHaar=true is not supported (ConfigSurfDescribe default is false)");
 	if (c.width_large_grid < 1 || c.width_sub_region < 1 || c.width_sample < 1) fail(BS_ERR_ARG, "descriptor widths must be >= 1");
 	const int grid = c.width_large_grid * c.width_sub_region + (c.variant == 1 ? 2 * c.overlap : 0);
 	if (grid > MAX_DESC_GRID) fail(BS_ERR_ARG, "descriptor sample grid larger than 32x32 is not supported");

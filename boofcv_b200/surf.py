@@ -109,6 +109,29 @@ def _p(a):
 
 
 # ------------------------------------------------------------------------------------------------ DetectDescribePoint
+class RetainedFeatures:
+    """Handle of a bs_features set (device memory); close() or garbage collection frees it."""
+
+    def __init__(self, handle, device=0):
+        self._h = handle; self.device = device
+
+    def count(self):
+        n, dof = C.c_int(0), C.c_int(0)
+        N.check(N.lib().bs_features_count(self._h, C.byref(n), C.byref(dof)))
+        return n.value, dof.value
+
+    def close(self):
+        if getattr(self, "_h", None) and self._h.value:
+            N.lib().bs_features_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
 class HostFeatureBuffers:
     """Host-side result arrays of detectHostBatch, page-locked through the library (bs_host_register) so that the
     device->host copies run asynchronously.  frame f owns rows frame_offset[f]:frame_offset[f+1] of every array."""
@@ -176,6 +199,13 @@ class DetectDescribeSurf:
 
     def setWorkspace(self, chunkFrames=0, poolFeatures=0):
         N.check(N.lib().bs_surf_set_workspace(self._h, chunkFrames, poolFeatures))
+
+    def retainFrame(self, frame=0, stream=None):
+        """Device-resident copy of one frame's features that survives later detect calls (bs_surf_retain): what the
+        frame-at-a-time DDA tracker keeps of the previous frame (FactoryPointTracker.java:169-175)."""
+        h = C.c_void_p()
+        N.check(N.lib().bs_surf_retain(self._h, int(frame), C.c_void_p(stream or 0), C.byref(h)))
+        return RetainedFeatures(h, self.device)
 
     def setWalkScratch(self, maxFeatures=0):
         """surfStable: cap the sliding-window walk scratch (features); the rest is walked inside describe_kernel."""

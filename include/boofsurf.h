@@ -68,7 +68,7 @@ typedef struct bs_desc_cfg {
 	int width_large_grid;    /* widthLargeGrid = 4 */
 	int width_sub_region;    /* widthSubRegion = 5 */
 	int width_sample;        /* widthSample = 3 */
-	int use_haar;            /* useHaar = false; true is rejected with BS_ERR_ARG (not on the north-star path) */
+	int use_haar;            /* useHaar = false; true: SparseIntegralHaar_NoBorder_F32/_I32 samples the descriptor (IP/alg/transform/ii/impl/SparseIntegralHaar_NoBorder_F32.java:37-73) */
 	double weight_sigma;     /* Speed.weightSigma = 4.5 */
 	int overlap;             /* Stability.overLap = 2 */
 	double sigma_large_grid; /* Stability.sigmaLargeGrid = 2.5 */
@@ -185,6 +185,20 @@ typedef struct bs_surf_device_view {
 } bs_surf_device_view;
 int bs_surf_view(bs_surf* s, bs_surf_device_view* v);
 
+/* Retained feature sets: a device-resident copy of ONE frame's features that outlives later detect calls on the handle.
+ * The frame-at-a-time callers of the reference keep the previous frame's descriptors while the next frame is detected —
+ * DetectDescribeAssociate / the DDA point tracker built by FactoryPointTracker.dda_FH_SURF_Fast/Stable
+ * (main/boofcv-geo/src/main/java/boofcv/factory/feature/tracker/FactoryPointTracker.java:169-175, 204-210) swap a "source" and a
+ * "destination" FastQueue<BrightFeature> every frame.  Here: detect frame t, bs_surf_retain it, detect frame t+1, retain it,
+ * bs_assoc_features_device(previous, current) — nothing leaves HBM.  The copy is ~545 bytes per feature (device to device). */
+typedef struct bs_features bs_features;
+int bs_surf_retain(bs_surf* s, int frame, void* stream, bs_features** out);
+int bs_features_count(const bs_features* f, int* n, int* dof);
+/* device pointers of the set (batch = 1, total = n, d_frame_offset = {0, n}); valid until bs_features_destroy */
+int bs_features_view(const bs_features* f, bs_surf_device_view* v);
+int bs_features_destroy(bs_features* f);
+/* (bs_assoc_features_device, declared with the associator below, associates two retained sets.) */
+
 /* ------------------------------------------------------------------------------------------------------------------
  * Stage-level entry points (parity tests call these; each runs exactly the kernel the full pipeline uses).
  * Host pointers in, host pointers out.
@@ -289,6 +303,11 @@ int bs_assoc_frames_device(bs_assoc* a, bs_surf* s, int frame_src, int frame_dst
  * association only (AssociateGreedy); results are those of n_pairs bs_assoc_frames_device calls. */
 int bs_assoc_frames_batch_device(bs_assoc* a, bs_surf* s, int n_pairs, const int32_t* frame_src, const int32_t* frame_dst,
                                  int32_t* d_pairs, double* d_fit, long cap, long* offsets, void* stream);
+
+/* AssociateDescription.associate on two retained sets (surf_basic != 0: WrapAssociateSurfBasic's split by Laplacian sign):
+ * d_pairs[n_src] / d_fit[n_src] as in bs_assoc_run_device. */
+int bs_assoc_features_device(bs_assoc* a, const bs_features* src, const bs_features* dst, int surf_basic, int32_t* d_pairs,
+                             double* d_fit, void* stream);
 
 /* Sharded association: the src rows of one rank against ALL dst rows.
  * Step 1 (bs_assoc_forward_device): forward pass for the local rows + per-column partial minima over the local rows:

@@ -186,11 +186,11 @@ def gaussian_width(sigma, width):
     return out.reshape(width, width)
 
 
-def gradient(ii, width, xy, safe=True):
+def gradient(ii, width, xy, safe=True, haar=False):
     a, st = _img(ii, np.float32)
     xy = np.ascontiguousarray(xy, np.int32)
     out = np.zeros((len(xy), 2), np.float64)
-    lib().orc_gradient_f32(_p(a), st, a.shape[1], a.shape[0], C.c_double(width), _p(xy), len(xy), int(safe), _p(out))
+    lib().orc_gradient_f32(_p(a), st, a.shape[1], a.shape[0], C.c_double(width), _p(xy), len(xy), int(safe), _p(out), int(haar))
     return out
 
 

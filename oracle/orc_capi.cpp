@@ -135,8 +135,8 @@ int orc_gaussian(int kind, double sigma, int n, double* out) {
 	return (int)k.size();
 }
 
-void orc_gradient_f32(const float* ii, int stride, int w, int h, double width, const int* xy, int n, int safe, double* dxdy) {
-	SparseGradient<float> g; g.ii = Img<float>{ii, stride, w, h}; g.set_width(width);
+void orc_gradient_f32(const float* ii, int stride, int w, int h, double width, const int* xy, int n, int safe, double* dxdy, int haar) {
+	SparseGradient<float> g; g.ii = Img<float>{ii, stride, w, h}; g.haar = haar != 0; g.set_width(width);
 	for (int i = 0; i < n; i++) { if (safe) g.compute_safe(xy[2 * i], xy[2 * i + 1], dxdy[2 * i], dxdy[2 * i + 1]); else g.compute(xy[2 * i], xy[2 * i + 1], dxdy[2 * i], dxdy[2 * i + 1]); }
 }
 

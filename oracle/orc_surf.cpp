@@ -507,13 +507,31 @@ template <typename T> void SparseGradient<T>::set_width(double width) {
 	r = ((int)(width + 0.5)) / 2;
 	if (r <= 0) r = 1;
 	w = r * 2 + 1;
+	if (haar) w = 2 * r;                    // SparseIntegralHaar_NoBorder_F32.setWidth :37-43: w = 2r, x0 = y0 = -r, x1 = y1 = r
 }
-// SparseScaleGradient.isInBounds :47-50 with x0=y0=-r-1, x1=y1=r (SparseIntegralGradient_NoBorder_F32.java:37-43)
+// SparseScaleGradient.isInBounds :47-50 with x0=y0=-r-1, x1=y1=r (SparseIntegralGradient_NoBorder_F32.java:37-43); Haar: x0=y0=-r
 template <typename T> bool SparseGradient<T>::in_bounds(int x, int y) const {
+	if (haar) return x - r >= 0 && y - r >= 0 && x + r < ii.width && y + r < ii.height;
 	return x - r - 1 >= 0 && y - r - 1 >= 0 && x + r < ii.width && y + r < ii.height;
+}
+// SparseIntegralHaar_NoBorder_F32.compute :46-73 / _I32 :46-73
+static void haar_compute(const Img<float>& ii, int r, int w, int x, int y, double& dx, double& dy) {
+	const float* d = ii.data;
+	long i1 = (long)(y - r) * ii.stride + (x - r), i2 = (long)y * ii.stride + (x - r), i3 = (long)(y + r) * ii.stride + (x - r);
+	float p0 = d[i1], p1 = d[i1 + r], p2 = d[i1 + w], p3 = d[i2], p5 = d[i2 + w], p6 = d[i3], p7 = d[i3 + r], p8 = d[i3 + w];
+	float left = p7 - p1 - p6 + p0, right = p8 - p2 - p7 + p1, top = p5 - p2 - p3 + p0, bottom = p8 - p5 - p6 + p3;
+	dx = (double)(right - left); dy = (double)(bottom - top);
+}
+static void haar_compute(const Img<int32_t>& ii, int r, int w, int x, int y, double& dx, double& dy) {
+	const int32_t* d = ii.data;
+	long i1 = (long)(y - r) * ii.stride + (x - r), i2 = (long)y * ii.stride + (x - r), i3 = (long)(y + r) * ii.stride + (x - r);
+	int32_t p0 = d[i1], p1 = d[i1 + r], p2 = d[i1 + w], p3 = d[i2], p5 = d[i2 + w], p6 = d[i3], p7 = d[i3 + r], p8 = d[i3 + w];
+	int32_t left = sum4(p7, p1, p6, p0), right = sum4(p8, p2, p7, p1), top = sum4(p5, p2, p3, p0), bottom = sum4(p8, p5, p6, p3);
+	dx = (double)wrap_sub(right, left); dy = (double)wrap_sub(bottom, top);
 }
 // SparseIntegralGradient_NoBorder_F32.compute :46-76 (float) / _I32 (int, wrapping)
 template <> void SparseGradient<float>::compute(int x, int y, double& dx, double& dy) const {
+	if (haar) { haar_compute(ii, r, w, x, y, dx, dy); return; }
 	const float* d = ii.data;
 	long i1 = (long)(y - r - 1) * ii.stride + (x - r - 1);
 	long i2 = i1 + (long)r * ii.stride, i3 = i2 + ii.stride, i4 = i3 + (long)r * ii.stride;
@@ -529,6 +547,7 @@ template <> void SparseGradient<float>::compute(int x, int y, double& dx, double
 	dy = (double)(bottom - top);
 }
 template <> void SparseGradient<int32_t>::compute(int x, int y, double& dx, double& dy) const {
+	if (haar) { haar_compute(ii, r, w, x, y, dx, dy); return; }
 	const int32_t* d = ii.data;
 	long i1 = (long)(y - r - 1) * ii.stride + (x - r - 1);
 	long i2 = i1 + (long)r * ii.stride, i3 = i2 + ii.stride, i4 = i3 + (long)r * ii.stride;
@@ -690,7 +709,6 @@ void normalize_l2(double* v, int n) {
 
 // DescribePointSurf ctor :112-139, DescribePointSurfMod ctor :71-99
 template <typename T> Describe<T>::Describe(const DescribeConfig& c) : cfg(c) {
-	if (cfg.use_haar) throw std::invalid_argument("useHaar=true is not restated (default is false, ConfigSurfDescribe.java:46)");
 	const int region = cfg.width_large_grid * cfg.width_sub_region;
 	dof = cfg.width_large_grid * cfg.width_large_grid * 4;
 	radius_descriptor = region / 2;
@@ -718,6 +736,7 @@ template <typename T> void Describe<T>::describe_raw(double x, double y, double 
 	double c = fd_cos(angle), s = fd_sin(angle);
 	bool isInBounds = is_inside_rotated(ii.width, ii.height, x, y, radius_descriptor, cfg.width_sample, scale, c, s);
 	g.ii = ii;
+	g.haar = cfg.use_haar != 0;             // DescribePointSurf :135: SurfDescribeOps.createGradient(useHaar, inputType)
 	g.set_width(cfg.width_sample * scale);
 	if (cfg.variant == 0) features_fast(x, y, c, s, scale, !isInBounds, desc);
 	else features_mod(x, y, c, s, scale, !isInBounds, desc);

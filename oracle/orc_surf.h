@@ -81,6 +81,7 @@ std::vector<double> gaussian_width(double sigma, int width);    // even or odd w
 //      TY/struct/sparse/SparseGradientSafe.java:56-61 ----
 template <typename T> struct SparseGradient {
 	Img<T> ii; int r = 1, w = 3;
+	bool haar = false;                       // SparseIntegralHaar_NoBorder_F32/_I32 (IP/alg/transform/ii/impl/...Haar_NoBorder_F32.java:37-73)
 	void set_width(double width);
 	bool in_bounds(int x, int y) const;
 	void compute(int x, int y, double& dx, double& dy) const;        // unchecked, like the Java (reads raw indices)

@@ -87,6 +87,49 @@ def test_surf_configs(bs, orc):
         bs.FactoryDetectDescribe.surfFast(bad, None, None, np.float32)
 
 
+def test_surf_use_haar_end_to_end(bs, orc):
+    # the Java config object -> bs_desc_cfg.use_haar -> describe_kernel, through the drop-in interface (integer images too)
+    img = blob_image(320, 240, 12)
+    d = bs.ConfigSurfDescribe.Speed(); d.useHaar = True
+    det = bs.FactoryDetectDescribe.surfFast(None, d, None, np.float32)
+    det.detect(img)
+    cfg = dict(orc.DESC_SPEED); cfg["use_haar"] = 1
+    _same(det.readFrame(0), orc.surf(img, None, orc.ORI_AVERAGE, cfg))
+    det.close()
+    u8 = np.clip(img, 0, 255).astype(np.uint8)
+    det = bs.FactoryDetectDescribe.surfFast(None, d, None, np.uint8)
+    det.detect(u8)
+    _same(det.readFrame(0), orc.surf(u8, None, orc.ORI_AVERAGE, cfg))
+    det.close()
+
+
+def test_retained_features_frame_at_a_time_tracker(bs, orc):
+    # FactoryPointTracker.dda_FH_SURF_Fast (FactoryPointTracker.java:169-175): detect frame t, keep its features, detect frame t+1
+    # on the SAME detector, associate previous -> current.  The previous frame's descriptors must survive the second detect.
+    a, b = shifted_pair(320, 240)
+    c = blob_image(320, 240, 99)
+    det = bs.FactoryDetectDescribe.surfFast(None, None, None, np.float32)
+    oa, ob, oc = orc.surf_fast(a), orc.surf_fast(b), orc.surf_fast(c)
+    det.detect(a); prev = det.retainFrame(0)
+    det.detect(b); cur = det.retainFrame(0)
+    assert prev.count() == (len(oa["x"]), 64) and cur.count() == (len(ob["x"]), 64)
+    det.detect(c)                                    # overwrites the detector's pool twice over
+    for backwards, basic in ((True, False), (False, False), (True, True)):
+        assoc = bs.FactoryAssociation.greedy(bs.ScoreAssociateEuclideanSq_F64(), 0.1, backwards)
+        p, f = assoc.associateRetained(prev, cur, surfBasic=basic)
+        if basic:                                    # the oracle's matches, in AssociateSurfBasic's order (white class first)
+            matches, _, _ = orc.associate_surf_basic(oa["desc"], oa["white"], ob["desc"], ob["white"], 0.1, backwards)
+            pn, fn = p.cpu().numpy(), f.cpu().numpy()
+            got = sorted((i, int(pn[i]), float(fn[i])) for i in range(len(pn)) if pn[i] >= 0)
+            assert got == sorted(matches) and len(matches) > 10
+        else:
+            op, of = orc.associate(oa["desc"], ob["desc"], 0.1, backwards)
+            assert np.array_equal(p.cpu().numpy(), op) and np.array_equal(f.cpu().numpy(), of), (backwards, basic)
+        assoc.close()
+    _same(det.readFrame(0), oc)
+    prev.close(); cur.close(); det.close()
+
+
 def test_surf_max_features_per_scale(bs, orc):
     # ExampleFeatureSurf.java:62 style configuration: ConfigFastHessian(0, 2, 200, 2, 9, 4, 4); here 25 per scale, batch of 3
     import torch

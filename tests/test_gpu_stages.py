@@ -224,6 +224,24 @@ def test_describe_bit_exact(st, orc, variant):
     assert np.allclose(np.linalg.norm(gd, axis=1), 1.0, atol=1e-12)
 
 
+@pytest.mark.parametrize("variant", ["speed", "stability"])
+def test_describe_haar_bit_exact(st, orc, variant):
+    # ConfigSurfDescribe.useHaar = true: SparseIntegralHaar_NoBorder_F32 samples the descriptor (border features included, where
+    # SparseGradientSafe returns zero for samples whose 2r x 2r window leaves the image)
+    ii, d = _points(orc, blob_image(400, 300, 23))
+    ang = orc.orientation(ii, d["x"], d["y"], d["scale"])
+    cfg = dict(orc.DESC_SPEED if variant == "speed" else orc.DESC_STABILITY); cfg["use_haar"] = 1
+    gd, gw = st.describe(ii, d["x"], d["y"], ang, d["scale"], cfg)
+    od, ow = orc.describe(ii, d["x"], d["y"], ang, d["scale"], cfg)
+    assert len(od) > 50 and np.array_equal(gd, od) and np.array_equal(gw, ow)
+    plain, _ = orc.describe(ii, d["x"], d["y"], ang, d["scale"], orc.DESC_SPEED if variant == "speed" else orc.DESC_STABILITY)
+    assert not np.array_equal(od, plain)                         # the switch really changes the sampler
+    x = np.array([2.0, 397.0, 200.0]); y = np.array([2.0, 297.0, 1.0]); s = np.array([1.5, 2.0, 3.0]); a = np.array([0.0, 1.0, -2.0])
+    gd, gw = st.describe(ii, x, y, a, s, cfg)
+    od, ow = orc.describe(ii, x, y, a, s, cfg)
+    assert np.array_equal(gd, od) and np.array_equal(gw, ow)
+
+
 def test_describe_border_and_constant(st, orc):
     # BaseTestDescribeSurf.java:125-151 — features at the border do not blow up; constant image -> all zeros
     ii = orc.integral(_noise(80, 60, 24))

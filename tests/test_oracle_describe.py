@@ -57,6 +57,25 @@ def test_gradient_definition_and_bounds(orc):
             assert dy == win[r + 1:, :].sum() - win[:r, :].sum()
 
 
+def test_haar_definition_and_bounds(orc):
+    """SparseIntegralHaar_NoBorder_F32.compute :46-73 == right half minus left half (bottom minus top) of the 2r x 2r window whose
+    first pixel is (x-r+1, y-r+1); bounds x0 = y0 = -r, x1 = y1 = r (setWidth :37-43); SparseGradientSafe -> 0 outside."""
+    img = np.random.default_rng(2).integers(0, 50, (40, 40)).astype(np.float32)
+    ii = orc.integral(img)
+    for width in (2.0, 4.0, 6.6):
+        r = max(1, int(width + 0.5) // 2)
+        xy = np.array([[20, 20], [r, r], [39 - r, 39 - r], [r - 1, 20], [20, 40 - r], [0, 0]], np.int32)
+        g = orc.gradient(ii, width, xy, safe=True, haar=True)
+        for (x, y), (dx, dy) in zip(xy, g):
+            inb = x - r >= 0 and y - r >= 0 and x + r < 40 and y + r < 40
+            if not inb:
+                assert dx == 0 and dy == 0
+                continue
+            win = img[y - r + 1:y + r + 1, x - r + 1:x + r + 1]
+            assert dx == win[:, r:].sum() - win[:, :r].sum()
+            assert dy == win[r:, :].sum() - win[:r, :].sum()
+
+
 def test_is_inside(orc):
     assert orc.is_inside_rect(100, 100, 10, 10, 20, 4)
     assert not orc.is_inside_rect(100, 100, 2, 10, 20, 4)        # x0 = 2 - 2 - 1 < 0
