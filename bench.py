@@ -388,10 +388,12 @@ def run_config5(torch, dist, dev, rank, world, local_rank, pairs_total=8192, pai
     t = torch.tensor([e0.elapsed_time(e1)], device=dev, dtype=torch.float64)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    _, _, (tc_runs, tc_fallbacks) = assoc.filterScores(np.zeros((1, 64)), np.zeros((1, 64)), want_scores=False)
     det.close(); assoc.close(); del frames
     torch.cuda.empty_cache()
     ms = float(t.item())
-    return {"workload": "stereo stream: %d x (2 x 1920x1080) per GPU (sample of BASELINE configs[4]: 8192 pairs over the ranks), surfFast x2 + "
+    return {"association_tensor_core_runs": int(tc_runs) - 1, "association_exact_fallbacks": int(tc_fallbacks),
+            "workload": "stereo stream: %d x (2 x 1920x1080) per GPU (sample of BASELINE configs[4]: 8192 pairs over the ranks), surfFast x2 + "
                         "greedy(backward, maxFit 0.1) per pair, device resident" % P,
             "pairs_per_s": world * P / (ms / 1e3), "frames_per_s": 2 * world * P / (ms / 1e3), "ms": ms, "matches_first_pair": matched,
             "scaling": "weak"}

@@ -54,7 +54,9 @@ constexpr int TC_EPI_WARPS = 16;           // four groups: (A half) x (column ha
 constexpr int TC_EC = TC_BN / 2;           // columns of an accumulator one epilogue thread reduces
 constexpr int TC_ISSUER2 = 2 + TC_EPI_WARPS;  // warp index of the second MMA issuer (after the epilogue warps)
 constexpr int TC_THREADS = 96 + 32 * TC_EPI_WARPS;
-constexpr int TC_CAND_CAP = 64;            // candidates kept per row; more -> the caller falls back to the exact kernel
+constexpr int TC_CAND_CAP = 128;           // candidates kept per row; more -> the caller falls back to the exact kernel.  Real SURF
+                                           // descriptors of a 1080p frame (10k x 10k, ~8 running-minimum chains per row: 4 CTAs x 2
+                                           // column halves) average 44 per row and reach 90: tools/dbg_stereo.py
 constexpr int TC_TMEM_COLS = 512;
 
 // Norms are stored tile by tile, 132 floats per 128 rows: the 128 squared norms, then a flag (non-zero: the 128 are one and the
@@ -291,8 +293,8 @@ filter_kernel(const __grid_constant__ CUtensorMap tmB, FilterArgs P) {
 			const int col0 = t * TC_BN + ch * TC_EC;
 			// The row's other thread (the other 64 columns of every tile) shares its running minimum: a value tagged with the row block
 			// it belongs to, one 64-bit shared-memory word per thread.  A stale value is still a valid (looser) bound, so once every
-			// four tiles is enough after the first eight (where the minimum still moves fast and short shares of a CTA end).
-			if (n < 8 || (n & 3) == 0) {
+			// four tiles is enough after the first sixteen (where the minimum still moves fast and short shares of a CTA end).
+			if (n < 16 || (n & 3) == 0) {
 				const unsigned long long mine = ((unsigned long long)(uint32_t)rp << 32) | __float_as_uint(run);
 				unsigned long long other;
 				asm volatile("st.shared.b64 [%0], %1;" ::"r"(run_mine), "l"(mine) : "memory");

@@ -51,7 +51,7 @@ def test_filter_estimate_stays_inside_its_error_budget(bs):
         err = np.abs(scores.astype(np.float64) - exact)
         assert np.isfinite(scores).all()
         assert (err <= 0.75 * budget).all(), float((err / budget).max())     # the budget is a worst-case bound
-        assert (cnt >= 1).all() and cnt.max() <= 64
+        assert (cnt >= 1).all() and cnt.max() <= 128
         g.close()
 
 
@@ -96,7 +96,7 @@ def test_mode1_near_ties_duplicates_and_threshold(bs, orc):
 
 
 def test_mode1_candidate_overflow_falls_back_to_exact(bs, orc):
-    # 200 identical destinations: every one of them is a candidate of every source -> lists overflow (cap 64) -> exact redo
+    # 200 identical destinations: every one of them is a candidate of every source -> lists overflow (cap 128) -> exact redo
     rng = np.random.default_rng(9)
     dst = np.repeat(_unit(rng, 1), 200, axis=0); src = _unit(rng, 50)
     tc = _greedy(bs, True)
