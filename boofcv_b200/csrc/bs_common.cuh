@@ -141,6 +141,10 @@ struct DescribeParams {
 // ---------------------------------------------------------------- stage launchers (implemented in the .cu files)
 template <typename TI, typename TO>
 void launch_integral(const TI* d_in, long in_frame_stride, int in_stride, TO* d_out, int W, int H, int batch, cudaStream_t st);
+// parallel (any-association) scan: exact for integer images, opt-in for float; d_scratch >= integral_scan_scratch_bytes()
+size_t integral_scan_scratch_bytes(int W, int H, int batch);
+template <typename TI, typename TO>
+bool launch_integral_scan(const TI* d_in, long in_frame_stride, int in_stride, TO* d_out, void* d_scratch, int W, int H, int batch, cudaStream_t st);
 
 template <typename T>
 void launch_hessian_plan(const T* d_ii, const Plan& plan, const Plan* d_plan, float* d_inten, int batch, cudaStream_t st);

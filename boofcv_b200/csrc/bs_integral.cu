@@ -10,6 +10,7 @@
 // Parallelism comes from rows x frames and columns x frames.  Integer images use the same kernels with uint32
 // wrap-around arithmetic (== Java int).
 #include "bs_common.cuh"
+#include <type_traits>
 
 namespace bs {
 
@@ -105,6 +106,158 @@ integral_cols_kernel(TO* __restrict__ out, int W, int H) {
 template <typename T> struct AccOf { typedef uint32_t type; };
 template <> struct AccOf<float> { typedef float type; };
 
+// ---------------------------------------------------------------- parallel scan (integer images)
+// Integer sums are exact under any association (Java int arithmetic wraps, uint32 here), so GrayU8 -> S32 and S32 -> S32 need
+// not run the reference's serial order: the image is cut into bands of SCAN_ROWS rows, a CTA scans a band row by row —
+// every thread owns V consecutive columns: local scan, warp scan of the thread totals by shuffles, warp totals through shared
+// memory — and keeps the running column sums of its columns in registers.
+//   pass A: column sums of each band's row-scanned values -> partial[frame][band][W]           (reads the input once)
+//   pass B: exclusive scan of the partials over the bands of a frame (tiny: 1 / SCAN_ROWS of the image)
+//   pass C: the band scan again, starting from the band's prefix, writes the integral           (input again + output)
+// Traffic per pixel: 2 x input + 4 bytes out (+ 1/16 for the partials) against 16 bytes for the two serial passes above;
+// the second read goes to DRAM again (launches that would keep it in L2 are too small to fill the GPU).
+// Float images do NOT take this path: the same kernels instantiated for float ran at 6.25 vs 7.05 us per 1080p frame, but another
+// association is another realisation of the float integral's rounding noise (sums reach 5e8 at 1080p: ulp 32) and 85 % of the
+// descriptors moved by more than 1e-4 against the reference (tools/bench_integral.py history in DESIGN.md).
+__device__ __forceinline__ int word_of(int32_t v) { return v; }
+__device__ __forceinline__ int word_of(float v) { return __float_as_int(v); }
+constexpr int SCAN_THREADS = 256;
+constexpr int SCAN_ROWS = 32;
+
+template <typename TI, typename ACC, int V>
+__device__ __forceinline__ void scan_load_row(const TI* __restrict__ row, int W, int x0, ACC (&v)[V]) {
+	// V consecutive pixels starting at x0; vector loads when the row pointer allows it, zero beyond W
+	if (x0 + V <= W) {
+		if (sizeof(TI) == 1 && V % 8 == 0 && (reinterpret_cast<uintptr_t>(row + x0) & 7) == 0) {
+#pragma unroll
+			for (int i = 0; i < V; i += 8) {
+				const uint2 q = __ldg(reinterpret_cast<const uint2*>(row + x0 + i));
+#pragma unroll
+				for (int k = 0; k < 4; k++) { v[i + k] = (ACC)((q.x >> (8 * k)) & 0xffu); v[i + 4 + k] = (ACC)((q.y >> (8 * k)) & 0xffu); }
+			}
+			return;
+		}
+		if (sizeof(TI) == 4 && V % 4 == 0 && (reinterpret_cast<uintptr_t>(row + x0) & 15) == 0) {
+#pragma unroll
+			for (int i = 0; i < V; i += 4) {
+				const int4 q = __ldg(reinterpret_cast<const int4*>(row + x0 + i));
+				const TI* e = reinterpret_cast<const TI*>(&q);
+#pragma unroll
+				for (int k = 0; k < 4; k++) v[i + k] = (ACC)e[k];
+			}
+			return;
+		}
+	}
+#pragma unroll
+	for (int i = 0; i < V; i++) v[i] = x0 + i < W ? (ACC)__ldg(row + x0 + i) : (ACC)0;
+}
+
+// WRITE = false: pass A (partial[band] = column sums of the band's row scans); true: pass C (out = prefix + running sums)
+template <typename TI, typename TO, typename ACC, int V, bool WRITE>
+__global__ void __launch_bounds__(SCAN_THREADS)
+integral_scan_kernel(const TI* __restrict__ in, long in_frame_stride, int in_stride, TO* __restrict__ out, ACC* __restrict__ partial, int W, int H,
+                     int bands) {
+	__shared__ ACC warp_tot[2][SCAN_THREADS / 32];
+	const int band = blockIdx.x, frame = blockIdx.y;
+	const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+	const int x0 = threadIdx.x * V;
+	const int y0 = band * SCAN_ROWS, y1 = min(H, y0 + SCAN_ROWS);
+	const TI* src = in + (long)frame * in_frame_stride;
+	ACC* part = partial + ((long)frame * bands + band) * W;
+	ACC col[V];
+#pragma unroll
+	for (int i = 0; i < V; i++) col[i] = WRITE && x0 + i < W ? part[x0 + i] : (ACC)0;
+	ACC cur[V], nxt[V];
+	scan_load_row<TI, ACC, V>(src + (long)y0 * in_stride, W, x0, cur);
+	for (int y = y0; y < y1; y++) {
+		if (y + 1 < y1) scan_load_row<TI, ACC, V>(src + (long)(y + 1) * in_stride, W, x0, nxt);
+		// inclusive scan of the thread's V pixels, then of the thread totals across the warp
+#pragma unroll
+		for (int i = 1; i < V; i++) cur[i] = (ACC)(cur[i] + cur[i - 1]);
+		ACC t = cur[V - 1];
+#pragma unroll
+		for (int d = 1; d < 32; d <<= 1) {
+			const ACC o = __shfl_up_sync(0xffffffffu, t, d);
+			if (lane >= d) t = (ACC)(t + o);
+		}
+		const int b = (y - y0) & 1;
+		if (lane == 31) warp_tot[b][warp] = t;
+		__syncthreads();                               // one barrier per row: the totals alternate between two buffers
+		ACC base = (ACC)(t - cur[V - 1]);              // exclusive prefix inside the warp
+#pragma unroll
+		for (int w = 0; w < SCAN_THREADS / 32; w++) if (w < warp) base = (ACC)(base + warp_tot[b][w]);
+#pragma unroll
+		for (int i = 0; i < V; i++) col[i] = (ACC)(col[i] + (ACC)(cur[i] + base));
+		if (WRITE) {
+			TO* dst = out + ((long)frame * H + y) * W + x0;
+			if (x0 + V <= W && V % 4 == 0 && (reinterpret_cast<uintptr_t>(dst) & 15) == 0) {
+#pragma unroll
+				for (int i = 0; i < V; i += 4) {
+					*reinterpret_cast<int4*>(dst + i) = make_int4(word_of((TO)col[i]), word_of((TO)col[i + 1]), word_of((TO)col[i + 2]), word_of((TO)col[i + 3]));
+				}
+			} else {
+#pragma unroll
+				for (int i = 0; i < V; i++) if (x0 + i < W) dst[i] = (TO)col[i];
+			}
+		}
+#pragma unroll
+		for (int i = 0; i < V; i++) cur[i] = nxt[i];
+	}
+	if (!WRITE) {
+#pragma unroll
+		for (int i = 0; i < V; i++) if (x0 + i < W) part[x0 + i] = col[i];
+	}
+}
+
+// pass B: partial[frame][band][x] -> exclusive prefix over the bands (thread = column)
+template <typename ACC>
+__global__ void integral_scan_bands_kernel(ACC* __restrict__ partial, int W, int bands) {
+	const int x = blockIdx.x * blockDim.x + threadIdx.x;
+	if (x >= W) return;
+	ACC* p = partial + (long)blockIdx.y * bands * W + x;
+	ACC run = 0;
+	for (int b = 0; b < bands; b++) {
+		const ACC v = p[(long)b * W];
+		p[(long)b * W] = run;
+		run = (ACC)(run + v);
+	}
+}
+
+size_t integral_scan_scratch_bytes(int W, int H, int batch) { return (size_t)batch * div_up(H, SCAN_ROWS) * W * 4; }
+
+// false if the shape is outside what the scan kernels are built for (W > 8192): the caller uses the serial passes
+template <typename TI, typename TO>
+bool launch_integral_scan(const TI* d_in, long in_frame_stride, int in_stride, TO* d_out, void* d_scratch, int W, int H, int batch, cudaStream_t st) {
+	typedef typename AccOf<TO>::type ACC;
+	if (W <= 0 || H <= 0 || batch <= 0) return true;
+	if (W > SCAN_THREADS * 32) return false;
+	const int bands = div_up(H, SCAN_ROWS);
+	ACC* part = static_cast<ACC*>(d_scratch);
+	// One launch per pass over the whole batch: bands x frames CTAs (1088 for 32 frames of 1080p).  Sub-batches small enough
+	// for the input to stay in L2 between pass A and pass C (5 frames) left 170 CTAs per launch and ran at half the speed.
+	const int sub = batch;
+	for (int f0 = 0; f0 < batch; f0 += sub) {
+		const int n = std::min(sub, batch - f0);
+		const TI* in = d_in + (long)f0 * in_frame_stride;
+		TO* out = d_out + (long)f0 * W * H;
+		ACC* pp = part + (long)f0 * bands * W;
+		dim3 g(bands, n);
+		auto go = [&](auto vtag) {
+			constexpr int V = decltype(vtag)::value;
+			BS_LAUNCH((integral_scan_kernel<TI, TO, ACC, V, false>), g, SCAN_THREADS, 0, st, in, in_frame_stride, in_stride, out, pp, W, H, bands);
+			BS_LAUNCH((integral_scan_bands_kernel<ACC>), dim3(div_up(W, 128), n), 128, 0, st, pp, W, bands);
+			BS_LAUNCH((integral_scan_kernel<TI, TO, ACC, V, true>), g, SCAN_THREADS, 0, st, in, in_frame_stride, in_stride, out, pp, W, H, bands);
+		};
+		const int per = div_up(W, SCAN_THREADS);
+		if (per <= 4) go(std::integral_constant<int, 4>());
+		else if (per <= 8) go(std::integral_constant<int, 8>());
+		else if (per <= 16) go(std::integral_constant<int, 16>());
+		else go(std::integral_constant<int, 32>());
+	}
+	return true;
+}
+
+
 template <typename TI, typename TO>
 void launch_integral(const TI* d_in, long in_frame_stride, int in_stride, TO* d_out, int W, int H, int batch, cudaStream_t st) {
 	if (W <= 0 || H <= 0 || batch <= 0) return;
@@ -115,6 +268,9 @@ void launch_integral(const TI* d_in, long in_frame_stride, int in_stride, TO* d_
 	BS_LAUNCH((integral_cols_kernel<TO, ACC>), g2, COL_THREADS, 0, st, d_out, W, H);
 }
 
+template bool launch_integral_scan<float, float>(const float*, long, int, float*, void*, int, int, int, cudaStream_t);
+template bool launch_integral_scan<uint8_t, int32_t>(const uint8_t*, long, int, int32_t*, void*, int, int, int, cudaStream_t);
+template bool launch_integral_scan<int32_t, int32_t>(const int32_t*, long, int, int32_t*, void*, int, int, int, cudaStream_t);
 template void launch_integral<float, float>(const float*, long, int, float*, int, int, int, cudaStream_t);
 template void launch_integral<uint8_t, int32_t>(const uint8_t*, long, int, int32_t*, int, int, int, cudaStream_t);
 template void launch_integral<int32_t, int32_t>(const int32_t*, long, int, int32_t*, int, int, int, cudaStream_t);

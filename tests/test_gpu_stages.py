@@ -28,8 +28,11 @@ def test_integral_f32_bit_exact(st, orc, shape):
     assert np.array_equal(st.integral(img), orc.integral(img))
 
 
-@pytest.mark.parametrize("shape", [(20, 30), (641, 479), (1920, 1080)])
+@pytest.mark.parametrize("shape", [(20, 30), (641, 479), (1920, 1080), (1, 1), (1, 40), (7, 33), (1023, 31), (1025, 65), (2047, 40), (2049, 33),
+                                   (3840, 64), (4100, 35), (8192, 33), (8200, 34)])
 def test_integral_u8_s32_bit_exact(st, orc, shape):
+    # integer images take the parallel scan (bands of 32 rows, 256 threads x 4 / 8 / 16 / 32 columns, vector loads when aligned);
+    # widths beyond 8192 fall back to the serial passes; values wrap like Java int
     w, h = shape
     rng = np.random.default_rng(2)
     u8 = rng.integers(0, 256, (h, w), dtype=np.uint8)
@@ -50,6 +53,12 @@ def test_integral_sub_image(st, orc):
     big = _noise(100, 80, 4)
     sub = big[10:50, 20:90]                   # row-strided view == BoofCV sub-image
     assert np.array_equal(st.integral(sub), orc.integral(np.ascontiguousarray(sub)))
+    rng = np.random.default_rng(5)
+    for dt, lo, hi in ((np.uint8, 0, 256), (np.int32, -2**31, 2**31 - 1)):      # misaligned rows for the scan's vector loads
+        bigi = rng.integers(lo, hi, (90, 301), dtype=np.int64).astype(dt)
+        for x0 in (0, 1, 3, 4):
+            subi = bigi[5:77, x0:x0 + 263]
+            assert np.array_equal(st.integral(subi), orc.integral(np.ascontiguousarray(subi))), (dt, x0)
 
 
 def test_integral_empty(st):
