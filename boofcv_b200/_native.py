@@ -88,6 +88,7 @@ SIGNATURES = {
     "bs_assoc_forward_static": (_i, [_i, _vp, _i, _vp, _i, _i, _d, _vp, _vp, _vp]),
     "bs_assoc_forward_device": (_i, [_vp, _vp, _i, _i, _vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp]),
     "bs_assoc_merge_columns_device": (_i, [_vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "bs_nonmax": (_i, [_i, _vp, _i, _i, _i, _i, C.c_float, _i, _i, _vp, _vp]),
     "bs_surf_retain": (_i, [_vp, _i, _vp, _vp]),
     "bs_features_count": (_i, [_vp, _vp, _vp]),
     "bs_features_view": (_i, [_vp, _vp]),

@@ -962,6 +962,38 @@ int bs_integral(int device, int pixel_type, const void* in, int in_stride, int w
 	});
 }
 
+int bs_nonmax(int device, const float* intensity, int stride, int width, int height, int radius, float threshold_max, int ignore_border,
+              int max_out, int16_t* xy, int* n) {
+	return guarded([&] {
+		if (!n) fail(BS_ERR_ARG, "null argument");
+		*n = 0;
+		if (width <= 0 || height <= 0) return;
+		if (!intensity || (max_out > 0 && !xy)) fail(BS_ERR_ARG, "null argument");
+		if (stride < width) fail(BS_ERR_ARG, "stride must be >= width");
+		if (radius < 1) fail(BS_ERR_ARG, "radius must be >= 1");          // ConfigExtract.checkValidity
+		if (ignore_border < 0 || max_out < 0) fail(BS_ERR_ARG, "ignore_border and max_out must be >= 0");
+		if (width > 32767 || height > 32767) fail(BS_ERR_ARG, "image larger than 32767 (QueueCorner stores int16 coordinates)");
+		check_device(device);
+		DeviceGuard g(device);
+		TempStream ts;
+		DevBuf d_img, d_cand, d_out, d_total;
+		const int step = radius + 1;
+		const long blocks = (long)div_up(width, step) * div_up(height, step);
+		d_img.reserve((size_t)width * height * 4); d_cand.reserve((size_t)std::max<long>(blocks, 1) * 4);
+		d_out.reserve((size_t)std::max(max_out, 1) * 4); d_total.reserve(4);
+		BS_CUDA(cudaMemcpy2DAsync(d_img.p, (size_t)width * 4, intensity, (size_t)stride * 4, (size_t)width * 4, height, cudaMemcpyHostToDevice, ts.st));
+		launch_nonmax_single(d_img.as<float>(), width, width, height, radius, threshold_max, ignore_border, d_cand.as<int>(), max_out, d_out.as<int16_t>(),
+		                     d_total.as<int>(), ts.st);
+		int total = 0;
+		BS_CUDA(cudaMemcpyAsync(&total, d_total.p, 4, cudaMemcpyDeviceToHost, ts.st));
+		BS_CUDA(cudaStreamSynchronize(ts.st));
+		*n = total;
+		if (std::min(total, max_out) > 0) BS_CUDA(cudaMemcpy(xy, d_out.p, (size_t)std::min(total, max_out) * 4, cudaMemcpyDeviceToHost));
+		d_img.release(); d_cand.release(); d_out.release(); d_total.release();
+		if (total > max_out) fail(BS_ERR_CAPACITY, "more maxima than max_out");
+	});
+}
+
 int bs_hessian(int device, int ii_type, const void* ii, int width, int height, int skip, int size, float* out) {
 	return guarded([&] {
 		if (!out) fail(BS_ERR_ARG, "null argument");

@@ -165,6 +165,8 @@ struct Pool {
 };
 
 // d_keys / d_keep: [batch][ctas_per_frame * NMS_CTA_BLOCKS] scratch, needed only when plan.max_per_level > 0
+void launch_nonmax_single(const float* d_img, int stride, int W, int H, int radius, float thr, int border, int* d_cand, int cap, int16_t* d_out,
+                          int* d_total, cudaStream_t st);
 void launch_nms(const Plan& plan, const Plan* d_plan, const float* d_inten, int batch, RawPoint* d_stage, int* d_cta_counts,
                 unsigned* d_keys, unsigned char* d_keep, cudaStream_t st);
 // Exclusive scan of the per-CTA counts of the chunk's frames (frame0 .. frame0+batch), continuing from

@@ -399,4 +399,74 @@ void launch_compact(const Plan& plan, int batch, int frame0, const RawPoint* d_s
 	          (const int*)d_frame_offset, plan.ctas_per_frame, frame0, pool);
 }
 
+// ---------------------------------------------------------------- stand-alone NonMaxBlock (strict rule, maxima)
+// NonMaxBlock.process :69-94 with NonMaxBlockSearchStrict.Max (searchBlock :56-79, checkLocalMax :196-221) on ONE intensity
+// image: what FactoryFeatureExtractor.nonmax(ConfigExtract(radius, threshold, ignoreBorder, useStrictRule = true)) builds and
+// what BOverrideFactoryFeatureExtractor.nonmax can hand to a plug-in (F/factory/feature/detect/extract/FactoryFeatureExtractor.java:
+// 69-71).  One thread per (radius+1)^2 block; the survivors are compacted in block-row-major order (the reference's single-thread
+// emission order) by one CTA.
+__global__ void nonmax_block_kernel(const float* __restrict__ img, int stride, int W, int H, int radius, float thr, int border, int bw, int bh,
+                                    int* __restrict__ cand) {
+	const int b = blockIdx.x * blockDim.x + threadIdx.x;
+	if (b >= bw * bh) return;
+	const int by = b / bw, bx = b - by * bw;
+	const int step = radius + 1;
+	const int endX = W - border, endY = H - border;
+	const int x = border + bx * step, y = border + by * step;
+	const int x1 = min(x + step, endX), y1 = min(y + step, endY);
+	int peakX = 0, peakY = 0;
+	float peak = -FLT_MAX;
+	for (int yy = y; yy < y1; yy++)
+		for (int xx = x; xx < x1; xx++) {
+			const float v = __ldg(img + (long)yy * stride + xx);
+			if (v > peak) { peak = v; peakX = xx; peakY = yy; }
+		}
+	int res = -1;
+	if (peak >= thr && peak != FLT_MAX) {
+		const int x0 = max(peakX - radius, 0), xe = min(peakX + radius, W - 1);
+		const int y0 = max(peakY - radius, 0), ye = min(peakY + radius, H - 1);
+		bool ok = true;
+		for (int yy = y0; yy <= ye && ok; yy++)
+			for (int xx = x0; xx <= xe; xx++) {
+				const float v = __ldg(img + (long)yy * stride + xx);
+				if (v >= peak && !(xx == peakX && yy == peakY)) { ok = false; break; }
+			}
+		if (ok) res = (peakY << 16) | peakX;              // both < 32768 (checked by the caller)
+	}
+	cand[b] = res;
+}
+// one CTA of 1024 threads: ordered compaction of cand[0..n) (>= 0) into out (x, y as int16), *total = how many
+__global__ void __launch_bounds__(1024) nonmax_compact_kernel(const int* __restrict__ cand, int n, int cap, int16_t* __restrict__ out, int* __restrict__ total) {
+	__shared__ int warp_cnt[32];
+	__shared__ int base;
+	const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+	if (threadIdx.x == 0) base = 0;
+	__syncthreads();
+	for (int i0 = 0; i0 < n; i0 += 1024) {
+		const int i = i0 + threadIdx.x;
+		const int c = i < n ? cand[i] : -1;
+		const unsigned m = __ballot_sync(0xffffffffu, c >= 0);
+		if (lane == 0) warp_cnt[warp] = __popc(m);
+		__syncthreads();
+		int off = base;
+		for (int w = 0; w < warp; w++) off += warp_cnt[w];
+		off += __popc(m & ((1u << lane) - 1));
+		if (c >= 0 && off < cap) { out[2 * off] = (int16_t)(c & 0xffff); out[2 * off + 1] = (int16_t)(c >> 16); }
+		__syncthreads();
+		if (threadIdx.x == 0) { int t = 0; for (int w = 0; w < 32; w++) t += warp_cnt[w]; base += t; }
+		__syncthreads();
+	}
+	if (threadIdx.x == 0) *total = base;
+}
+void launch_nonmax_single(const float* d_img, int stride, int W, int H, int radius, float thr, int border, int* d_cand, int cap, int16_t* d_out,
+                          int* d_total, cudaStream_t st) {
+	const int step = radius + 1;
+	const int endX = W - border, endY = H - border;
+	BS_CUDA(cudaMemsetAsync(d_total, 0, 4, st));
+	if (endX <= border || endY <= border) return;
+	const int bw = (endX - border + step - 1) / step, bh = (endY - border + step - 1) / step;
+	BS_LAUNCH(nonmax_block_kernel, div_up(bw * bh, 128), 128, 0, st, d_img, stride, W, H, radius, thr, border, bw, bh, d_cand);
+	BS_LAUNCH(nonmax_compact_kernel, 1, 1024, 0, st, (const int*)d_cand, bw * bh, cap, d_out, d_total);
+}
+
 }  // namespace bs

@@ -83,6 +83,22 @@ def hessian(ii, skip, size, device=0):
     return out
 
 
+def nonmax(intensity, radius, threshold, ignore_border=0, device=0):
+    """NonMaxBlock + NonMaxBlockSearchStrict.Max on one intensity image (bs_nonmax): int16 (x, y) in the reference's order."""
+    a = np.asarray(intensity, np.float32)
+    if a.ndim != 2:
+        raise ValueError("intensity must be [height][width]")
+    if a.strides[1] != 4:
+        a = np.ascontiguousarray(a)
+    h, w = a.shape
+    stride = a.strides[0] // 4 if h > 1 else max(w, 1)
+    cap = max(1, w * h)
+    xy = np.zeros((cap, 2), np.int16)
+    n = C.c_int(0)
+    N.check(N.lib().bs_nonmax(device, _p(a), stride, w, h, int(radius), C.c_float(threshold), int(ignore_border), cap, _p(xy), C.byref(n)))
+    return xy[:n.value].copy()
+
+
 def fh_intensity(ii, cfg=None, device=0):
     """Every layer of the Fast-Hessian scale space, computed by the kernels the batch path uses (FastHessianFeatureDetector
     .detectOctave's intensity[] images).  Returns a list of dicts {size, skip, intensity[h,w]} in (octave, scale) order."""

@@ -208,6 +208,15 @@ int bs_features_destroy(bs_features* f);
  * width*height (float for F32, int32 otherwise).  in_stride in elements. */
 int bs_integral(int device, int pixel_type, const void* in, int in_stride, int width, int height, void* out);
 
+/* NonMaxSuppression.process for the strict rule on maxima: NonMaxBlock.process (F/alg/feature/detect/extract/NonMaxBlock.java:
+ * 69-94) with NonMaxBlockSearchStrict.Max (:56-79, :196-221) — what FactoryFeatureExtractor.nonmax(new ConfigExtract(radius,
+ * threshold, ignoreBorder, true)) returns and the one plug-in hook the reference has on this path
+ * (BOverrideFactoryFeatureExtractor.nonmax, F/factory/feature/detect/extract/FactoryFeatureExtractor.java:69-71).
+ * intensity: host float image (stride in elements).  xy[2*max_out] receives (x, y) as int16 like QueueCorner, in the
+ * reference's single-thread order (block rows, then blocks); *n = number found (BS_ERR_CAPACITY if > max_out). */
+int bs_nonmax(int device, const float* intensity, int stride, int width, int height, int radius, float threshold_max,
+              int ignore_border, int max_out, int16_t* xy, int* n);
+
 /* IntegralImageFeatureIntensity.hessian (F/alg/feature/detect/intensity/IntegralImageFeatureIntensity.java:43-79).
  * ii dense width*height of integral type (ii_type: BS_PIXEL_F32 -> float, else int32); out dense (w/skip)*(h/skip). */
 int bs_hessian(int device, int ii_type, const void* ii, int width, int height, int skip, int size, float* out);

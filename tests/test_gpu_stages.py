@@ -65,6 +65,23 @@ def test_integral_empty(st):
     assert st.integral(np.zeros((0, 0), np.float32)).shape == (0, 0)
 
 
+# ------------------------------------------------------------------ stand-alone NonMaxBlock (bs_nonmax)
+@pytest.mark.parametrize("shape,radius,thr,border", [((120, 90), 2, 5.0, 0), ((121, 91), 2, 5.0, 3), ((640, 480), 1, 0.5, 1), ((77, 50), 5, -1e30, 0),
+                                                     ((1920, 1080), 2, 50.0, 4), ((10, 10), 3, 0.0, 6)])
+def test_nonmax_block_strict_equals_oracle(st, orc, shape, radius, thr, border):
+    # GenericNonMaxTests / TestNonMaxBlockStrict: same points, same order as NonMaxBlock + NonMaxBlockSearchStrict.Max; the oracle's
+    # block search is itself pinned against NonMaxExtractorNaive.strictRule (tests/test_oracle_detect.py)
+    w, h = shape
+    rng = np.random.default_rng(w + h)
+    img = rng.uniform(0, 100, (h, w)).astype(np.float32)
+    img[h // 2, w // 2] = 500.0; img[h // 2, w // 2 + 1] = 500.0          # equal neighbours: the strict rule rejects both
+    got = st.nonmax(img, radius, thr, border)
+    ref = orc.nonmax(img, radius, thr, border)
+    assert np.array_equal(got, ref) and (len(ref) > 0 or w <= 2 * border)
+    sub = np.zeros((h + 7, w + 9), np.float32); sub[3:3 + h, 5:5 + w] = img
+    assert np.array_equal(st.nonmax(sub[3:3 + h, 5:5 + w], radius, thr, border), ref)      # strided view == sub-image
+
+
 # ------------------------------------------------------------------ Fast-Hessian intensity
 @pytest.mark.parametrize("skip,size", [(1, 9), (2, 9), (3, 9), (4, 9), (1, 15), (1, 27), (2, 51), (4, 99), (8, 195)])
 def test_hessian_bit_exact_f32(st, orc, skip, size):
