@@ -312,9 +312,10 @@ def run_association(torch, dist, dev, rank, world, n=100000, reps=5):
         out = {"workload": "%d x %d SURF-64 descriptors, greedy + backward validation, HBM resident%s" % (
                    n, n, ", source rows sharded over %d ranks" % world if world > 1 else ""),
                "ms": ms, "pairs_per_s": n * float(n) / (ms / 1e3),
-               "algorithmic_tflops": alg, "frac_of_bf16_peak": alg / pk["bf16_tflops"],
-               "frac_of_bf16_peak_sustained": alg / pk.get("bf16_tflops_sustained", pk["bf16_tflops"]),
-               "target_ms_for_half_of_peak": 2.0 * n * n * 64 / (0.5 * pk["bf16_tflops"] * 1e12) * 1e3,
+               "algorithmic_tflops": alg, "frac_of_bf16_peak": alg / (world * pk["bf16_tflops"]),             # of the peak of ALL the GPUs used
+               "frac_of_bf16_peak_sustained": alg / (world * pk.get("bf16_tflops_sustained", pk["bf16_tflops"])),
+               "frac_of_one_gpu_bf16_peak": alg / pk["bf16_tflops"],
+               "target_ms_for_half_of_peak": 2.0 * n * n * 64 / (0.5 * world * pk["bf16_tflops"] * 1e12) * 1e3,
                "tensor_pipe_tflops_executed": 2 * alg,            # two K = 64 GEMM passes (forward, backward) are issued
                "planted_permutation_recovered": bool(ok.item() == 1), "exact_fallbacks": fallbacks,
                "parity_probe": None if bad is None else ("ok: 48 sampled rows exact vs fp64 CPU rule" if bad == 0 else "%d of 48 sampled rows differ" % bad)}
