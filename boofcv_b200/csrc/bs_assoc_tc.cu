@@ -50,8 +50,8 @@ constexpr int TC_TILE_BYTES = TC_BN * 128; // 16 KB: 128 rows x 128 B
 constexpr int TC_NB = TC_BN + 4;           // norms of a 128-row tile: 128 floats + {all equal?, 0, 0, 0}; see norm_index()
 constexpr int TC_SLOTS = 3;                // accumulators in flight
 constexpr int TC_A_COL = TC_SLOTS * TC_BN; // TMEM columns [384, 448): the two A halves, 32 columns each
-constexpr int TC_EPI_WARPS = 16;           // four groups: (A half) x (column half)
-constexpr int TC_EC = TC_BN / 2;           // columns of an accumulator one epilogue thread reduces
+constexpr int TC_EPI_WARPS = 16;           // four groups: (A half) x (tile parity)
+constexpr int TC_EC = TC_BN / 2;           // columns of an accumulator one epilogue thread reads per round
 constexpr int TC_ISSUER2 = 2 + TC_EPI_WARPS;  // warp index of the second MMA issuer (after the epilogue warps)
 constexpr int TC_THREADS = 96 + 32 * TC_EPI_WARPS;
 constexpr int TC_CAND_CAP = 128;           // candidates kept per row; more -> the caller falls back to the exact kernel.  Real SURF
@@ -152,8 +152,8 @@ filter_kernel(const __grid_constant__ CUtensorMap tmB, FilterArgs P) {
 	const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 	if (threadIdx.x == 0) {
 		mbar_init(&bar->a_full, TC_EPI_WARPS / 2);                   // the warps that write A: column half 0 of both A halves
-		for (int s = 0; s < TC_STAGES; s++) { mbar_init(&bar->b_full[s], 1); mbar_init(&bar->b_empty[s], TC_EPI_WARPS); }
-		for (int s = 0; s < TC_SLOTS; s++) { mbar_init(&bar->acc_full[s][0], 1); mbar_init(&bar->acc_full[s][1], 1); mbar_init(&bar->acc_empty[s][0], TC_EPI_WARPS / 2); mbar_init(&bar->acc_empty[s][1], TC_EPI_WARPS / 2); }
+		for (int s = 0; s < TC_STAGES; s++) { mbar_init(&bar->b_full[s], 1); mbar_init(&bar->b_empty[s], TC_EPI_WARPS / 2); }
+		for (int s = 0; s < TC_SLOTS; s++) { mbar_init(&bar->acc_full[s][0], 1); mbar_init(&bar->acc_full[s][1], 1); mbar_init(&bar->acc_empty[s][0], TC_EPI_WARPS / 4); mbar_init(&bar->acc_empty[s][1], TC_EPI_WARPS / 4); }
 		mbar_fence_init();
 	}
 	// no row block yet in the running-minimum exchange (shared memory keeps what the previous kernel left there)
@@ -224,17 +224,19 @@ filter_kernel(const __grid_constant__ CUtensorMap tmB, FilterArgs P) {
 			}
 		}
 	} else {
-		// ===== epilogue: warps 2..17.  TMEM lane quarter = warp % 4 (hardware rule); group = (warp - 2) / 4 =====
+		// ===== epilogue: warps 2..17.  TMEM lane quarter = warp % 4 (hardware rule); group = (warp - 2) / 4 = (A half, tile parity):
+		// a group takes every OTHER tile of its half and all 128 columns of it, in two rounds of 64 (registers).  (With the columns of every tile
+		// split between two groups each warp paid the ~95 instructions of per-tile bookkeeping and three barrier round trips on every
+		// tile: 1425 cycles per tile against 584 of MMAs.) =====
 		const int q = warp & 3;
 		const int g = (warp - 2) >> 2;
 		const int h = g >> 1;                                        // A half (rows h*128 .. h*128+127 of the row block)
-		const int ch = g & 1;                                        // column half of every accumulator
+		const int par = g & 1;                                       // tiles n = par, par + 2, ...
 		const int e = (warp - 2) * 32 + lane;                        // 0..511 among the epilogue threads
 		const int L = q * 32 + lane;                                 // TMEM lane = row inside the 128-row half
 		const uint32_t lane_base = tmem + ((uint32_t)(q * 32) << 16);
-		const uint32_t run_mine = smem_u32(s_run + (h * TC_BM + L) * 2 + ch), run_other = smem_u32(s_run + (h * TC_BM + L) * 2 + (ch ^ 1));
+		const uint32_t run_mine = smem_u32(s_run + (h * TC_BM + L) * 2 + par), run_other = smem_u32(s_run + (h * TC_BM + L) * 2 + (par ^ 1));
 		const float nb_max = __uint_as_float(*P.max_norm_b_bits);
-		int rp = rp0, t = t0;
 		int row = 0;
 		bool live = false;
 		float na = 0.0f, tol = 0.0f, run = INFINITY;
@@ -251,16 +253,36 @@ filter_kernel(const __grid_constant__ CUtensorMap tmB, FilterArgs P) {
 					    make_int2(s_pend[i * (32 * TC_EPI_WARPS) + e], s_pend[(TC_PEND + i) * (32 * TC_EPI_WARPS) + e]);
 			n_pend = 0;
 		};
-		static_assert(TC_SLOTS == 3, "the slot / use-count stepping below is written for three slots");
+		// this thread's row of block `blk` goes into TMEM as a row of the A operand (lane = row, column j = k 2j | 2j+1)
+		auto write_a = [&](int blk) {
+			uint32_t ar[32];
+			const uint4* src = reinterpret_cast<const uint4*>(P.opA + (size_t)(blk * TC_MROWS + h * TC_BM + L) * TC_K);   // padded to whole row blocks
+#pragma unroll
+			for (int i = 0; i < 8; i++) {
+				const uint4 v = __ldg(src + i);
+				ar[4 * i] = v.x; ar[4 * i + 1] = v.y; ar[4 * i + 2] = v.z; ar[4 * i + 3] = v.w;
+			}
+			tmem_st32(lane_base + (uint32_t)(TC_A_COL + h * (TC_K / 2)), ar);
+			tc_fence_before();
+			__syncwarp();
+			if (lane == 0) mbar_arrive(&bar->a_full);
+		};
+		static_assert(TC_SLOTS == 3 && TC_STAGES % 2 == 0, "the slot / use-count / stage stepping below is written for three slots, an even ring");
 		const uint32_t bfull_addr = smem_u32(&bar->b_full[0]), bempty_addr = smem_u32(&bar->b_empty[0]);
 		const uint32_t accfull_addr = smem_u32(&bar->acc_full[0][0]), accempty_addr = smem_u32(&bar->acc_empty[0][0]);
 		const uint32_t snb_addr = smem_u32(s_nb);
-		uint32_t st = 0, sph = 0;                                    // B stage of tile n and the parity of its use
-		uint32_t slot = (uint32_t)h, use = 0;                        // accumulator m = 2 n + h: slot m % 3, use count m / 3
-		for (int n = 0; n < n_tiles; n++) {
-			if (t == 0 || n == 0) {
+		if (par == 0 && n_tiles > 0) write_a(rp0);
+		int rp = rp0, t = t0 + par;
+		while (t >= P.b_tiles) { t -= P.b_tiles; rp++; }
+		int rp_loaded = -1;
+		uint32_t st = (uint32_t)par, sph = 0;                        // B stage of tile n and the parity of its use
+		uint32_t slot = (uint32_t)(2 * par + h) % TC_SLOTS, use = (uint32_t)(2 * par + h) / TC_SLOTS;   // accumulator m = 2 n + h
+		uint32_t k = 0;                                              // this group's tile count
+		for (int n = par; n < n_tiles; n += 2, k++) {
+			if (rp != rp_loaded) {
 				// ---- new row block
 				flush();
+				rp_loaded = rp;
 				row = rp * TC_MROWS + h * TC_BM + L;
 				live = row < P.nA;
 				na = live ? P.norm_a[norm_index(row)] : 0.0f;
@@ -274,27 +296,11 @@ filter_kernel(const __grid_constant__ CUtensorMap tmB, FilterArgs P) {
 					const double ub = P.row_bound[row];
 					if (ub < 1e30) run = __double2float_ru(ub) - na + 0.25f * tol;
 				}
-				if (ch == 0) {
-					// this thread's row goes into TMEM as a row of the A operand (lane = row, column j = k 2j | 2j+1).  The MMAs that
-					// read this half of the previous block have completed: this warp waited for the last of them.
-					uint32_t ar[32];
-					const uint4* src = reinterpret_cast<const uint4*>(P.opA + (size_t)row * TC_K);     // the operand is padded to whole row blocks
-#pragma unroll
-					for (int i = 0; i < 8; i++) {
-						const uint4 v = __ldg(src + i);
-						ar[4 * i] = v.x; ar[4 * i + 1] = v.y; ar[4 * i + 2] = v.z; ar[4 * i + 3] = v.w;
-					}
-					tmem_st32(lane_base + (uint32_t)(TC_A_COL + h * (TC_K / 2)), ar);
-					tc_fence_before();
-					__syncwarp();
-					if (lane == 0) mbar_arrive(&bar->a_full);
-				}
 			}
-			const int col0 = t * TC_BN + ch * TC_EC;
-			// The row's other thread (the other 64 columns of every tile) shares its running minimum: a value tagged with the row block
-			// it belongs to, one 64-bit shared-memory word per thread.  A stale value is still a valid (looser) bound, so once every
-			// four tiles is enough after the first sixteen (where the minimum still moves fast and short shares of a CTA end).
-			if (n < 16 || (n & 3) == 0) {
+			// The row's other thread (the tiles in between) shares its running minimum: a value tagged with the row block it belongs
+			// to, one 64-bit shared-memory word per thread.  A stale value is still a valid (looser) bound, so every other tile is
+			// enough after the first eight (where the minimum still moves fast and short shares of a CTA end).
+			if (k < 8 || (k & 1) == 0) {
 				const unsigned long long mine = ((unsigned long long)(uint32_t)rp << 32) | __float_as_uint(run);
 				unsigned long long other;
 				asm volatile("st.shared.b64 [%0], %1;" ::"r"(run_mine), "l"(mine) : "memory");
@@ -302,116 +308,125 @@ filter_kernel(const __grid_constant__ CUtensorMap tmB, FilterArgs P) {
 				if ((int)(other >> 32) == rp) run = fminf(run, __uint_as_float((uint32_t)other));
 			}
 			mbar_wait_addr(bfull_addr + 8u * st, sph);               // the stage's norms have landed (long since: the MMAs needed its tile)
+			// parity waits on [slot][use & 1]: the phase before the awaited one belongs to accumulator m - 6, a tile of the OTHER group; it has
+			// completed because the commits of one issuer arrive in order and this group has seen the one of m - 4
 			mbar_wait_addr(accfull_addr + 8u * (2u * slot + (use & 1u)), (use >> 1) & 1u);
 			tc_fence_after();
-			// This thread's 64 columns are fetched at once and the accumulator handed back to the MMA issuer before any
-			// arithmetic: the slot is held for one TMEM round trip, not for the reduction.
-			const uint32_t tbase = lane_base + slot * TC_BN + ch * TC_EC;
-			uint32_t r0[32], r1[32];
-			tmem_ld32_issue(tbase, r0); tmem_ld32_issue(tbase + 32, r1);
-			tmem_ld_wait(r0); tmem_ld_wait(r1);
-			tc_fence_before();
-			__syncwarp();
-			if (lane == 0) mbar_arrive_addr(accempty_addr + 8u * (2u * slot + (use & 1u)));
-			const uint32_t nb_addr = snb_addr + (uint32_t)(TC_NB * 4) * st + (uint32_t)(ch * TC_EC * 4);     // this thread's 64 column norms
 			const uint32_t flag_addr = snb_addr + (uint32_t)(TC_NB * 4) * st + (uint32_t)(TC_BN * 4);
-			// Candidate path of one 32-column chunk whose minimum came within tol of the row's running minimum (rare once the minimum
-			// has settled: ~1.3 / columns-seen per column).  val(k) = d' of column k of the chunk.  Dead rows (padding) carry
-			// run = -inf and never get here.
-			// Candidate path of one 32-column chunk whose best column came within tol of the row's running minimum (per row ~1.3 /
-			// columns-seen per column; a 32-lane warp takes it whenever ONE of its rows does: about a third of the tiles of a first
-			// direction at 100k columns).  Kept small on purpose — two larger variants (an unrolled walk with 32 store sites: 4096
-			// instructions of kernel code; a warp-cooperative scan through shared memory) lost more to instruction fetch and
-			// serialisation than they saved: 1.56 -> 2.3 / 1.9 ms per 100k x 100k pass.  A hit goes to the thread's pending list as
-			// (column, cmin): the chunk's best estimate stands in for the estimate of each of its hits — never above the hit's own,
-			// and the estimate of a column that is in the list, which is all the re-score's pruning rule needs.
-			// val(k): k-th value of the chunk; hits are val <= lim (LE) or val >= lim (!LE)
-			auto scan = [&](bool want, float cmin, int c, float lim, auto val, auto le) {
-				constexpr bool LE = decltype(le)::value;
-				if (want) {
-					unsigned hits = 0;
-#pragma unroll
-					for (int k = 0; k < 32; k++) hits |= ((LE ? val(k) <= lim : val(k) >= lim) ? 1u : 0u) << k;
-					while (hits) {
-						const int k = __ffs(hits) - 1;
-						hits &= hits - 1;
-						s_pend[n_pend * (32 * TC_EPI_WARPS) + e] = col0 + c * 32 + k;
-						s_pend[(TC_PEND + n_pend) * (32 * TC_EPI_WARPS) + e] = __float_as_int(cmin);
-						if (++n_pend == TC_PEND) flush();
-					}
+			const bool uniform = !DBG && lds32(flag_addr) != 0u;
+#pragma unroll 1
+			for (int c2 = 0; c2 < 2; c2++) {
+				const int col0 = t * TC_BN + c2 * TC_EC;
+				const uint32_t tbase = lane_base + slot * TC_BN + c2 * TC_EC;
+				uint32_t r0[32], r1[32];
+				tmem_ld32_issue(tbase, r0); tmem_ld32_issue(tbase + 32, r1);
+				tmem_ld_wait(r0); tmem_ld_wait(r1);
+				if (c2 == 1) {
+					// the accumulator goes back to the MMA issuer before the arithmetic on its second half
+					tc_fence_before();
+					__syncwarp();
+					if (lane == 0) mbar_arrive_addr(accempty_addr + 8u * (2u * slot + (use & 1u)));
 				}
-			};
-			// SURF descriptors are unit vectors: where the 128 column norms of a tile are one and the same float (flagged by
-			// norm_flags_kernel) min_j (nb - 2 s_j) = nb - 2 max_j s_j (fma is monotonic), and the row maximum of the raw accumulators
-			// is all the fast path needs: half an instruction per element, nothing but two words read from shared memory.
-			if (!DBG && lds32(flag_addr) != 0u) {
-				const float nbc = __uint_as_float(lds32(nb_addr));
-				auto row_max = [&](const uint32_t (&r)[32]) {
-					float a[11];
+				const uint32_t nb_addr = snb_addr + (uint32_t)(TC_NB * 4) * st + (uint32_t)(c2 * TC_EC * 4);     // the 64 column norms of this round
+				// Candidate path of one 32-column chunk whose best column came within tol of the row's running minimum (per row ~1.3 /
+				// columns-seen per column; a 32-lane warp takes it whenever ONE of its rows does: about a third of the tiles of a first
+				// direction at 100k columns).  Kept small on purpose — two larger variants (an unrolled walk with 32 store sites: 4096
+				// instructions of kernel code; a warp-cooperative scan through shared memory) lost more to instruction fetch and
+				// serialisation than they saved: 1.56 -> 2.3 / 1.9 ms per 100k x 100k pass.  A hit goes to the thread's pending list as
+				// (column, cmin): the chunk's best estimate stands in for the estimate of each of its hits — never above the hit's own,
+				// and the estimate of a column that is in the list, which is all the re-score's pruning rule needs.
+				// val(k): k-th value of the chunk; hits are val <= lim (LE) or val >= lim (!LE)
+				auto scan = [&](bool want, float cmin, int c, float lim, auto val, auto le) {
+					constexpr bool LE = decltype(le)::value;
+					if (want) {
+						unsigned hits = 0;
 #pragma unroll
-					for (int i = 0; i < 10; i++) a[i] = fmax3(__uint_as_float(r[3 * i]), __uint_as_float(r[3 * i + 1]), __uint_as_float(r[3 * i + 2]));
-					a[10] = fmaxf(__uint_as_float(r[30]), __uint_as_float(r[31]));
-					const float b0 = fmax3(a[0], a[1], a[2]), b1 = fmax3(a[3], a[4], a[5]), b2 = fmax3(a[6], a[7], a[8]), b3 = fmaxf(a[9], a[10]);
-					return fmaxf(fmax3(b0, b1, b2), b3);
-				};
-				const float m0 = row_max(r0), m1 = row_max(r1);
-				// one test for both chunks: nothing to do while the tile's best column stays more than tol above the running minimum
-				// one test for both chunks: nothing to do while the tile's best column stays more than tol above the running minimum
-				if (fmaf(-2.0f, fmaxf(m0, m1), nbc) <= run + tol) {
-					// s >= lim is implied by nb - 2 s <= thr: half the difference, less a margin for the roundings of both sides
-					auto chunk = [&](float mx, int c, const uint32_t (&r)[32]) {
-						const float cmin = fmaf(-2.0f, mx, nbc);
-						const bool want = cmin <= run + tol && cmin < INFINITY;
-						if (want) run = fminf(run, cmin);
-						const float thr = run + tol;
-						const float lim = 0.5f * (nbc - thr) - 1e-6f * (fabsf(nbc) + fabsf(thr));
-						scan(want, cmin, c, lim, [&](int k) { return __uint_as_float(r[k]); }, std::false_type());
-					};
-					chunk(m0, 0, r0);
-					chunk(m1, 1, r1);
-				}
-			} else {
-				// general norms: d' = |b_j|^2 - 2 s_j in place (packed pairs), then the same tree of three-input minima
-				auto row_min = [&](uint32_t (&r)[32], int c) {
-#pragma unroll
-					for (int k = 0; k < 8; k++) {
-						const float4 b = lds128(nb_addr + (uint32_t)(c * 128 + k * 16));
-						const float2 u = ffma2(make_float2(__uint_as_float(r[4 * k]), __uint_as_float(r[4 * k + 1])), make_float2(-2.0f, -2.0f), make_float2(b.x, b.y));
-						const float2 w = ffma2(make_float2(__uint_as_float(r[4 * k + 2]), __uint_as_float(r[4 * k + 3])), make_float2(-2.0f, -2.0f), make_float2(b.z, b.w));
-						r[4 * k] = __float_as_uint(u.x); r[4 * k + 1] = __float_as_uint(u.y); r[4 * k + 2] = __float_as_uint(w.x); r[4 * k + 3] = __float_as_uint(w.y);
-					}
-					float a[11];
-#pragma unroll
-					for (int i = 0; i < 10; i++) a[i] = fmin3(__uint_as_float(r[3 * i]), __uint_as_float(r[3 * i + 1]), __uint_as_float(r[3 * i + 2]));
-					a[10] = fminf(__uint_as_float(r[30]), __uint_as_float(r[31]));
-					const float b0 = fmin3(a[0], a[1], a[2]), b1 = fmin3(a[3], a[4], a[5]), b2 = fmin3(a[6], a[7], a[8]), b3 = fminf(a[9], a[10]);
-					if (DBG) {
-						if (P.dbg && live) {
-#pragma unroll
-							for (int k = 0; k < 32; k++)
-								if (col0 + c * 32 + k < P.nB) P.dbg[(size_t)row * P.nB + col0 + c * 32 + k] = __uint_as_float(r[k]) + na;
+						for (int kk = 0; kk < 32; kk++) hits |= ((LE ? val(kk) <= lim : val(kk) >= lim) ? 1u : 0u) << kk;
+						while (hits) {
+							const int kk = __ffs(hits) - 1;
+							hits &= hits - 1;
+							s_pend[n_pend * (32 * TC_EPI_WARPS) + e] = col0 + c * 32 + kk;
+							s_pend[(TC_PEND + n_pend) * (32 * TC_EPI_WARPS) + e] = __float_as_int(cmin);
+							if (++n_pend == TC_PEND) flush();
 						}
 					}
-					return fminf(fmin3(b0, b1, b2), b3);
 				};
-				const float c0 = row_min(r0, 0), c1 = row_min(r1, 1);
-				if (fminf(c0, c1) <= run + tol) {
-					auto chunk = [&](float cmin, int c, const uint32_t (&r)[32]) {
-						const bool want = cmin <= run + tol && cmin < INFINITY;
-						if (want) run = fminf(run, cmin);
-						scan(want, cmin, c, run + tol, [&](int k) { return __uint_as_float(r[k]); }, std::true_type());
+				// SURF descriptors are unit vectors: where the 128 column norms of a tile are one and the same float (flagged by
+				// norm_flags_kernel) min_j (nb - 2 s_j) = nb - 2 max_j s_j (fma is monotonic), and the row maximum of the raw accumulators
+				// is all the fast path needs: half an instruction per element, nothing but two words read from shared memory.
+				if (uniform) {
+					const float nbc = __uint_as_float(lds32(nb_addr));
+					auto row_max = [&](const uint32_t (&r)[32]) {
+						float a[11];
+#pragma unroll
+						for (int i = 0; i < 10; i++) a[i] = fmax3(__uint_as_float(r[3 * i]), __uint_as_float(r[3 * i + 1]), __uint_as_float(r[3 * i + 2]));
+						a[10] = fmaxf(__uint_as_float(r[30]), __uint_as_float(r[31]));
+						const float b0 = fmax3(a[0], a[1], a[2]), b1 = fmax3(a[3], a[4], a[5]), b2 = fmax3(a[6], a[7], a[8]), b3 = fmaxf(a[9], a[10]);
+						return fmaxf(fmax3(b0, b1, b2), b3);
 					};
-					chunk(c0, 0, r0);
-					chunk(c1, 1, r1);
+					const float m0 = row_max(r0), m1 = row_max(r1);
+					// one test for both chunks: nothing to do while the round's best column stays more than tol above the running minimum
+					if (fmaf(-2.0f, fmaxf(m0, m1), nbc) <= run + tol) {
+						// s >= lim is implied by nb - 2 s <= thr: half the difference, less a margin for the roundings of both sides
+						auto chunk = [&](float mx, int c, const uint32_t (&r)[32]) {
+							const float cmin = fmaf(-2.0f, mx, nbc);
+							const bool want = cmin <= run + tol && cmin < INFINITY;
+							if (want) run = fminf(run, cmin);
+							const float thr = run + tol;
+							const float lim = 0.5f * (nbc - thr) - 1e-6f * (fabsf(nbc) + fabsf(thr));
+							scan(want, cmin, c, lim, [&](int kk) { return __uint_as_float(r[kk]); }, std::false_type());
+						};
+						chunk(m0, 0, r0);
+						chunk(m1, 1, r1);
+					}
+				} else {
+					// general norms: d' = |b_j|^2 - 2 s_j in place (packed pairs), then the same tree of three-input minima
+					auto row_min = [&](uint32_t (&r)[32], int c) {
+#pragma unroll
+						for (int kk = 0; kk < 8; kk++) {
+							const float4 b = lds128(nb_addr + (uint32_t)(c * 128 + kk * 16));
+							const float2 u = ffma2(make_float2(__uint_as_float(r[4 * kk]), __uint_as_float(r[4 * kk + 1])), make_float2(-2.0f, -2.0f), make_float2(b.x, b.y));
+							const float2 w = ffma2(make_float2(__uint_as_float(r[4 * kk + 2]), __uint_as_float(r[4 * kk + 3])), make_float2(-2.0f, -2.0f), make_float2(b.z, b.w));
+							r[4 * kk] = __float_as_uint(u.x); r[4 * kk + 1] = __float_as_uint(u.y); r[4 * kk + 2] = __float_as_uint(w.x); r[4 * kk + 3] = __float_as_uint(w.y);
+						}
+						float a[11];
+#pragma unroll
+						for (int i = 0; i < 10; i++) a[i] = fmin3(__uint_as_float(r[3 * i]), __uint_as_float(r[3 * i + 1]), __uint_as_float(r[3 * i + 2]));
+						a[10] = fminf(__uint_as_float(r[30]), __uint_as_float(r[31]));
+						const float b0 = fmin3(a[0], a[1], a[2]), b1 = fmin3(a[3], a[4], a[5]), b2 = fmin3(a[6], a[7], a[8]), b3 = fminf(a[9], a[10]);
+						if (DBG) {
+							if (P.dbg && live) {
+#pragma unroll
+								for (int kk = 0; kk < 32; kk++)
+									if (col0 + c * 32 + kk < P.nB) P.dbg[(size_t)row * P.nB + col0 + c * 32 + kk] = __uint_as_float(r[kk]) + na;
+							}
+						}
+						return fminf(fmin3(b0, b1, b2), b3);
+					};
+					const float c0 = row_min(r0, 0), c1 = row_min(r1, 1);
+					if (fminf(c0, c1) <= run + tol) {
+						auto chunk = [&](float cmin, int c, const uint32_t (&r)[32]) {
+							const bool want = cmin <= run + tol && cmin < INFINITY;
+							if (want) run = fminf(run, cmin);
+							scan(want, cmin, c, run + tol, [&](int kk) { return __uint_as_float(r[kk]); }, std::true_type());
+						};
+						chunk(c0, 0, r0);
+						chunk(c1, 1, r1);
+					}
 				}
 			}
 			__syncwarp();
 			if (lane == 0) mbar_arrive_addr(bempty_addr + 8u * st);  // this warp is done with the stage's norms
-			// next tile: stage and its phase, accumulator slot and its use count (m advances by two: slot (m % 3) steps back by one,
-			// the use count m / 3 goes up whenever the slot does not wrap), column tile and row block
-			if (++st == (uint32_t)TC_STAGES) { st = 0; sph ^= 1u; }
-			if (slot == 0) slot = TC_SLOTS - 1; else { slot--; use++; }
-			if (++t == P.b_tiles) { t = 0; rp++; }
+			// The last tile of a row block: the MMAs that read this half of A have completed (this warp waited for the last of them
+			// above), so the next block's rows can go in; the other group is still on the tile before and never touches A.
+			if (t == P.b_tiles - 1 && n + 1 < n_tiles) write_a(rp + 1);
+			// this group's next tile (n + 2): stage and its phase, accumulator m + 4 (slot (m % 3) + 1, use count m / 3 up by one, by two
+			// when the slot wraps), column tile and row block
+			st += 2;
+			if (st >= (uint32_t)TC_STAGES) { st -= TC_STAGES; sph ^= 1u; }
+			if (slot == TC_SLOTS - 1) { slot = 0; use += 2; } else { slot++; use++; }
+			t += 2;
+			while (t >= P.b_tiles) { t -= P.b_tiles; rp++; }
 		}
 		flush();
 	}
