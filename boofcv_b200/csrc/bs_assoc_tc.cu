@@ -310,7 +310,7 @@ filter_kernel(const __grid_constant__ CUtensorMap tmB, FilterArgs P) {
 			mbar_wait_addr(bfull_addr + 8u * st, sph);               // the stage's norms have landed (long since: the MMAs needed its tile)
 			// parity waits on [slot][use & 1]: the phase before the awaited one belongs to accumulator m - 6, a tile of the OTHER group; it has
 			// completed because the commits of one issuer arrive in order and this group has seen the one of m - 4
-			mbar_wait_addr(accfull_addr + 8u * (2u * slot + (use & 1u)), (use >> 1) & 1u);
+			mbar_wait_addr_sleepy(accfull_addr + 8u * (2u * slot + (use & 1u)), (use >> 1) & 1u, 2000u);
 			tc_fence_after();
 			const uint32_t flag_addr = snb_addr + (uint32_t)(TC_NB * 4) * st + (uint32_t)(TC_BN * 4);
 			const bool uniform = !DBG && lds32(flag_addr) != 0u;

@@ -42,6 +42,25 @@ __device__ __forceinline__ void mbar_wait_addr(uint32_t addr, uint32_t parity) {
 	while (!mbar_try_wait(addr, parity))
 		if (++spin == (1u << 24)) __trap();
 }
+// The same wait with a suspend-time hint: a failing poll may keep the warp asleep for up to `ns` (the hardware wakes it when the
+// phase completes; ptxas emits NANOSLEEP.SYNCS), so a warp that waits long executes a handful of polls instead of one every ~60
+// cycles — the counter arithmetic of the poll loop runs on the ALU pipe the filter's epilogue is short of.
+__device__ __forceinline__ void mbar_wait_addr_sleepy(uint32_t addr, uint32_t parity, uint32_t ns) {
+	uint32_t spin = 0;
+#pragma unroll 1
+	while (true) {
+		uint32_t done;
+		asm volatile(
+		    "{\n\t.reg .pred p;\n\t"
+		    "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
+		    "selp.u32 %0, 1, 0, p;\n\t}"
+		    : "=r"(done)
+		    : "r"(addr), "r"(parity), "r"(ns)
+		    : "memory");
+		if (done) break;
+		if (++spin == (1u << 22)) __trap();
+	}
+}
 __device__ __forceinline__ void mbar_arrive_addr(uint32_t addr) {
 	asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(addr) : "memory");
 }

@@ -1,8 +1,16 @@
-// Dev probe (not part of the library): the skeleton of filter_kernel's accumulator hand-off as it is built now — two MMA issuers (one
-// per A half), four accumulator slots of 112 columns (slot = 2 * half + tile parity), four epilogue groups of four warps (half x tile
-// parity) that read a slot in two rounds (64 + 48 columns) and reduce it — without TMA, norms, candidate lists or the running-minimum
-// exchange.  Prints cycles per tile (= one accumulator of each half) for variants with pieces removed, to tell the hand-off structure
-// from the rest of the kernel.
+// Dev probe (not part of the library): what the accumulator hand-off of filter_kernel costs, piece by piece.
+//  micro 1   one thread: MMAs + tcgen05.commit + wait for that commit              (completion signal: ~245 cycles; ~95 per dependent MMA)
+//  micro 3/4 a pipeline of D groups in flight, the issuing thread waits (mbarrier try_wait) for the group D back, directly or relayed by
+//            another warp: 625 cycles per group for EVERY D — a try_wait of the thread that issued a commit does not return before that
+//            commit has arrived, so the pipe drains between two groups of one issuer; 380 without the wait
+//  micro 5   a 200-cycle pause of the issuing thread per group costs 134 cycles: the pipe takes MMAs from the thread almost synchronously
+//  micro 6   the issuer polls a shared-memory word a relay warp writes after ITS mbarrier wait: 366 cycles per group at D >= 2 (pipe-bound).
+//            In filter_kernel the extra relay hop lengthened the slot round trip by more than it saved (3.27 against 2.69 ms): not kept.
+//  micro 2   mbarrier arrive -> try_wait hop between two warps: 85-100 cycles
+//  ldtm      tcgen05.ld throughput with 1..16 warps
+// The first section (a skeleton of the whole hand-off: two or four issuers, four slots, sixteen epilogue warps) is kept for reference only:
+// its result moved between 1200 and 2060 cycles per tile from one build of this file to the next (register arrays in local memory, code
+// layout), so nothing is concluded from it.  Results: profiles/r2c_hs2_probe.txt.
 // Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -I ../../boofcv_b200/csrc -o hs2_probe hs2_probe.cu
 #include <cuda.h>
 #include <cuda_runtime.h>
@@ -170,6 +178,7 @@ __global__ void __launch_bounds__(608, 1) micro_kernel(int which, int cols, int 
 	if (threadIdx.x == 0) {
 		for (int s = 0; s < 4; s++) { mbar_init(&bar->full[s], 1); mbar_init(&bar->empty[s], 1); }
 		mbar_init(&bar->done[0], 1); mbar_init(&bar->done[1], 1);
+		bar->pad = 0;
 		mbar_fence_init();
 	}
 	asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -191,6 +200,25 @@ __global__ void __launch_bounds__(608, 1) micro_kernel(int which, int cols, int 
 					mbar_wait(&bar->full[0], n & 1);
 					tc_fence_after();
 				}
+				cycles[blockIdx.x] = clock64() - t0;
+				mbar_arrive(&bar->done[0]);
+			}
+		} else if (which >= 60) {
+			// micro 6: the issuer never executes an mbarrier wait: a relay warp (warp 2) waits for the commits and publishes how many groups
+			// have completed in a shared-memory word the issuer polls with plain volatile loads; depth D = which - 60 groups in flight
+			const int D = which - 60;
+			volatile uint32_t* done_ctr = reinterpret_cast<volatile uint32_t*>(&bar->pad);
+			if (elect_one()) {
+				const uint32_t idesc = idesc_of(128, cols);
+				const uint64_t db = umma_desc_sw128(smem_u32(sB));
+				const long long t0 = clock64();
+				for (int n = 0; n < iters; n++) {
+					const int sl = n & 3;
+					if (n >= D) { uint32_t spin = 0; while ((int)*done_ctr < n - D + 1) { if (++spin == (1u << 24)) __trap(); } tc_fence_after(); }
+					for (int kk = 0; kk < nmma; kk++) umma_bf16_ts(tmem + sl * cols, tmem + 448 + 8 * (kk & 3), db + 2 * (kk & 3), idesc, kk != 0);
+					umma_commit(&bar->full[sl]);
+				}
+				uint32_t spin = 0; while ((int)*done_ctr < iters) { if (++spin == (1u << 26)) __trap(); }
 				cycles[blockIdx.x] = clock64() - t0;
 				mbar_arrive(&bar->done[0]);
 			}
@@ -245,6 +273,12 @@ __global__ void __launch_bounds__(608, 1) micro_kernel(int which, int cols, int 
 				mbar_wait(&bar->empty[0], n & 1);
 			}
 			if (lane == 0) { cycles[blockIdx.x] = clock64() - t0; mbar_arrive(&bar->done[0]); }
+		}
+	} else if (warp == 2 && which >= 60) {
+		volatile uint32_t* done_ctr = reinterpret_cast<volatile uint32_t*>(&bar->pad);
+		for (int n = 0; n < iters; n++) {
+			mbar_wait(&bar->full[n & 3], (n >> 2) & 1);
+			if (lane == 0) *done_ctr = (uint32_t)(n + 1);
 		}
 	} else if (warp == 2 && which == 50) {
 		// free-running partner: completes a phase of empty[0] as soon as the issuer has consumed the previous one (ping-pong through full[1])
@@ -344,6 +378,8 @@ int main() {
 	    {34, 112, 4, 0, "self-paced depth 4, no fence", 1}, {34, 112, 4, 0, "depth 4, no wait (commit every group)", 2}, {34, 112, 4, 0, "depth 4, no wait, no commit", 6},
 	    {34, 112, 4, 0, "depth 4, wait+fence but no commit (waits on phase never... skipped)", 2 + 4}, {34, 128, 4, 0, "depth 4 (cols 128: timing only), no fence", 1},
 	    {34, 112, 1, 0, "depth 4, ONE MMA, no fence", 1}, {34, 112, 8, 0, "depth 4, EIGHT MMAs, no fence", 1}, {34, 112, 8, 0, "depth 4, EIGHT MMAs, fence", 0},
+	    {61, 112, 4, 0, "issuer polls a shared-memory counter (relay warp waits), depth 1"}, {62, 112, 4, 0, "shared-memory counter, depth 2"}, {63, 112, 4, 0, "shared-memory counter, depth 3"},
+	    {62, 112, 1, 0, "shared-memory counter, depth 2, ONE MMA"}, {62, 112, 4, 12, "shared-memory counter, depth 2, 12 warps polling"},
 	    {51, 112, 4, 0, "no wait, 200-cycle clock spin per group"}, {52, 112, 4, 0, "MMAs + commit, then wait for the commit of 3 groups ago"},
 	    {52, 112, 1, 0, "ONE MMA + commit, then wait for the commit of 3 groups ago"},
 	    {31, 112, 4, 0, "self-paced, depth 1"}, {32, 112, 4, 0, "self-paced, depth 2"}, {33, 112, 4, 0, "self-paced, depth 3"}, {34, 112, 4, 0, "self-paced, depth 4"},
