@@ -6,32 +6,33 @@
 //
 // The reference evaluates all N*M distances in fp64.  Here the N*M work runs on the 5th-generation tensor cores and only
 // a handful of pairs per row is re-scored in fp64, in the reference's summation order, so the result is bit-identical:
-//   1. split_kernel: every descriptor is rounded to bf16 (one K = 64 row = one 128-byte swizzle atom) and its squared norm
-//      kept in fp32.
-//   2. filter_kernel (tcgen05): s = a~ . b~ for 128 rows x 128 columns per accumulator, fp32 in TMEM; d' = |b|^2 - 2 s.
-//      Each row keeps the running minimum m of d' and emits column j as a CANDIDATE whenever d'_j <= m + tol.
+//   1. split_kernel: every descriptor is scaled by a power of two to a norm in [1, 2) and rounded to fp16 (one K = 64 row = one 128-byte
+//      swizzle atom); its squared norm and its scale are kept in fp32.
+//   2. filter_kernel (tcgen05, kind::f16 with F16 inputs AND an F16 accumulator): s = a~ . b~ for 128 rows x 112 columns per accumulator;
+//      d' = |b|^2 - 2 * 2^(ea+eb) s.  Each row keeps the running minimum m of d' and emits column j as a CANDIDATE whenever d'_j <= m + tol.
 //      tol = 2 * (bound on |d' - exact|), so the exact minimum — and every exact tie — is always among the candidates
 //      (the bound is stated at tolerance_of()).
 //   3. rescore_kernel: exact fp64 distance of every candidate, sequential over k without FMA like the reference; minimum,
 //      first and last index of the minimum -> pairs/fit (forward) or the column statistics used by backward validation.
-// The filter's shape follows what tools/probe/tc_probe.cu measured on this GPU (profiles/r2_tc_probe.txt): a 128x128x16 UMMA
-// with both operands in shared memory takes 97 cycles (operand fetch), 73 with A in TMEM (floor 64), and reading a whole
-// accumulator back costs far less than producing it (tcgen05.ld: ~880 B/cycle/SM).  So: the 256 rows of a row block live in
-// TMEM as the A operand (written there by the epilogue threads with tcgen05.st), B tiles stream through an 8-stage TMA ring
-// together with their column norms, three 128-column accumulators rotate between the MMA issuer and two epilogue groups.
-// Roles inside the CTA (608 threads): warp 0 = TMA producer, warps 1 and 18 = MMA issuers (one elected thread each, one per A
-// half), warps 2-17 = epilogue in
-// four groups of four warps (a group covers the four TMEM lane quarters): group g takes the accumulators of A half g >> 1 and
-// the 64 columns g & 1 of each — one TMEM lane = one row per thread, two threads per row.  An epilogue warp's serial chain per
-// accumulator (barrier wake-up, tcgen05.ld round trip, the reduction) was longer than the two MMAs it has to keep up with when
-// eight warps shared the work (650 vs 584 cycles: the filter ran at 45 % of the MMA rate); sixteen warps halve the chain.
-// The two threads of a row exchange their running minima through shared memory once per tile.  The work of a launch is the
-// sequence of (row block, B tile) pairs in row-block-major order, cut into one contiguous range per CTA.
+// Why fp16 all the way (tools/probe/f16acc_probe.cu, alu_probe.cu, hs2_probe.cu): what bounds this kernel is not the tensor pipe
+// but getting the accumulators out of TMEM and through a row maximum.  An F16 accumulator keeps one element per 32-bit TMEM column like an
+// fp32 one, but tcgen05.ld .pack::16b delivers two per register: a thread holds a whole 112-column accumulator row in 56 registers (one read
+// round, the slot goes back at once) and the packed maximum reduces two elements per issue slot.  The accumulator rounds to nearest after
+// each of the four 16-term MMAs; with rows normalised to [1, 2) the estimate is MORE accurate than bf16 inputs with an fp32 accumulator
+// (measured worst 7.0e-4 |a||b| against 1.8e-3).
+// Shape: the 256 rows of a row block live in TMEM as the A operand (written there by the epilogue threads with tcgen05.st: 73 cycles per
+// UMMA against 97 with A in shared memory, tools/probe/tc_probe.cu), B tiles stream through an 8-stage TMA ring together with their records
+// (norms, flag, scales), four 112-column accumulators: slot = 2 * (A half) + (tile parity).
+// Roles inside the CTA (608 threads): warp 0 = TMA producer, warps 1 and 18 = MMA issuers (one elected thread each, one per A half), warps
+// 2-17 = epilogue in four groups of four warps (a group covers the four TMEM lane quarters): group (A half, tile parity) owns one slot and
+// takes every other tile of its half — one TMEM lane = one row per thread, two threads per row (they exchange their running minima through
+// shared memory).  The work of a launch is the sequence of (row block, B tile) pairs in row-block-major order, cut into one contiguous
+// range per CTA.
 #include "bs_common.cuh"
 #include <cstdlib>
 #include "bs_sm100.cuh"
 
-#include <cuda_bf16.h>
+#include <cuda_fp16.h>
 #include <math_constants.h>
 #include <cfloat>
 #include <cmath>
@@ -42,16 +43,16 @@ namespace bs {
 using namespace sm100;
 
 constexpr int TC_DOF = 64;                 // descriptor length this path is built for (SURF-64)
-constexpr int TC_K = TC_DOF;               // bf16 per operand row: one 128-byte swizzle atom
-constexpr int TC_BM = 128, TC_BN = 128;    // one accumulator: 128 x 128, four 128x128x16 UMMAs
+constexpr int TC_K = TC_DOF;               // fp16 values per operand row: one 128-byte swizzle atom
+constexpr int TC_BM = 128, TC_BN = 112;    // one accumulator: 128 rows x 112 columns, four 128x112x16 UMMAs (four of them + A = 512 TMEM columns)
 constexpr int TC_MROWS = 2 * TC_BM;        // rows per row block (two A halves resident in TMEM)
 constexpr int TC_STAGES = 8;               // B ring
-constexpr int TC_TILE_BYTES = TC_BN * 128; // 16 KB: 128 rows x 128 B
-constexpr int TC_NB = TC_BN + 4;           // norms of a 128-row tile: 128 floats + {all equal?, 0, 0, 0}; see norm_index()
-constexpr int TC_SLOTS = 3;                // accumulators in flight
-constexpr int TC_A_COL = TC_SLOTS * TC_BN; // TMEM columns [384, 448): the two A halves, 32 columns each
-constexpr int TC_EPI_WARPS = 16;           // four groups: (A half) x (tile parity)
-constexpr int TC_EC = TC_BN / 2;           // columns of an accumulator one epilogue thread reads per round
+constexpr int TC_TILE_BYTES = TC_BN * 128; // 14 KB: 112 rows x 128 B (a multiple of the 1024-byte swizzle atom)
+constexpr int TC_NB = 2 * TC_BN + 4;       // the record of a 112-row tile: 112 squared norms, {all equal?, 0, 0, 0}, 112 scales (-2 * 2^e); see norm_index()
+constexpr int TC_SC = TC_BN + 4;           // float offset of the scales inside a tile's record
+constexpr int TC_SLOTS = 4;                // accumulators in flight: slot = 2 * (A half) + (tile parity)
+constexpr int TC_A_COL = TC_SLOTS * TC_BN; // TMEM columns [448, 512): the two A halves, 32 columns each
+constexpr int TC_EPI_WARPS = 16;           // four groups: (A half) x (tile parity), each the only reader of one slot
 constexpr int TC_ISSUER2 = 2 + TC_EPI_WARPS;  // warp index of the second MMA issuer (after the epilogue warps)
 constexpr int TC_THREADS = 96 + 32 * TC_EPI_WARPS;
 constexpr int TC_CAND_CAP = 128;           // candidates kept per row; more -> the caller falls back to the exact kernel.  Real SURF
@@ -59,56 +60,73 @@ constexpr int TC_CAND_CAP = 128;           // candidates kept per row; more -> t
                                            // column halves) average 44 per row and reach 90: tools/dbg_stereo.py
 constexpr int TC_TMEM_COLS = 512;
 
-// Norms are stored tile by tile, 132 floats per 128 rows: the 128 squared norms, then a flag (non-zero: the 128 are one and the
-// same finite float) and three zeros, so that one bulk copy brings a tile's norms and its flag into shared memory.
-__host__ __device__ __forceinline__ size_t norm_index(int row) { return (size_t)row + (size_t)(row >> 7) * 4; }
+// Norms are stored tile by tile, 228 floats per 112 rows: the 112 squared norms, a flag (non-zero: the 112 are one and the same finite
+// float) and three zeros, then the 112 scales -2 * 2^e of the rows (see split_kernel), so that one bulk copy brings all a tile's columns
+// need into shared memory.
+__host__ __device__ __forceinline__ size_t norm_index(int row) { return (size_t)row + (size_t)(row / TC_BN) * (TC_NB - TC_BN); }
+static_assert(TC_BN % 16 == 0 && TC_TILE_BYTES % 1024 == 0 && (TC_NB * 4) % 16 == 0 && TC_A_COL + TC_K <= 512, "tile shape");
 
 // ---------------------------------------------------------------- 1. split
-// Rows >= n (padding up to a multiple of 256) are zero with norm = +inf.
-__global__ void split_kernel(const double* __restrict__ x, int n, int n_pad, __nv_bfloat16* __restrict__ out, float* __restrict__ norm) {
+// Every row is scaled by a power of two, 2^-e with 4^e <= |x|^2 < 4^(e+1) (of the norm as rounded to float), before it is rounded to fp16: the operand rows have norms in
+// [1, 2) whatever the descriptors' magnitude (fp16 has 5 exponent bits), the scaling is exact, and the product of two rows is
+// a.b = 2^(ea+eb) * (a' . b').  The record keeps |x|^2 and -2 * 2^e per row.  Rows >= n are zero (the operand is padded to a multiple of
+// 256 rows) with norm = +inf (the records to whole 112-row tiles).
+__global__ void split_kernel(const double* __restrict__ x, int n, int n_pad, int n_norm, __half* __restrict__ out, float* __restrict__ norm) {
 	const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
 	const int lane = threadIdx.x & 31;
-	if (row >= n_pad) return;
+	if (row >= n_norm) return;
 	double2 v = make_double2(0.0, 0.0);
 	if (row < n) v = reinterpret_cast<const double2*>(x + (size_t)row * TC_DOF)[lane];
-	reinterpret_cast<__nv_bfloat162*>(out + (size_t)row * TC_K)[lane] = __nv_bfloat162(__double2bfloat16(v.x), __double2bfloat16(v.y));
 	double sq = v.x * v.x + v.y * v.y;
 	for (int d = 16; d > 0; d >>= 1) sq += __shfl_xor_sync(0xffffffffu, sq, d);
-	if (lane == 0) norm[norm_index(row)] = row < n ? (float)sq : INFINITY;
+	int e = 0;
+	const float sqf = (float)sq;
+	if (sqf > 0.0f && sqf < INFINITY) e = ilogbf(sqf) >> 1;              // floor(log4 |x|^2) of the ROUNDED norm: rows with equal float norms get equal
+	                                                                     // scales (the fast path relies on it); the shift of a negative int is arithmetic
+	e = max(-60, min(60, e));                                            // 2^e stays a normal float; rows beyond that range end in the exact kernel anyway
+	if (row < n_pad) reinterpret_cast<__half2*>(out + (size_t)row * TC_K)[lane] = __halves2half2(__double2half(scalbn(v.x, -e)), __double2half(scalbn(v.y, -e)));
+	if (lane == 0) {
+		const size_t i = norm_index(row);
+		norm[i] = row < n ? (float)sq : INFINITY;
+		norm[i + TC_SC] = -2.0f * scalbnf(1.0f, e);
+	}
 }
-// one warp per 128-row tile: flag = the tile's norms are all the same finite value; the largest norm of the real rows (one atomic
+// one warp per 112-row tile (28 lanes x 4 norms): flag = the tile's norms are all the same finite value; the largest norm of the real rows (one atomic
 // per tile: one per row in split_kernel was 100 k atomics on one address, 60 of that kernel's 70 us at 100 k rows)
 __global__ void norm_flags_kernel(float* __restrict__ norm, int tiles, int n, unsigned* __restrict__ max_norm_bits) {
 	const int tile = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
 	const int lane = threadIdx.x & 31;
 	if (tile >= tiles) return;
 	float* t = norm + (size_t)tile * TC_NB;
-	const float4 v = reinterpret_cast<const float4*>(t)[lane];
+	const bool in = lane < TC_BN / 4;
+	const float4 v = reinterpret_cast<const float4*>(t)[in ? lane : 0];
 	const float first = __shfl_sync(0xffffffffu, v.x, 0);
 	const bool same = v.x == first && v.y == first && v.z == first && v.w == first && first < INFINITY;
 	const bool all = __all_sync(0xffffffffu, same);
-	if (lane == 0) reinterpret_cast<float4*>(t)[32] = make_float4(all ? 1.0f : 0.0f, 0.0f, 0.0f, 0.0f);
+	if (lane == 0) reinterpret_cast<float4*>(t)[TC_BN / 4] = make_float4(all ? 1.0f : 0.0f, 0.0f, 0.0f, 0.0f);
 	const int r0 = tile * TC_BN + lane * 4;
 	unsigned mx = 0;                                                 // non-negative floats order like their bit patterns
-	if (r0 < n) mx = __float_as_uint(v.x);
-	if (r0 + 1 < n) mx = max(mx, __float_as_uint(v.y));
-	if (r0 + 2 < n) mx = max(mx, __float_as_uint(v.z));
-	if (r0 + 3 < n) mx = max(mx, __float_as_uint(v.w));
+	if (in && r0 < n) mx = __float_as_uint(v.x);
+	if (in && r0 + 1 < n) mx = max(mx, __float_as_uint(v.y));
+	if (in && r0 + 2 < n) mx = max(mx, __float_as_uint(v.z));
+	if (in && r0 + 3 < n) mx = max(mx, __float_as_uint(v.w));
 	mx = __reduce_max_sync(0xffffffffu, mx);
 	if (lane == 0 && mx) atomicMax(max_norm_bits, mx);
 }
 
-// Bound on |d'_computed - d'_exact| for one pair, d' = |b|^2 - 2 a.b, s = fp32 sum of the 64 products a~_k b~_k:
-//   rounding to bf16 (round to nearest, 8-bit significand): a~_k = a_k (1 + e), |e| <= 2^-9
-//       |a~.b~ - a.b| <= (2 * 2^-9 + 2^-18) sum |a_k b_k| <= 3.91e-3 |a||b|            (Cauchy-Schwarz)
-//   fp32 accumulation of 64 exact bf16 x bf16 products: <= 64 * 2^-23 |a~||b~| = 7.7e-6 |a||b|   (truncating adder assumed)
-//   => |s - a.b| <= 3.92e-3 |a||b|, budgeted 4e-3; d' doubles it: 8e-3 |a||b|
+// Bound on |d'_computed - d'_exact| for one pair, d' = |b|^2 - 2 a.b, s = the tensor core's a' . b' of the scaled fp16 rows (F16 inputs,
+// F16 accumulator: tools/probe/f16acc_probe.cu — the accumulator rounds to nearest after each of the four 16-term MMAs):
+//   rounding to fp16 (11-bit significand, rows of norm 1..2: a component below the normal range costs at most 2^-25 absolute):
+//       |a~.b~ - a'.b'| <= (2 * 2^-11 + 2^-22) sum |a'_k b'_k| + 2^-21 |a'||b'| <= 9.8e-4 |a'||b'|         (Cauchy-Schwarz)
+//   four roundings of partial sums of magnitude <= |a~||b~|: <= 4 * 2^-11 (1 + 1e-3) |a'||b'| = 1.96e-3 |a'||b'|
+//   fp32-or-better accumulation of 16 exact products inside an MMA: <= 16 * 2^-23 per MMA, 7.7e-6 |a'||b'| in all
+//   => |s - a'.b'| <= 2.95e-3 |a'||b'|, budgeted 3.2e-3; undoing the (exact) scaling and doubling: 6.4e-3 |a||b|
 //   fp32 rounding of |b|^2 and of the final fma: <= 2.4e-7 (|a|^2 + |b|^2); budgeted 1e-6
-// tol = 2 * bound (tests/test_gpu_assoc_tc.py measures the real error and asserts it stays below a quarter of the budget).
-// Values beyond bf16's range (|x| >= 3.4e38) make the norms infinite, tol infinite, every column a candidate: the lists overflow and the
-// caller redoes the problem with the exact kernel.
+// tol = 2 * bound (tests/test_gpu_assoc_tc.py measures the real error and asserts it stays below three quarters of the budget).
+// Non-finite values make the norms infinite, tol infinite, every column a candidate: the lists overflow and the caller redoes the problem
+// with the exact kernel.
 __device__ __forceinline__ float tolerance_of(float na, float nb_max) {
-	return 1.6e-2f * sqrtf(na * nb_max) + 2e-6f * (na + nb_max);
+	return 1.28e-2f * sqrtf(na * nb_max) + 2e-6f * (na + nb_max);
 }
 
 // ---------------------------------------------------------------- 2. filter
@@ -116,7 +134,7 @@ struct FilterArgs {
 	int nA, nB;                 // real rows / columns
 	int a_blocks;               // ceil(nA / 256)
 	int b_tiles;                // ceil(nB / 128)
-	const __nv_bfloat16* opA;   // [a_blocks * 256][64]
+	const __half* opA;          // [a_blocks * 256][64], rows scaled to norm 1..2
 	const float* norm_a;        // [nA_pad]
 	const float* norm_b;        // [nB_pad] (+inf in the padding)
 	const unsigned* max_norm_b_bits;
@@ -129,7 +147,7 @@ struct FilterArgs {
 struct __align__(8) FilterBarriers {
 	uint64_t a_full;
 	uint64_t b_full[TC_STAGES], b_empty[TC_STAGES];
-	uint64_t acc_full[TC_SLOTS][2], acc_empty[TC_SLOTS][2];  // [slot][use & 1], see the MMA issuers
+	uint64_t acc_full[TC_SLOTS], acc_empty[TC_SLOTS];        // one issuer thread and one epilogue group per slot
 	uint32_t tmem_base;
 	uint32_t pad;
 };
@@ -153,7 +171,7 @@ filter_kernel(const __grid_constant__ CUtensorMap tmB, FilterArgs P) {
 	if (threadIdx.x == 0) {
 		mbar_init(&bar->a_full, TC_EPI_WARPS / 2);                   // the warps that write A: column half 0 of both A halves
 		for (int s = 0; s < TC_STAGES; s++) { mbar_init(&bar->b_full[s], 1); mbar_init(&bar->b_empty[s], TC_EPI_WARPS / 2); }
-		for (int s = 0; s < TC_SLOTS; s++) { mbar_init(&bar->acc_full[s][0], 1); mbar_init(&bar->acc_full[s][1], 1); mbar_init(&bar->acc_empty[s][0], TC_EPI_WARPS / 4); mbar_init(&bar->acc_empty[s][1], TC_EPI_WARPS / 4); }
+		for (int s = 0; s < TC_SLOTS; s++) { mbar_init(&bar->acc_full[s], 1); mbar_init(&bar->acc_empty[s], TC_EPI_WARPS / 4); }
 		mbar_fence_init();
 	}
 	// no row block yet in the running-minimum exchange (shared memory keeps what the previous kernel left there)
@@ -187,47 +205,69 @@ filter_kernel(const __grid_constant__ CUtensorMap tmB, FilterArgs P) {
 			}
 		}
 	} else if (warp == 1 || warp == TC_ISSUER2) {
-		// ===== MMA issuers: warp 1 takes A half 0, warp 18 A half 1 (one elected thread each).  An accumulator is four MMAs
+		// ===== MMA issuers: warp 1 takes A half 0, warp 18 A half 1 (one elected thread each), two accumulator slots per half.  An accumulator is four MMAs
 		// (K = 64) between a wait and a commit: one thread's instruction stream for both halves (~45 dependent instructions per
 		// accumulator, sharing its scheduler with four epilogue warps) took longer than the MMAs themselves (measured with
 		// tools/probe/hs_probe.cu: 513 cycles per accumulator whatever the number of slots, 292 without the hand-off). =====
+		// The tensor pipe takes MMAs from the issuing thread almost synchronously (tools/probe/hs2_probe.cu: a 200-cycle pause of the
+		// thread between two groups of four MMAs costs 134 cycles of pipe time; the thread stalls at each tcgen05.mma until the one
+		// before it has been dispatched), so whatever the thread does between the last MMA of one accumulator and the first of the
+		// next — barrier waits, descriptor arithmetic — leaves the pipe idle beyond the ~95 cycles of that last MMA.  The loop
+		// therefore does the next accumulator's bookkeeping BETWEEN the MMAs of the current one, where the thread would stall anyway.
 		if (elect_one()) {
-			constexpr uint32_t idesc = umma_idesc_bf16(TC_BM, TC_BN);
+			constexpr uint32_t idesc = umma_idesc_f16_f16acc(TC_BM, TC_BN);
 			const uint32_t h = warp == 1 ? 0u : 1u;
 			const uint32_t a = tmem + (uint32_t)(TC_A_COL) + h * (TC_K / 2);
-			int t = t0;
-			uint32_t seg = 0;                                        // row-block segments started
-			for (int n = 0; n < n_tiles; n++) {
-				if (t == 0 || n == 0) {                              // the epilogue threads have written this row block's A into TMEM
-					mbar_wait(&bar->a_full, seg & 1);
-					seg++;
-				}
-				const int s = n % TC_STAGES;
-				const uint32_t m = 2u * (uint32_t)n + h;
-				const uint32_t slot = m % TC_SLOTS;
-				mbar_wait(&bar->b_full[s], (n / TC_STAGES) & 1);
-				// The epilogue drained the slot's previous accumulator (use u - 1).  A parity wait is only sound if the waiter knows that
-				// the phase before the one it waits for has completed (otherwise "previous phase still open" reads as "my phase done").
-				// The uses of a slot alternate between the two issuers (and between the two epilogue halves), so with ONE barrier per
-				// slot nobody would know that.  With one barrier per use parity, [slot][u & 1], the phase before is the one this same
-				// thread (warp) waited for two uses earlier.  The same holds for acc_full.
-				const uint32_t u = m / TC_SLOTS;
-				if (u > 0) mbar_wait(&bar->acc_empty[slot][(u - 1) & 1], ((u - 1) >> 1) & 1);
+			const uint32_t d0 = tmem + 2u * h * TC_BN;                  // this half's two accumulators: tile parity 0 / 1
+			const uint32_t full0 = smem_u32(&bar->acc_full[2 * h]), empty0 = smem_u32(&bar->acc_empty[2 * h]);
+			const uint32_t bfull0 = smem_u32(&bar->b_full[0]);
+			const uint64_t db0 = umma_desc_sw128(smem_u32(sB));
+			if (n_tiles > 0) {
+				mbar_wait(&bar->a_full, 0);                             // the epilogue threads have written the first row block's A into TMEM
+				mbar_wait_addr(bfull0, 0);
 				tc_fence_after();
-				const uint64_t db = umma_desc_sw128(smem_u32(sB + s * TC_TILE_BYTES));
-				const uint32_t d = tmem + slot * TC_BN;
-#pragma unroll
-				for (int kk = 0; kk < TC_K / 16; kk++)               // 16 bf16 = 8 TMEM columns of A = 32 bytes = 2 descriptor units of B
-					umma_bf16_ts(d, a + 8 * kk, db + 2 * kk, idesc, kk != 0 ? 1u : 0u);
-				umma_commit(&bar->acc_full[slot][u & 1]);
-				if (++t == P.b_tiles) t = 0;
+			}
+			int t = t0;
+			uint32_t seg = 1;                                        // row-block segments started
+			uint32_t st = 0, sph = 0;                                // B stage of tile n and the parity of its use
+			uint64_t db = db0;
+			for (int n = 0; n < n_tiles; n++) {
+				const uint32_t par = (uint32_t)n & 1u;
+				const uint32_t d = d0 + par * TC_BN;
+				umma_f16_ts(d, a, db, idesc, 0u);
+				// tile n + 1: stage, descriptor, row block
+				const bool more = n + 1 < n_tiles;
+				uint32_t st1 = st + 1, sph1 = sph;
+				uint64_t db1 = db + (TC_TILE_BYTES >> 4);
+				if (st1 == (uint32_t)TC_STAGES) { st1 = 0; sph1 ^= 1u; db1 = db0; }
+				int t1 = t + 1;
+				if (t1 == P.b_tiles) t1 = 0;
+				umma_f16_ts(d, a + 8, db + 2, idesc, 1u);
+				if (more) mbar_wait_addr(bfull0 + 8u * st1, sph1);      // landed long ago as a rule: the producer runs TC_STAGES tiles ahead
+				umma_f16_ts(d, a + 16, db + 4, idesc, 1u);
+				// the other slot's epilogue group has read the accumulator of tile n - 1 (use (n - 1) / 2 of that slot): awaited HERE, where the
+				// thread would stall on the last MMA anyway, not between this accumulator and the next
+				// (one probe: if the group is late, this accumulator is committed first and the wait follows it)
+				const bool need = more && n >= 1;
+				const uint32_t e_addr = empty0 + 8u * (par ^ 1u), e_par = (((uint32_t)n - 1u) >> 1) & 1u;
+				const bool got = need && mbar_try_wait(e_addr, e_par);
+				umma_f16_ts(d, a + 24, db + 6, idesc, 1u);
+				asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(full0 + 8u * par) : "memory");
+				if (need && !got) mbar_wait_addr(e_addr, e_par);
+				if (more) {
+					if (t1 == 0) {                                       // next row block: its A is written once the MMAs above have completed
+						mbar_wait(&bar->a_full, seg & 1);
+						seg++;
+					}
+					tc_fence_after();
+				}
+				st = st1; sph = sph1; db = db1; t = t1;
 			}
 		}
 	} else {
 		// ===== epilogue: warps 2..17.  TMEM lane quarter = warp % 4 (hardware rule); group = (warp - 2) / 4 = (A half, tile parity):
-		// a group takes every OTHER tile of its half and all 128 columns of it, in two rounds of 64 (registers).  (With the columns of every tile
-		// split between two groups each warp paid the ~95 instructions of per-tile bookkeeping and three barrier round trips on every
-		// tile: 1425 cycles per tile against 584 of MMAs.) =====
+		// a group takes every OTHER tile of its half, reads the whole accumulator row in one round and hands the slot back before
+		// any arithmetic. =====
 		const int q = warp & 3;
 		const int g = (warp - 2) >> 2;
 		const int h = g >> 1;                                        // A half (rows h*128 .. h*128+127 of the row block)
@@ -239,7 +279,7 @@ filter_kernel(const __grid_constant__ CUtensorMap tmB, FilterArgs P) {
 		const float nb_max = __uint_as_float(*P.max_norm_b_bits);
 		int row = 0;
 		bool live = false;
-		float na = 0.0f, tol = 0.0f, run = INFINITY;
+		float na = 0.0f, rs = 1.0f, tol = 0.0f, run = INFINITY;
 		// Candidates are collected per thread (a row belongs to two threads inside a segment) and appended to the row's list
 		// TC_PEND at a time: ONE atomicAdd reserves the slots, the stores do not depend on each other.
 		int n_pend = 0;
@@ -267,16 +307,16 @@ filter_kernel(const __grid_constant__ CUtensorMap tmB, FilterArgs P) {
 			__syncwarp();
 			if (lane == 0) mbar_arrive(&bar->a_full);
 		};
-		static_assert(TC_SLOTS == 3 && TC_STAGES % 2 == 0, "the slot / use-count / stage stepping below is written for three slots, an even ring");
+		static_assert(TC_SLOTS == 4 && TC_STAGES % 2 == 0, "slot = 2 h + tile parity; the stage stepping below is written for an even ring");
+		const uint32_t slot = (uint32_t)(2 * h + par);               // the accumulators this group reads: one TMEM slot, its k-th use = tile par + 2k
 		const uint32_t bfull_addr = smem_u32(&bar->b_full[0]), bempty_addr = smem_u32(&bar->b_empty[0]);
-		const uint32_t accfull_addr = smem_u32(&bar->acc_full[0][0]), accempty_addr = smem_u32(&bar->acc_empty[0][0]);
+		const uint32_t accfull_addr = smem_u32(&bar->acc_full[slot]), accempty_addr = smem_u32(&bar->acc_empty[slot]);
 		const uint32_t snb_addr = smem_u32(s_nb);
 		if (par == 0 && n_tiles > 0) write_a(rp0);
 		int rp = rp0, t = t0 + par;
 		while (t >= P.b_tiles) { t -= P.b_tiles; rp++; }
 		int rp_loaded = -1;
 		uint32_t st = (uint32_t)par, sph = 0;                        // B stage of tile n and the parity of its use
-		uint32_t slot = (uint32_t)(2 * par + h) % TC_SLOTS, use = (uint32_t)(2 * par + h) / TC_SLOTS;   // accumulator m = 2 n + h
 		uint32_t k = 0;                                              // this group's tile count
 		for (int n = par; n < n_tiles; n += 2, k++) {
 			if (rp != rp_loaded) {
@@ -286,6 +326,7 @@ filter_kernel(const __grid_constant__ CUtensorMap tmB, FilterArgs P) {
 				row = rp * TC_MROWS + h * TC_BM + L;
 				live = row < P.nA;
 				na = live ? P.norm_a[norm_index(row)] : 0.0f;
+				rs = live ? -0.5f * P.norm_a[norm_index(row) + TC_SC] : 1.0f;   // 2^e of this row (split_kernel)
 				tol = tolerance_of(na, nb_max);
 				// A row's candidates are the columns within tol of its running minimum.  Where the caller knows a distance the row
 				// really attains — the second direction takes it from the first one's matches — the minimum starts there: the true
@@ -308,123 +349,116 @@ filter_kernel(const __grid_constant__ CUtensorMap tmB, FilterArgs P) {
 				if ((int)(other >> 32) == rp) run = fminf(run, __uint_as_float((uint32_t)other));
 			}
 			mbar_wait_addr(bfull_addr + 8u * st, sph);               // the stage's norms have landed (long since: the MMAs needed its tile)
-			// parity waits on [slot][use & 1]: the phase before the awaited one belongs to accumulator m - 6, a tile of the OTHER group; it has
-			// completed because the commits of one issuer arrive in order and this group has seen the one of m - 4
-			mbar_wait_addr_sleepy(accfull_addr + 8u * (2u * slot + (use & 1u)), (use >> 1) & 1u, 2000u);
+			mbar_wait_addr(accfull_addr, k & 1u);
 			tc_fence_after();
-			const uint32_t flag_addr = snb_addr + (uint32_t)(TC_NB * 4) * st + (uint32_t)(TC_BN * 4);
-			const bool uniform = !DBG && lds32(flag_addr) != 0u;
-#pragma unroll 1
-			for (int c2 = 0; c2 < 2; c2++) {
-				const int col0 = t * TC_BN + c2 * TC_EC;
-				const uint32_t tbase = lane_base + slot * TC_BN + c2 * TC_EC;
-				uint32_t r0[32], r1[32];
-				tmem_ld32_issue(tbase, r0); tmem_ld32_issue(tbase + 32, r1);
-				tmem_ld_wait(r0); tmem_ld_wait(r1);
-				if (c2 == 1) {
-					// the accumulator goes back to the MMA issuer before the arithmetic on its second half
-					tc_fence_before();
-					__syncwarp();
-					if (lane == 0) mbar_arrive_addr(accempty_addr + 8u * (2u * slot + (use & 1u)));
-				}
-				const uint32_t nb_addr = snb_addr + (uint32_t)(TC_NB * 4) * st + (uint32_t)(c2 * TC_EC * 4);     // the 64 column norms of this round
-				// Candidate path of one 32-column chunk whose best column came within tol of the row's running minimum (per row ~1.3 /
-				// columns-seen per column; a 32-lane warp takes it whenever ONE of its rows does: about a third of the tiles of a first
-				// direction at 100k columns).  Kept small on purpose — two larger variants (an unrolled walk with 32 store sites: 4096
-				// instructions of kernel code; a warp-cooperative scan through shared memory) lost more to instruction fetch and
-				// serialisation than they saved: 1.56 -> 2.3 / 1.9 ms per 100k x 100k pass.  A hit goes to the thread's pending list as
-				// (column, cmin): the chunk's best estimate stands in for the estimate of each of its hits — never above the hit's own,
-				// and the estimate of a column that is in the list, which is all the re-score's pruning rule needs.
-				// val(k): k-th value of the chunk; hits are val <= lim (LE) or val >= lim (!LE)
-				auto scan = [&](bool want, float cmin, int c, float lim, auto val, auto le) {
-					constexpr bool LE = decltype(le)::value;
-					if (want) {
-						unsigned hits = 0;
+			// The whole accumulator row in one round: 112 fp16 values, two per register (tcgen05.ld .pack::16b), and the slot goes back to the
+			// MMA issuer before any arithmetic.
+			const int col0 = t * TC_BN;
+			const uint32_t tbase = lane_base + slot * TC_BN;
+			uint32_t r0[32], r1[16], r2[8];                              // columns [0, 64), [64, 96), [96, 112)
+			tmem_ld64p_issue(tbase, r0); tmem_ld32p_issue(tbase + 64, r1); tmem_ld16p_issue(tbase + 96, r2);
+			tmem_ld_wait(r0); tmem_ld_wait(r1); tmem_ld_wait(r2);
+			tc_fence_before();
+			__syncwarp();
+			if (lane == 0) mbar_arrive_addr(accempty_addr);
+			const uint32_t nb_addr = snb_addr + (uint32_t)(TC_NB * 4) * st;     // the tile's record: 112 norms, flag, 112 scales
+			// Candidate path of one 32-column chunk (16 registers; the last chunk of a tile has 16 columns) whose best column came within tol
+			// of the row's running minimum (per row ~1.3 / columns-seen per column; a 32-lane warp takes it whenever ONE of its rows does).
+			// Kept small on purpose (two larger variants lost more to instruction fetch and serialisation than they saved).  A hit goes to the
+			// thread's pending list as (column, cmin): the chunk's best estimate stands in for the estimate of each of its hits — never above
+			// the hit's own, and the estimate of a column that is in the list, which is all the re-score's pruning rule needs.
+			// val(k): estimate-side value of column k of the chunk; hits are val <= lim (LE) or val >= lim (!LE)
+			auto scan = [&](bool want, float cmin, int cbase, int ncols, float lim, auto val, auto le) {
+				constexpr bool LE = decltype(le)::value;
+				if (want) {
+					unsigned hits = 0;
 #pragma unroll
-						for (int kk = 0; kk < 32; kk++) hits |= ((LE ? val(kk) <= lim : val(kk) >= lim) ? 1u : 0u) << kk;
-						while (hits) {
-							const int kk = __ffs(hits) - 1;
-							hits &= hits - 1;
-							s_pend[n_pend * (32 * TC_EPI_WARPS) + e] = col0 + c * 32 + kk;
-							s_pend[(TC_PEND + n_pend) * (32 * TC_EPI_WARPS) + e] = __float_as_int(cmin);
-							if (++n_pend == TC_PEND) flush();
+					for (int kk = 0; kk < 32; kk++)
+						if (kk < ncols) hits |= ((LE ? val(kk) <= lim : val(kk) >= lim) ? 1u : 0u) << kk;
+					while (hits) {
+						const int kk = __ffs(hits) - 1;
+						hits &= hits - 1;
+						s_pend[n_pend * (32 * TC_EPI_WARPS) + e] = col0 + cbase + kk;
+						s_pend[(TC_PEND + n_pend) * (32 * TC_EPI_WARPS) + e] = __float_as_int(cmin);
+						if (++n_pend == TC_PEND) flush();
+					}
+				}
+			};
+			// pair maximum of `cnt` registers starting at r[first] (cnt a power of two), both halves
+			auto pmax = [&](const uint32_t* r, int first, int cnt) {
+				uint32_t m[16];
+#pragma unroll
+				for (int i = 0; i < 16; i++) m[i] = i < cnt ? r[first + i] : 0u;
+#pragma unroll
+				for (int w = cnt / 2; w >= 1; w >>= 1)
+#pragma unroll
+					for (int i = 0; i < 16; i++)
+						if (i < w) m[i] = hmax2(m[i], m[i + w]);
+				return m[0];
+			};
+			// SURF descriptors are unit vectors: where the 112 column norms of a tile are one and the same float (flagged by
+			// norm_flags_kernel; equal norms have equal scales) min_j (nb - 2 s_j) = nb - 2 max_j s_j (fma is monotonic), and the row maximum
+			// of the raw accumulators is all the fast path needs: a quarter of an instruction per element (packed fp16 maximum).
+			if (!DBG && lds32(nb_addr + (uint32_t)(TC_BN * 4)) != 0u) {
+				const float nbc = __uint_as_float(lds32(nb_addr));
+				const float sc = __uint_as_float(lds32(nb_addr + (uint32_t)(TC_SC * 4))) * rs;      // -2 * 2^(e_row + e_columns): exact
+				const uint32_t m0 = pmax(r0, 0, 16), m1 = pmax(r0, 16, 16), m2 = pmax(r1, 0, 16), m3 = pmax(r2, 0, 8);
+				const uint32_t mt = hmax2(hmax2(m0, m1), hmax2(m2, m3));
+				// one test for the tile: nothing to do while its best column stays more than tol above the running minimum
+				if (fmaf(sc, fmaxf(h2lo(mt), h2hi(mt)), nbc) <= run + tol) {
+					// s >= lim is implied by nb + sc s <= thr (sc < 0): the difference over |sc|, less a margin for the roundings of both sides
+					auto chunk = [&](uint32_t mp, int cbase, int ncols, const uint32_t* r, int first) {
+						const float cmin = fmaf(sc, fmaxf(h2lo(mp), h2hi(mp)), nbc);
+						const bool want = cmin <= run + tol && cmin < INFINITY;
+						if (want) run = fminf(run, cmin);
+						const float thr = run + tol;
+						const float lim = (nbc - thr) / -sc - 1e-6f * (fabsf(nbc) + fabsf(thr)) / -sc;
+						scan(want, cmin, cbase, ncols, lim, [&](int kk) { return (kk & 1) ? h2hi(r[first + (kk >> 1)]) : h2lo(r[first + (kk >> 1)]); }, std::false_type());
+					};
+					chunk(m0, 0, 32, r0, 0);
+					chunk(m1, 32, 32, r0, 16);
+					chunk(m2, 64, 32, r1, 0);
+					chunk(m3, 96, 16, r2, 0);
+				}
+			} else {
+				// general norms: d'_j = |b_j|^2 + (-2 * 2^e_j * 2^e_row) s_j column by column in fp32
+				auto chunk = [&](int cbase, int ncols, const uint32_t* r, int first) {
+					float d[32];
+					float cmin = INFINITY;
+#pragma unroll
+					for (int kk = 0; kk < 32; kk++) {
+						if (kk < ncols) {
+							const float sv = (kk & 1) ? h2hi(r[first + (kk >> 1)]) : h2lo(r[first + (kk >> 1)]);
+							const float nbj = __uint_as_float(lds32(nb_addr + (uint32_t)((cbase + kk) * 4)));
+							const float scj = __uint_as_float(lds32(nb_addr + (uint32_t)((TC_SC + cbase + kk) * 4))) * rs;
+							d[kk] = fmaf(scj, sv, nbj);
+							cmin = fminf(cmin, d[kk]);
+						} else d[kk] = INFINITY;
+					}
+					if (DBG) {
+						if (P.dbg && live) {
+#pragma unroll
+							for (int kk = 0; kk < 32; kk++)
+								if (kk < ncols && col0 + cbase + kk < P.nB) P.dbg[(size_t)row * P.nB + col0 + cbase + kk] = d[kk] + na;
 						}
 					}
+					const bool want = cmin <= run + tol && cmin < INFINITY;
+					if (want) run = fminf(run, cmin);
+					scan(want, cmin, cbase, ncols, run + tol, [&](int kk) { return d[kk]; }, std::true_type());
 				};
-				// SURF descriptors are unit vectors: where the 128 column norms of a tile are one and the same float (flagged by
-				// norm_flags_kernel) min_j (nb - 2 s_j) = nb - 2 max_j s_j (fma is monotonic), and the row maximum of the raw accumulators
-				// is all the fast path needs: half an instruction per element, nothing but two words read from shared memory.
-				if (uniform) {
-					const float nbc = __uint_as_float(lds32(nb_addr));
-					auto row_max = [&](const uint32_t (&r)[32]) {
-						float a[11];
-#pragma unroll
-						for (int i = 0; i < 10; i++) a[i] = fmax3(__uint_as_float(r[3 * i]), __uint_as_float(r[3 * i + 1]), __uint_as_float(r[3 * i + 2]));
-						a[10] = fmaxf(__uint_as_float(r[30]), __uint_as_float(r[31]));
-						const float b0 = fmax3(a[0], a[1], a[2]), b1 = fmax3(a[3], a[4], a[5]), b2 = fmax3(a[6], a[7], a[8]), b3 = fmaxf(a[9], a[10]);
-						return fmaxf(fmax3(b0, b1, b2), b3);
-					};
-					const float m0 = row_max(r0), m1 = row_max(r1);
-					// one test for both chunks: nothing to do while the round's best column stays more than tol above the running minimum
-					if (fmaf(-2.0f, fmaxf(m0, m1), nbc) <= run + tol) {
-						// s >= lim is implied by nb - 2 s <= thr: half the difference, less a margin for the roundings of both sides
-						auto chunk = [&](float mx, int c, const uint32_t (&r)[32]) {
-							const float cmin = fmaf(-2.0f, mx, nbc);
-							const bool want = cmin <= run + tol && cmin < INFINITY;
-							if (want) run = fminf(run, cmin);
-							const float thr = run + tol;
-							const float lim = 0.5f * (nbc - thr) - 1e-6f * (fabsf(nbc) + fabsf(thr));
-							scan(want, cmin, c, lim, [&](int kk) { return __uint_as_float(r[kk]); }, std::false_type());
-						};
-						chunk(m0, 0, r0);
-						chunk(m1, 1, r1);
-					}
-				} else {
-					// general norms: d' = |b_j|^2 - 2 s_j in place (packed pairs), then the same tree of three-input minima
-					auto row_min = [&](uint32_t (&r)[32], int c) {
-#pragma unroll
-						for (int kk = 0; kk < 8; kk++) {
-							const float4 b = lds128(nb_addr + (uint32_t)(c * 128 + kk * 16));
-							const float2 u = ffma2(make_float2(__uint_as_float(r[4 * kk]), __uint_as_float(r[4 * kk + 1])), make_float2(-2.0f, -2.0f), make_float2(b.x, b.y));
-							const float2 w = ffma2(make_float2(__uint_as_float(r[4 * kk + 2]), __uint_as_float(r[4 * kk + 3])), make_float2(-2.0f, -2.0f), make_float2(b.z, b.w));
-							r[4 * kk] = __float_as_uint(u.x); r[4 * kk + 1] = __float_as_uint(u.y); r[4 * kk + 2] = __float_as_uint(w.x); r[4 * kk + 3] = __float_as_uint(w.y);
-						}
-						float a[11];
-#pragma unroll
-						for (int i = 0; i < 10; i++) a[i] = fmin3(__uint_as_float(r[3 * i]), __uint_as_float(r[3 * i + 1]), __uint_as_float(r[3 * i + 2]));
-						a[10] = fminf(__uint_as_float(r[30]), __uint_as_float(r[31]));
-						const float b0 = fmin3(a[0], a[1], a[2]), b1 = fmin3(a[3], a[4], a[5]), b2 = fmin3(a[6], a[7], a[8]), b3 = fminf(a[9], a[10]);
-						if (DBG) {
-							if (P.dbg && live) {
-#pragma unroll
-								for (int kk = 0; kk < 32; kk++)
-									if (col0 + c * 32 + kk < P.nB) P.dbg[(size_t)row * P.nB + col0 + c * 32 + kk] = __uint_as_float(r[kk]) + na;
-							}
-						}
-						return fminf(fmin3(b0, b1, b2), b3);
-					};
-					const float c0 = row_min(r0, 0), c1 = row_min(r1, 1);
-					if (fminf(c0, c1) <= run + tol) {
-						auto chunk = [&](float cmin, int c, const uint32_t (&r)[32]) {
-							const bool want = cmin <= run + tol && cmin < INFINITY;
-							if (want) run = fminf(run, cmin);
-							scan(want, cmin, c, run + tol, [&](int kk) { return __uint_as_float(r[kk]); }, std::true_type());
-						};
-						chunk(c0, 0, r0);
-						chunk(c1, 1, r1);
-					}
-				}
+				chunk(0, 32, r0, 0);
+				chunk(32, 32, r0, 16);
+				chunk(64, 32, r1, 0);
+				chunk(96, 16, r2, 0);
 			}
 			__syncwarp();
 			if (lane == 0) mbar_arrive_addr(bempty_addr + 8u * st);  // this warp is done with the stage's norms
 			// The last tile of a row block: the MMAs that read this half of A have completed (this warp waited for the last of them
 			// above), so the next block's rows can go in; the other group is still on the tile before and never touches A.
 			if (t == P.b_tiles - 1 && n + 1 < n_tiles) write_a(rp + 1);
-			// this group's next tile (n + 2): stage and its phase, accumulator m + 4 (slot (m % 3) + 1, use count m / 3 up by one, by two
-			// when the slot wraps), column tile and row block
+			// this group's next tile (n + 2): stage and its phase, column tile and row block
 			st += 2;
 			if (st >= (uint32_t)TC_STAGES) { st -= TC_STAGES; sph ^= 1u; }
-			if (slot == TC_SLOTS - 1) { slot = 0; use += 2; } else { slot++; use++; }
 			t += 2;
 			while (t >= P.b_tiles) { t -= P.b_tiles; rp++; }
 		}
@@ -540,14 +574,14 @@ static EncodeTiledFn encode_tiled_fn() {
 	return fn;
 }
 
-// operand matrix [rows_pad][64] bf16, box = 64 elements (one 128-byte swizzle atom) x 128 rows
+// operand matrix [rows_pad][64] fp16, box = 64 elements (one 128-byte swizzle atom) x 112 rows
 static CUtensorMap operand_map(const void* base, int rows_pad) {
 	CUtensorMap m;
 	const cuuint64_t dims[2] = {(cuuint64_t)TC_K, (cuuint64_t)rows_pad};
 	const cuuint64_t strides[1] = {(cuuint64_t)TC_K * 2};
-	const cuuint32_t box[2] = {64, (cuuint32_t)TC_BM};
+	const cuuint32_t box[2] = {64, (cuuint32_t)TC_BN};
 	const cuuint32_t estr[2] = {1, 1};
-	const CUresult r = encode_tiled_fn()(&m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+	const CUresult r = encode_tiled_fn()(&m, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
 	                                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
 	                                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
 	if (r != CUDA_SUCCESS) fail(BS_ERR_CUDA, "cuTensorMapEncodeTiled failed");
@@ -556,7 +590,8 @@ static CUtensorMap operand_map(const void* base, int rows_pad) {
 
 int tc_pad_rows(int n) { return ((n + TC_MROWS - 1) / TC_MROWS) * TC_MROWS; }
 size_t tc_operand_bytes(int n) { return (size_t)tc_pad_rows(n) * TC_K * 2; }
-size_t tc_norm_bytes(int n) { return (size_t)(tc_pad_rows(n) / TC_BN) * TC_NB * 4; }
+static int tc_norm_tiles(int n) { return (tc_pad_rows(n) + TC_BN - 1) / TC_BN; }   // covers the rows a row block reads (A side) and whole tiles (B side)
+size_t tc_norm_bytes(int n) { return (size_t)tc_norm_tiles(n) * TC_NB * 4; }
 int tc_cand_cap() { return TC_CAND_CAP; }
 size_t tc_cand_bytes(size_t rows) { return rows * TC_CAND_CAP * 8; }   // (column, estimate) per candidate
 bool tc_supported(int dof) { return dof == TC_DOF; }
@@ -564,8 +599,9 @@ bool tc_supported(int dof) { return dof == TC_DOF; }
 void launch_tc_split(const double* d_x, int n, void* d_operand, float* d_norm, unsigned* d_max_norm_bits, cudaStream_t st) {
 	const int n_pad = tc_pad_rows(n);
 	BS_CUDA(cudaMemsetAsync(d_max_norm_bits, 0, 4, st));
-	BS_LAUNCH(split_kernel, div_up(n_pad, 8), 256, 0, st, d_x, n, n_pad, static_cast<__nv_bfloat16*>(d_operand), d_norm);
-	BS_LAUNCH(norm_flags_kernel, div_up(n_pad / TC_BN, 8), 256, 0, st, d_norm, n_pad / TC_BN, n, d_max_norm_bits);
+	const int tiles = tc_norm_tiles(n);
+	BS_LAUNCH(split_kernel, div_up(tiles * TC_BN, 8), 256, 0, st, d_x, n, n_pad, tiles * TC_BN, static_cast<__half*>(d_operand), d_norm);
+	BS_LAUNCH(norm_flags_kernel, div_up(tiles, 8), 256, 0, st, d_norm, tiles, n, d_max_norm_bits);
 }
 
 // rows of A against all rows of B: candidate lists for the rows of A
@@ -580,7 +616,7 @@ void launch_tc_filter(const void* d_opA, const float* d_normA, int nA, const voi
 	P.nA = nA; P.nB = nB;
 	P.a_blocks = tc_pad_rows(nA) / TC_MROWS;
 	P.b_tiles = div_up(nB, TC_BN);
-	P.opA = static_cast<const __nv_bfloat16*>(d_opA);
+	P.opA = static_cast<const __half*>(d_opA);
 	P.norm_a = d_normA; P.norm_b = d_normB; P.max_norm_b_bits = d_max_norm_b_bits;
 	P.cand_count = d_cand_count; P.cand = d_cand; P.dbg = d_dbg;
 	P.row_bound = d_row_bound;

@@ -136,7 +136,7 @@ __device__ __forceinline__ void umma_bf16(uint32_t d_tmem, uint64_t a_desc, uint
 }
 // the same with the A operand in TMEM (lane = row, 32-bit column j = elements k = 2j | 2j+1 of a 16-bit type; a K = 16 step is 8
 // columns): no shared-memory traffic for A.  Measured: 73 cycles per 128x128x16 against 97 with both operands in shared memory.
-__device__ __forceinline__ void umma_bf16_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+__device__ __forceinline__ void umma_f16_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
 	asm volatile(
 	    "{\n\t.reg .pred p;\n\t"
 	    "setp.ne.b32 p, %4, 0;\n\t"
@@ -173,6 +173,58 @@ __device__ __forceinline__ void tmem_ld16_issue(uint32_t taddr, uint32_t (&r)[32
 	      "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
 	    : "r"(taddr)
 	    : "memory");
+}
+// Packed loads of 16-bit accumulators (kind::f16 with an F16 accumulator keeps one element per 32-bit TMEM column): register j =
+// {column 2j (low half), column 2j + 1 (high half)}.  64 / 32 / 16 columns into 32 / 16 / 8 registers (tools/probe/f16acc_probe.cu).
+__device__ __forceinline__ void tmem_ld64p_issue(uint32_t taddr, uint32_t (&r)[32]) {
+#define BS_OUT(k) "=r"(r[k])
+	asm volatile(
+	    "tcgen05.ld.sync.aligned.32x32b.x32.pack::16b.b32 "
+	    "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+	    "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+	    : BS_R32(BS_OUT)
+	    : "r"(taddr)
+	    : "memory");
+#undef BS_OUT
+}
+__device__ __forceinline__ void tmem_ld32p_issue(uint32_t taddr, uint32_t (&r)[16]) {
+	asm volatile(
+	    "tcgen05.ld.sync.aligned.32x32b.x16.pack::16b.b32 "
+	    "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+	    : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]), "=r"(r[10]),
+	      "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+	    : "r"(taddr)
+	    : "memory");
+}
+__device__ __forceinline__ void tmem_ld16p_issue(uint32_t taddr, uint32_t (&r)[8]) {
+	asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.pack::16b.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+	             : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+	             : "r"(taddr)
+	             : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait(uint32_t (&r)[16]) {
+	asm volatile("tcgen05.wait::ld.sync.aligned;"
+	             : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]), "+r"(r[7]), "+r"(r[8]), "+r"(r[9]), "+r"(r[10]),
+	               "+r"(r[11]), "+r"(r[12]), "+r"(r[13]), "+r"(r[14]), "+r"(r[15])::"memory");
+}
+__device__ __forceinline__ void tmem_ld_wait(uint32_t (&r)[8]) {
+	asm volatile("tcgen05.wait::ld.sync.aligned;" : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]), "+r"(r[7])::"memory");
+}
+// packed fp16 pair maximum (HMNMX2: one issue slot per two elements) and the halves of a pair as floats (exact)
+__device__ __forceinline__ uint32_t hmax2(uint32_t a, uint32_t b) {
+	uint32_t d;
+	asm("max.f16x2 %0, %1, %2;" : "=r"(d) : "r"(a), "r"(b));
+	return d;
+}
+__device__ __forceinline__ float h2lo(uint32_t v) {
+	float f;
+	asm("{\n\t.reg .b16 lo, hi;\n\tmov.b32 {lo, hi}, %1;\n\tcvt.f32.f16 %0, lo;\n\t}" : "=f"(f) : "r"(v));
+	return f;
+}
+__device__ __forceinline__ float h2hi(uint32_t v) {
+	float f;
+	asm("{\n\t.reg .b16 lo, hi;\n\tmov.b32 {lo, hi}, %1;\n\tcvt.f32.f16 %0, hi;\n\t}" : "=f"(f) : "r"(v));
+	return f;
 }
 __device__ __forceinline__ void tmem_ld_wait(uint32_t (&r)[32]) {
 #define BS_INOUT(k) "+r"(r[k])
@@ -231,6 +283,8 @@ __device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr) {
 }
 // Instruction descriptor for kind::f16: D = F32 (bits 4-5 = 1), A = B = BF16 (bits 7-9, 10-12 = 1), both K-major (bits 15,16 = 0),
 // N >> 3 at bits 17-22, M >> 4 at bits 24-28
+// the same for D = F16, A = B = F16 (all format fields 0)
+__host__ __device__ constexpr uint32_t umma_idesc_f16_f16acc(int M, int N) { return ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24); }
 __host__ __device__ constexpr uint32_t umma_idesc_bf16(int M, int N) {
 	return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
 }

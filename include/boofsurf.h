@@ -258,13 +258,13 @@ int bs_assoc_create(int device, double max_fit_error, int backwards_validation, 
 int bs_assoc_destroy(bs_assoc* a);
 int bs_assoc_set_max_fit_error(bs_assoc* a, double max_fit_error); /* Associate.setMaxScoreThreshold */
 
-/* Filter mode: 0 = exact fp64 distances for every pair; 1 = tensor-core candidate filter (tcgen05 bf16 hi/lo split)
+/* Filter mode: 0 = exact fp64 distances for every pair; 1 = tensor-core candidate filter (tcgen05, fp16 operands scaled per row, fp16 accumulators)
  * followed by an exact fp64 re-score of the candidates (same pairs/fit, much faster for large N*M).  Default -1 = auto:
  * mode 1 when n*m >= 2^22 and dof == 64 (SURF-64), else mode 0.  Mode 1 synchronises the stream once per call (it has to
  * learn whether a candidate list overflowed, in which case the call is redone with the exact kernel). */
 int bs_assoc_set_mode(bs_assoc* a, int mode);
 
-/* Diagnostic for the tensor-core filter (mode 1): runs only the bf16 hi/lo split and the tcgen05 pass for src against dst
+/* Diagnostic for the tensor-core filter (mode 1): runs only the fp16 split and the tcgen05 pass for src against dst
  * and returns what the exact re-score would start from.  scores[n][m] (host, may be NULL) = the filter's fp32 estimate of
  * every squared distance; cand_count[n] (host, may be NULL) = candidates emitted per source row; stats[2] (may be NULL) =
  * {runs of the tensor-core path, runs that fell back to the exact kernel because a candidate list overflowed}.

@@ -1,4 +1,4 @@
-"""Tensor-core candidate filter (tcgen05, bf16 operands, K = 64) + exact fp64 re-score — bs_assoc mode 1, through the C ABI.
+"""Tensor-core candidate filter (tcgen05, fp16 operands scaled per row to norm 1..2, fp16 accumulators, K = 64) + exact fp64 re-score — bs_assoc mode 1, through the C ABI.
 
 The contract is the reference's (AssociateGreedy.java:65-118): pairs and fit must be BIT-IDENTICAL to the exact kernel and to
 the oracle, whatever the tensor cores round.  The filter only has to keep the exact minimum (and its exact ties) among the
@@ -38,20 +38,26 @@ def _greedy(bs, backwards, max_fit=np.finfo(np.float64).max, mode=1):
 
 
 def test_filter_estimate_stays_inside_its_error_budget(bs):
-    # 300 x 517: ragged against the 256-row / 128-column tiles; three norm regimes (unit, SURF-like, large)
+    # 300 x 517: ragged against the 256-row / 112-column tiles; norm regimes: unit, small, large (beyond fp16's range without the per-row
+    # scaling), and rows of very different magnitude in one problem
     rng = np.random.default_rng(1)
-    for scale in (1.0, 0.05, 300.0):
-        a = _unit(rng, 300) * scale; b = _unit(rng, 517) * scale
+    for scale in (1.0, 0.05, 300.0, None):
+        if scale is None:                                       # every row its own magnitude, 1e-4 .. 1e4
+            a = _unit(rng, 300) * 10.0 ** rng.uniform(-4, 4, size=(300, 1)); b = _unit(rng, 517) * 10.0 ** rng.uniform(-4, 4, size=(517, 1))
+        else:
+            a = _unit(rng, 300) * scale; b = _unit(rng, 517) * scale
         b[7] = a[3]                                             # an exact zero distance
         g = _greedy(bs, False)
         scores, cnt, _ = g.filterScores(a, b)
         exact = _exact_scores(a, b)
         na = (a * a).sum(1)[:, None]; nb = (b * b).sum(1)[None, :]
-        budget = 8e-3 * np.sqrt(na * nb) + 1e-6 * (na + nb)     # bs_assoc_tc.cu tolerance_of() is twice this
+        budget = 6.4e-3 * np.sqrt(na * nb) + 1e-6 * (na + nb)   # bs_assoc_tc.cu tolerance_of() is twice this
         err = np.abs(scores.astype(np.float64) - exact)
         assert np.isfinite(scores).all()
         assert (err <= 0.75 * budget).all(), float((err / budget).max())     # the budget is a worst-case bound
-        assert (cnt >= 1).all() and cnt.max() <= 128
+        # (with mixed magnitudes the tolerance, which is relative to the LARGEST column norm, admits hundreds of small columns: such a
+        # problem ends in the exact kernel — test_mode1_rows_of_mixed_magnitude)
+        assert (cnt >= 1).all() and (scale is None or cnt.max() <= 128)
         g.close()
 
 
@@ -74,8 +80,28 @@ def test_mode1_bit_exact_vs_exact_kernel_and_oracle(bs, orc, n, m, backwards):
     tc.close(); ex.close()
 
 
+def test_mode1_rows_of_mixed_magnitude(bs, orc):
+    # descriptors that are NOT normalised, magnitudes from 1e-3 to 1e3 inside one problem (the operands are scaled per row before the
+    # fp16 rounding: bs_assoc_tc.cu split_kernel), with planted matches at every magnitude
+    rng = np.random.default_rng(77)
+    n, m = 900, 1300
+    dst = _unit(rng, m) * 10.0 ** rng.uniform(-3, 3, size=(m, 1))
+    src = _unit(rng, n) * 10.0 ** rng.uniform(-3, 3, size=(n, 1))
+    k = 400
+    pick = rng.permutation(m)[:k]
+    src[:k] = dst[pick] * (1.0 + 0.01 * rng.normal(size=(k, 64)))
+    for backwards in (False, True):
+        tc, ex = _greedy(bs, backwards), _greedy(bs, backwards, mode=0)
+        for g in (tc, ex):
+            g.setSource(src); g.setDestination(dst); g.associate()
+        op, of = orc.associate(src, dst, np.finfo(np.float64).max, backwards)
+        assert np.array_equal(tc.getPairs(), op) and np.array_equal(tc.getFitQuality(), of)
+        assert np.array_equal(ex.getPairs(), op) and np.array_equal(ex.getFitQuality(), of)
+        tc.close(); ex.close()
+
+
 def test_mode1_near_ties_duplicates_and_threshold(bs, orc):
-    # adversarial for a low-precision filter: destinations that differ by 1e-9 .. 1e-4 (far below bf16 resolution), exact
+    # adversarial for a low-precision filter: destinations that differ by 1e-9 .. 1e-4 (far below fp16 resolution), exact
     # duplicates (tie -> later index forward, rejected backward), duplicate sources, and an inclusive threshold
     rng = np.random.default_rng(5)
     m = 640

@@ -52,7 +52,7 @@ __global__ void __launch_bounds__(128, 1) k(const uint16_t* A, const uint16_t* B
 	if (threadIdx.x == 0) {
 		const uint32_t idesc = idesc_of(128, 128, dfmt, abfmt);
 		const uint64_t db = umma_desc_sw128(smem_u32(sB));
-		for (int kk = 0; kk < 4; kk++) umma_bf16_ts(tmem, tmem + 480 + 8 * kk, db + 2 * kk, idesc, kk != 0);
+		for (int kk = 0; kk < 4; kk++) umma_f16_ts(tmem, tmem + 480 + 8 * kk, db + 2 * kk, idesc, kk != 0);
 		umma_commit(&bar->done);
 	}
 	mbar_wait(&bar->done, 0);

@@ -89,7 +89,7 @@ __global__ void __launch_bounds__(736, 1) hs2_kernel(int cols, int iters, long l
 				if (k > 0) wait_v(&bar->empty[slot], (k - 1) & 1, wmode);
 				tc_fence_after();
 #pragma unroll
-				for (int kk = 0; kk < 4; kk++) umma_bf16_ts(d, a_t + 8 * kk, db + 2 * kk, idesc, kk != 0);
+				for (int kk = 0; kk < 4; kk++) umma_f16_ts(d, a_t + 8 * kk, db + 2 * kk, idesc, kk != 0);
 				umma_commit(&bar->full[slot]);
 			}
 			umma_commit(&bar->done[0]);
@@ -109,7 +109,7 @@ __global__ void __launch_bounds__(736, 1) hs2_kernel(int cols, int iters, long l
 				tc_fence_after();
 				const uint32_t d = tmem + slot * (uint32_t)cols;
 #pragma unroll
-				for (int kk = 0; kk < 4; kk++) if (kk == 0 || !(flags & 64)) umma_bf16_ts(d, a_t + 8 * kk, db + 2 * kk, idesc, kk != 0);
+				for (int kk = 0; kk < 4; kk++) if (kk == 0 || !(flags & 64)) umma_f16_ts(d, a_t + 8 * kk, db + 2 * kk, idesc, kk != 0);
 				umma_commit(&bar->full[slot]);
 			}
 			umma_commit(&bar->done[h]);
@@ -195,7 +195,7 @@ __global__ void __launch_bounds__(608, 1) micro_kernel(int which, int cols, int 
 				const uint64_t db = umma_desc_sw128(smem_u32(sB));
 				const long long t0 = clock64();
 				for (int n = 0; n < iters; n++) {
-					for (int kk = 0; kk < nmma; kk++) umma_bf16_ts(tmem, tmem + 448 + 8 * (kk & 3), db + 2 * (kk & 3), idesc, kk != 0);
+					for (int kk = 0; kk < nmma; kk++) umma_f16_ts(tmem, tmem + 448 + 8 * (kk & 3), db + 2 * (kk & 3), idesc, kk != 0);
 					umma_commit(&bar->full[0]);
 					mbar_wait(&bar->full[0], n & 1);
 					tc_fence_after();
@@ -215,7 +215,7 @@ __global__ void __launch_bounds__(608, 1) micro_kernel(int which, int cols, int 
 				for (int n = 0; n < iters; n++) {
 					const int sl = n & 3;
 					if (n >= D) { uint32_t spin = 0; while ((int)*done_ctr < n - D + 1) { if (++spin == (1u << 24)) __trap(); } tc_fence_after(); }
-					for (int kk = 0; kk < nmma; kk++) umma_bf16_ts(tmem + sl * cols, tmem + 448 + 8 * (kk & 3), db + 2 * (kk & 3), idesc, kk != 0);
+					for (int kk = 0; kk < nmma; kk++) umma_f16_ts(tmem + sl * cols, tmem + 448 + 8 * (kk & 3), db + 2 * (kk & 3), idesc, kk != 0);
 					umma_commit(&bar->full[sl]);
 				}
 				uint32_t spin = 0; while ((int)*done_ctr < iters) { if (++spin == (1u << 26)) __trap(); }
@@ -236,7 +236,7 @@ __global__ void __launch_bounds__(608, 1) micro_kernel(int which, int cols, int 
 					const int sl = n & 3;
 					if (which == 50) { mbar_wait(&bar->empty[0], n & 1); }
 					if (which == 51) { const long long c0 = clock64(); while (clock64() - c0 < 200) {} }
-					for (int kk = 0; kk < nmma; kk++) umma_bf16_ts(tmem + sl * cols, tmem + 448 + 8 * (kk & 3), db + 2 * (kk & 3), idesc, kk != 0);
+					for (int kk = 0; kk < nmma; kk++) umma_f16_ts(tmem + sl * cols, tmem + 448 + 8 * (kk & 3), db + 2 * (kk & 3), idesc, kk != 0);
 					umma_commit(&bar->full[sl]);
 					if (which == 52 && n >= 3) { const int m = n - 3; mbar_wait(&bar->full[m & 3], (m >> 2) & 1); }
 				}
@@ -258,7 +258,7 @@ __global__ void __launch_bounds__(608, 1) micro_kernel(int which, int cols, int 
 					const int sl = n % D, u = n / D;
 					// mflags: 1 = no fence after the wait, 2 = no wait, 4 = no commit
 					if (u > 0 && !(mflags & 2)) { mbar_wait(relay ? &bar->empty[sl] : &bar->full[sl], (u - 1) & 1); if (!(mflags & 1)) tc_fence_after(); }
-					for (int kk = 0; kk < nmma; kk++) umma_bf16_ts(tmem + sl * cols, tmem + 448 + 8 * (kk & 3), db + 2 * (kk & 3), idesc, kk != 0);
+					for (int kk = 0; kk < nmma; kk++) umma_f16_ts(tmem + sl * cols, tmem + 448 + 8 * (kk & 3), db + 2 * (kk & 3), idesc, kk != 0);
 					if (!(mflags & 4)) umma_commit(&bar->full[sl]);
 				}
 				umma_commit(&bar->done[1]);

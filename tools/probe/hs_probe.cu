@@ -57,7 +57,7 @@ __global__ void __launch_bounds__(576, 1) hs_kernel(int slots, int cols, int dfm
 				if (!(flags & 1)) tc_fence_after();
 				const uint32_t d = tmem + (uint32_t)(slot * cols);
 #pragma unroll
-				for (int kk = 0; kk < 4; kk++) umma_bf16_ts(d, a_t + (uint32_t)((it & 1) * 32) + 8 * kk, db + 2 * kk, idesc, kk != 0);
+				for (int kk = 0; kk < 4; kk++) umma_f16_ts(d, a_t + (uint32_t)((it & 1) * 32) + 8 * kk, db + 2 * kk, idesc, kk != 0);
 				if (!(flags & 8)) umma_commit(&bar->full[slot]);
 			}
 			umma_commit(&bar->done);
@@ -139,7 +139,7 @@ __global__ void __launch_bounds__(128, 1) f16_check_kernel(const uint16_t* A, co
 	if (threadIdx.x == 0) {
 		const uint32_t idesc = idesc_of(128, 128, 0, abfmt);
 		const uint64_t db = umma_desc_sw128(smem_u32(sB));
-		for (int kk = 0; kk < 4; kk++) umma_bf16_ts(tmem, tmem + 480 + 8 * kk, db + 2 * kk, idesc, kk != 0);
+		for (int kk = 0; kk < 4; kk++) umma_f16_ts(tmem, tmem + 480 + 8 * kk, db + 2 * kk, idesc, kk != 0);
 		umma_commit(&bar->done);
 	}
 	mbar_wait(&bar->done, 0);

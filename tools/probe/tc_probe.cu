@@ -46,7 +46,7 @@ __global__ void __launch_bounds__(320, 1) rate_kernel(int mma, int N, int chains
 #pragma unroll
 					for (int kk = 0; kk < 4; kk++) {
 						if (mma == 1) umma_bf16(d, da + 2 * kk, db + 2 * kk, idesc, kk != 0);
-						else umma_bf16_ts(d, a_t + 8 * kk, db + 2 * kk, idesc, kk != 0);
+						else umma_f16_ts(d, a_t + 8 * kk, db + 2 * kk, idesc, kk != 0);
 					}
 				} else {
 #pragma unroll
@@ -54,7 +54,7 @@ __global__ void __launch_bounds__(320, 1) rate_kernel(int mma, int N, int chains
 						for (int c = 0; c < 2; c++) {       // two iterations' worth of MMAs per loop trip
 							const uint32_t d = tmem + (uint32_t)(c * N);
 							if (mma == 1) umma_bf16(d, da + 2 * kk, db + 2 * kk, idesc, kk != 0);
-							else umma_bf16_ts(d, a_t + 8 * kk, db + 2 * kk, idesc, kk != 0);
+							else umma_f16_ts(d, a_t + 8 * kk, db + 2 * kk, idesc, kk != 0);
 						}
 					it++;
 				}
@@ -122,7 +122,7 @@ __global__ void __launch_bounds__(128, 1) ts_check_kernel(const __nv_bfloat16* A
 	if (threadIdx.x == 0) {
 		const uint32_t idesc = umma_idesc_bf16(128, 128);
 		const uint64_t db = umma_desc_sw128(smem_u32(sB));
-		for (int kk = 0; kk < 4; kk++) umma_bf16_ts(tmem, tmem + 480 + 8 * kk, db + 2 * kk, idesc, kk != 0);
+		for (int kk = 0; kk < 4; kk++) umma_f16_ts(tmem, tmem + 480 + 8 * kk, db + 2 * kk, idesc, kk != 0);
 		umma_commit(&bar->done);
 	}
 	mbar_wait(&bar->done, 0);
