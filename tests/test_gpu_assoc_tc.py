@@ -61,7 +61,8 @@ def test_filter_estimate_stays_inside_its_error_budget(bs):
         g.close()
 
 
-@pytest.mark.parametrize("n,m,backwards", [(300, 517, True), (1000, 777, False), (2048, 2304, True), (129, 4100, True)])
+@pytest.mark.parametrize("n,m,backwards", [(300, 517, True), (1000, 777, False), (2048, 2304, True), (129, 4100, True),
+                                            (600, 100, True), (600, 224, False), (70, 112, True), (1, 113, True)])   # one / two column tiles per row block
 def test_mode1_bit_exact_vs_exact_kernel_and_oracle(bs, orc, n, m, backwards):
     rng = np.random.default_rng(n + m)
     dst = _unit(rng, m); src = _unit(rng, n)
