@@ -111,9 +111,10 @@ template <> struct AccOf<float> { typedef float type; };
 // not run the reference's serial order: the image is cut into bands of SCAN_ROWS rows, a CTA scans a band row by row —
 // every thread owns V consecutive columns: local scan, warp scan of the thread totals by shuffles, warp totals through shared
 // memory — and keeps the running column sums of its columns in registers.
-//   pass A: column sums of each band's row-scanned values -> partial[frame][band][W]           (reads the input once)
+//   pass A: each band's contribution to the rows below it = prefix over x of the band's column sums -> partial[frame][band][W]
+//           (the rows are only added up: no scan, no barrier per row; reads the input once)
 //   pass B: exclusive scan of the partials over the bands of a frame (tiny: 1 / SCAN_ROWS of the image)
-//   pass C: the band scan again, starting from the band's prefix, writes the integral           (input again + output)
+//   pass C: the band scan, four rows per step, starting from the band's prefix, writes the integral   (input again + output)
 // Traffic per pixel: 2 x input + 4 bytes out (+ 1/16 for the partials) against 16 bytes for the two serial passes above;
 // the second read goes to DRAM again (launches that would keep it in L2 are too small to fill the GPU).
 // Float images do NOT take this path: the same kernels instantiated for float ran at 6.25 vs 7.05 us per 1080p frame, but another
@@ -152,74 +153,205 @@ __device__ __forceinline__ void scan_load_row(const TI* __restrict__ row, int W,
 	for (int i = 0; i < V; i++) v[i] = x0 + i < W ? (ACC)__ldg(row + x0 + i) : (ACC)0;
 }
 
-// WRITE = false: pass A (partial[band] = column sums of the band's row scans); true: pass C (out = prefix + running sums)
-template <typename TI, typename TO, typename ACC, int V, bool WRITE>
+// eight GrayU8 pixels as two words: one 8-byte load where the address allows it, byte loads (zero beyond W) otherwise; unpack8 widens them
+__device__ __forceinline__ uint2 fetch8(const uint8_t* __restrict__ row, int W, int x0) {
+	if (x0 + 8 <= W && (reinterpret_cast<uintptr_t>(row + x0) & 7) == 0) return __ldg(reinterpret_cast<const uint2*>(row + x0));
+	uint2 q = make_uint2(0u, 0u);
+#pragma unroll
+	for (int k = 0; k < 4; k++) {
+		if (x0 + k < W) q.x |= (uint32_t)__ldg(row + x0 + k) << (8 * k);
+		if (x0 + 4 + k < W) q.y |= (uint32_t)__ldg(row + x0 + 4 + k) << (8 * k);
+	}
+	return q;
+}
+template <typename ACC>
+__device__ __forceinline__ void unpack8(uint2 q, ACC (&v)[8]) {
+#pragma unroll
+	for (int k = 0; k < 4; k++) { v[k] = (ACC)((q.x >> (8 * k)) & 0xffu); v[4 + k] = (ACC)((q.y >> (8 * k)) & 0xffu); }
+}
+
+// CTA-wide inclusive scan of the thread totals t (thread = V consecutive columns): returns the exclusive prefix of this thread.
+// `tot` = one row of shared memory of SCAN_THREADS / 32 words per concurrent scan; the caller separates uses by __syncthreads.
+template <typename ACC>
+__device__ __forceinline__ ACC scan_warp_inclusive(ACC t, int lane) {
+#pragma unroll
+	for (int d = 1; d < 32; d <<= 1) {
+		const ACC o = __shfl_up_sync(0xffffffffu, t, d);
+		if (lane >= d) t = (ACC)(t + o);
+	}
+	return t;
+}
+
+// pass A: partial[frame][band][x] = sum over the band's rows y of the row prefix sum_{x' <= x} in[y][x'] — which is the prefix over x
+// of the band's plain COLUMN sums: the rows are only added up (independent loads, no barrier), one scan across x per band.
+template <typename TI, typename ACC, int V>
 __global__ void __launch_bounds__(SCAN_THREADS)
-integral_scan_kernel(const TI* __restrict__ in, long in_frame_stride, int in_stride, TO* __restrict__ out, ACC* __restrict__ partial, int W, int H,
-                     int bands) {
-	__shared__ ACC warp_tot[2][SCAN_THREADS / 32];
+integral_band_sums_kernel(const TI* __restrict__ in, long in_frame_stride, int in_stride, ACC* __restrict__ partial, int W, int H, int bands) {
+	__shared__ ACC warp_tot[SCAN_THREADS / 32];
 	const int band = blockIdx.x, frame = blockIdx.y;
 	const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 	const int x0 = threadIdx.x * V;
 	const int y0 = band * SCAN_ROWS, y1 = min(H, y0 + SCAN_ROWS);
 	const TI* src = in + (long)frame * in_frame_stride;
-	ACC* part = partial + ((long)frame * bands + band) * W;
-	ACC col[V];
+	ACC sum[V];
 #pragma unroll
-	for (int i = 0; i < V; i++) col[i] = WRITE && x0 + i < W ? part[x0 + i] : (ACC)0;
-	ACC cur[V], nxt[V];
-	scan_load_row<TI, ACC, V>(src + (long)y0 * in_stride, W, x0, cur);
-	for (int y = y0; y < y1; y++) {
-		if (y + 1 < y1) scan_load_row<TI, ACC, V>(src + (long)(y + 1) * in_stride, W, x0, nxt);
-		// inclusive scan of the thread's V pixels, then of the thread totals across the warp
+	for (int i = 0; i < V; i++) sum[i] = (ACC)0;
+	int y = y0;
+	if constexpr (sizeof(TI) == 1 && V == 8) {
+		// bytes: sixteen rows in flight as raw words (two registers per row), widened only when they are added
+		for (; y + 16 <= y1; y += 16) {
+			uint2 q[16];
 #pragma unroll
-		for (int i = 1; i < V; i++) cur[i] = (ACC)(cur[i] + cur[i - 1]);
-		ACC t = cur[V - 1];
+			for (int k = 0; k < 16; k++) q[k] = fetch8(reinterpret_cast<const uint8_t*>(src) + (long)(y + k) * in_stride, W, x0);
 #pragma unroll
-		for (int d = 1; d < 32; d <<= 1) {
-			const ACC o = __shfl_up_sync(0xffffffffu, t, d);
-			if (lane >= d) t = (ACC)(t + o);
-		}
-		const int b = (y - y0) & 1;
-		if (lane == 31) warp_tot[b][warp] = t;
-		__syncthreads();                               // one barrier per row: the totals alternate between two buffers
-		ACC base = (ACC)(t - cur[V - 1]);              // exclusive prefix inside the warp
+			for (int k = 0; k < 16; k++) {
+				ACC r[8];
+				unpack8<ACC>(q[k], r);
 #pragma unroll
-		for (int w = 0; w < SCAN_THREADS / 32; w++) if (w < warp) base = (ACC)(base + warp_tot[b][w]);
-#pragma unroll
-		for (int i = 0; i < V; i++) col[i] = (ACC)(col[i] + (ACC)(cur[i] + base));
-		if (WRITE) {
-			TO* dst = out + ((long)frame * H + y) * W + x0;
-			if (x0 + V <= W && V % 4 == 0 && (reinterpret_cast<uintptr_t>(dst) & 15) == 0) {
-#pragma unroll
-				for (int i = 0; i < V; i += 4) {
-					*reinterpret_cast<int4*>(dst + i) = make_int4(word_of((TO)col[i]), word_of((TO)col[i + 1]), word_of((TO)col[i + 2]), word_of((TO)col[i + 3]));
-				}
-			} else {
-#pragma unroll
-				for (int i = 0; i < V; i++) if (x0 + i < W) dst[i] = (TO)col[i];
+				for (int i = 0; i < 8; i++) sum[i] = (ACC)(sum[i] + r[i]);
 			}
 		}
-#pragma unroll
-		for (int i = 0; i < V; i++) cur[i] = nxt[i];
 	}
-	if (!WRITE) {
+	constexpr int RF = V <= 8 ? 4 : (V <= 16 ? 2 : 1);      // rows in flight (registers)
+	for (; y + RF <= y1; y += RF) {
+		ACC r[RF][V];
 #pragma unroll
-		for (int i = 0; i < V; i++) if (x0 + i < W) part[x0 + i] = col[i];
+		for (int k = 0; k < RF; k++) scan_load_row<TI, ACC, V>(src + (long)(y + k) * in_stride, W, x0, r[k]);
+#pragma unroll
+		for (int k = 0; k < RF; k++)
+#pragma unroll
+			for (int i = 0; i < V; i++) sum[i] = (ACC)(sum[i] + r[k][i]);
+	}
+	for (; y < y1; y++) {
+		ACC r0[V];
+		scan_load_row<TI, ACC, V>(src + (long)y * in_stride, W, x0, r0);
+#pragma unroll
+		for (int i = 0; i < V; i++) sum[i] = (ACC)(sum[i] + r0[i]);
+	}
+#pragma unroll
+	for (int i = 1; i < V; i++) sum[i] = (ACC)(sum[i] + sum[i - 1]);
+	const ACC t = scan_warp_inclusive<ACC>(sum[V - 1], lane);
+	if (lane == 31) warp_tot[warp] = t;
+	__syncthreads();
+	ACC base = (ACC)(t - sum[V - 1]);
+#pragma unroll
+	for (int w = 0; w < SCAN_THREADS / 32; w++) if (w < warp) base = (ACC)(base + warp_tot[w]);
+	ACC* part = partial + ((long)frame * bands + band) * W;
+#pragma unroll
+	for (int i = 0; i < V; i++) if (x0 + i < W) part[x0 + i] = (ACC)(sum[i] + base);
+}
+
+// pass C: out = the band's prefix (pass B) + running sums of the row scans, R rows per step: R independent scans share one barrier
+// and interleave their shuffles (one row per step left the CTA waiting on a 5-shuffle chain and a barrier per row).
+template <typename TI, typename TO, typename ACC, int V, int R>
+__global__ void __launch_bounds__(SCAN_THREADS)
+integral_scan_kernel(const TI* __restrict__ in, long in_frame_stride, int in_stride, TO* __restrict__ out, const ACC* __restrict__ partial, int W, int H,
+                     int bands) {
+	__shared__ ACC warp_tot[2][R][SCAN_THREADS / 32];
+	const int band = blockIdx.x, frame = blockIdx.y;
+	const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+	const int x0 = threadIdx.x * V;
+	const int y0 = band * SCAN_ROWS, y1 = min(H, y0 + SCAN_ROWS);
+	const TI* src = in + (long)frame * in_frame_stride;
+	const ACC* part = partial + ((long)frame * bands + band) * W;
+	ACC col[V];
+#pragma unroll
+	for (int i = 0; i < V; i++) col[i] = x0 + i < W ? part[x0 + i] : (ACC)0;
+	int step = 0;
+	constexpr bool BYTES = sizeof(TI) == 1 && V == 8;    // bytes: the next step's rows are fetched as raw words (two registers per row) before this step's scan
+	uint2 nq[BYTES ? R : 1];
+	if constexpr (BYTES) {
+#pragma unroll
+		for (int r = 0; r < R; r++) nq[r] = y0 + r < y1 ? fetch8(reinterpret_cast<const uint8_t*>(src) + (long)(y0 + r) * in_stride, W, x0) : make_uint2(0u, 0u);
+	}
+	for (int y = y0; y < y1; y += R, step++) {
+		ACC cur[R][V];
+		if constexpr (BYTES) {
+			uint2 cq[R];
+#pragma unroll
+			for (int r = 0; r < R; r++) cq[r] = nq[r];
+#pragma unroll
+			for (int r = 0; r < R; r++)
+				nq[r] = y + R + r < y1 ? fetch8(reinterpret_cast<const uint8_t*>(src) + (long)(y + R + r) * in_stride, W, x0) : make_uint2(0u, 0u);
+#pragma unroll
+			for (int r = 0; r < R; r++) {
+				ACC w8[8];
+				unpack8<ACC>(cq[r], w8);
+#pragma unroll
+				for (int i = 0; i < V; i++) cur[r][i] = w8[i < 8 ? i : 0];
+			}
+		} else {
+#pragma unroll
+			for (int r = 0; r < R; r++) {
+				if (y + r < y1) scan_load_row<TI, ACC, V>(src + (long)(y + r) * in_stride, W, x0, cur[r]);
+				else {
+#pragma unroll
+					for (int i = 0; i < V; i++) cur[r][i] = (ACC)0;
+				}
+			}
+		}
+		ACC t[R];
+#pragma unroll
+		for (int r = 0; r < R; r++) {
+#pragma unroll
+			for (int i = 1; i < V; i++) cur[r][i] = (ACC)(cur[r][i] + cur[r][i - 1]);
+			t[r] = cur[r][V - 1];
+		}
+#pragma unroll
+		for (int d = 1; d < 32; d <<= 1) {
+#pragma unroll
+			for (int r = 0; r < R; r++) {
+				const ACC o = __shfl_up_sync(0xffffffffu, t[r], d);
+				if (lane >= d) t[r] = (ACC)(t[r] + o);
+			}
+		}
+		const int b = step & 1;
+		if (lane == 31) {
+#pragma unroll
+			for (int r = 0; r < R; r++) warp_tot[b][r][warp] = t[r];
+		}
+		__syncthreads();                               // one barrier per R rows: the totals alternate between two buffers
+#pragma unroll
+		for (int r = 0; r < R; r++) {
+			ACC base = (ACC)(t[r] - cur[r][V - 1]);        // exclusive prefix inside the warp
+#pragma unroll
+			for (int w = 0; w < SCAN_THREADS / 32; w++) if (w < warp) base = (ACC)(base + warp_tot[b][r][w]);
+#pragma unroll
+			for (int i = 0; i < V; i++) col[i] = (ACC)(col[i] + (ACC)(cur[r][i] + base));
+			if (y + r < y1) {
+				TO* dst = out + ((long)frame * H + (y + r)) * W + x0;
+				if (x0 + V <= W && V % 4 == 0 && (reinterpret_cast<uintptr_t>(dst) & 15) == 0) {
+#pragma unroll
+					for (int i = 0; i < V; i += 4) {
+						*reinterpret_cast<int4*>(dst + i) = make_int4(word_of((TO)col[i]), word_of((TO)col[i + 1]), word_of((TO)col[i + 2]), word_of((TO)col[i + 3]));
+					}
+				} else {
+#pragma unroll
+					for (int i = 0; i < V; i++) if (x0 + i < W) dst[i] = (TO)col[i];
+				}
+			}
+		}
 	}
 }
 
-// pass B: partial[frame][band][x] -> exclusive prefix over the bands (thread = column)
+// pass B: partial[frame][band][x] -> exclusive prefix over the bands (thread = column).  The loads of a column do not depend on each
+// other: sixteen are issued before the first store (as a read-modify-write loop the compiler could not hoist them over the stores, and
+// 34 dependent L2 round trips made this tiny pass as long as pass A: 60 us per 32 frames of 1080p).
 template <typename ACC>
 __global__ void integral_scan_bands_kernel(ACC* __restrict__ partial, int W, int bands) {
 	const int x = blockIdx.x * blockDim.x + threadIdx.x;
 	if (x >= W) return;
 	ACC* p = partial + (long)blockIdx.y * bands * W + x;
 	ACC run = 0;
-	for (int b = 0; b < bands; b++) {
-		const ACC v = p[(long)b * W];
-		p[(long)b * W] = run;
-		run = (ACC)(run + v);
+	for (int b0 = 0; b0 < bands; b0 += 16) {
+		ACC v[16];
+#pragma unroll
+		for (int k = 0; k < 16; k++) v[k] = b0 + k < bands ? p[(long)(b0 + k) * W] : (ACC)0;
+#pragma unroll
+		for (int k = 0; k < 16; k++) {
+			if (b0 + k < bands) p[(long)(b0 + k) * W] = run;
+			run = (ACC)(run + v[k]);
+		}
 	}
 }
 
@@ -242,17 +374,17 @@ bool launch_integral_scan(const TI* d_in, long in_frame_stride, int in_stride, T
 		TO* out = d_out + (long)f0 * W * H;
 		ACC* pp = part + (long)f0 * bands * W;
 		dim3 g(bands, n);
-		auto go = [&](auto vtag) {
-			constexpr int V = decltype(vtag)::value;
-			BS_LAUNCH((integral_scan_kernel<TI, TO, ACC, V, false>), g, SCAN_THREADS, 0, st, in, in_frame_stride, in_stride, out, pp, W, H, bands);
-			BS_LAUNCH((integral_scan_bands_kernel<ACC>), dim3(div_up(W, 128), n), 128, 0, st, pp, W, bands);
-			BS_LAUNCH((integral_scan_kernel<TI, TO, ACC, V, true>), g, SCAN_THREADS, 0, st, in, in_frame_stride, in_stride, out, pp, W, H, bands);
+		auto go = [&](auto vtag, auto rtag) {
+			constexpr int V = decltype(vtag)::value, R = decltype(rtag)::value;
+			BS_LAUNCH((integral_band_sums_kernel<TI, ACC, V>), g, SCAN_THREADS, 0, st, in, in_frame_stride, in_stride, pp, W, H, bands);
+			BS_LAUNCH((integral_scan_bands_kernel<ACC>), dim3(div_up(W, 64), n), 64, 0, st, pp, W, bands);
+			BS_LAUNCH((integral_scan_kernel<TI, TO, ACC, V, R>), g, SCAN_THREADS, 0, st, in, in_frame_stride, in_stride, out, pp, W, H, bands);
 		};
 		const int per = div_up(W, SCAN_THREADS);
-		if (per <= 4) go(std::integral_constant<int, 4>());
-		else if (per <= 8) go(std::integral_constant<int, 8>());
-		else if (per <= 16) go(std::integral_constant<int, 16>());
-		else go(std::integral_constant<int, 32>());
+		if (per <= 4) go(std::integral_constant<int, 4>(), std::integral_constant<int, 4>());
+		else if (per <= 8) go(std::integral_constant<int, 8>(), std::integral_constant<int, 4>());
+		else if (per <= 16) go(std::integral_constant<int, 16>(), std::integral_constant<int, 2>());
+		else go(std::integral_constant<int, 32>(), std::integral_constant<int, 1>());
 	}
 	return true;
 }
