@@ -156,6 +156,19 @@ constexpr int TC_PEND = 8;                // candidates an epilogue thread colle
 constexpr int TC_SMEM_BYTES = 1024 /*alignment slack*/ + TC_STAGES * TC_TILE_BYTES + TC_STAGES * TC_NB * 4 + (int)sizeof(FilterBarriers) +
                               2 * TC_PEND * 32 * TC_EPI_WARPS * 4 + TC_MROWS * 2 * 8;
 
+#ifdef BS_TC_TRACE
+// timing experiment (tools/trace_filter.py; build this file with -DBS_TC_TRACE): clock64 stamps of the hand-off events of tiles
+// [TR_N0, TR_N0 + 32) of CTA 0.  Result of round 2 (profiles/r2d_filter_trace.txt): a tile takes ~800 cycles per A half; the thread that
+// issues the MMAs needs ~360 cycles from the first MMA to the commit (its two barrier probes sit in there), the epilogue group sees the
+// commit ~300 cycles later, reads the accumulator in ~135 and releases the slot 25 later — ~830 cycles after the tile's first MMA, long
+// before the issuer comes back to that slot (~1600): the slots are not what it waits for, its own per-tile instruction stream is.
+constexpr int TR_N0 = 200;
+__device__ long long g_tc_trace[32 * 2 * 8];
+#define BS_TR(nn, hh, k) do { if (blockIdx.x == 0 && (nn) >= TR_N0 && (nn) < TR_N0 + 32) g_tc_trace[(((nn) - TR_N0) * 2 + (hh)) * 8 + (k)] = clock64(); } while (0)
+#else
+#define BS_TR(nn, hh, k) do { } while (0)
+#endif
+
 template <bool DBG>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 filter_kernel(const __grid_constant__ CUtensorMap tmB, FilterArgs P) {
@@ -234,6 +247,7 @@ filter_kernel(const __grid_constant__ CUtensorMap tmB, FilterArgs P) {
 			for (int n = 0; n < n_tiles; n++) {
 				const uint32_t par = (uint32_t)n & 1u;
 				const uint32_t d = d0 + par * TC_BN;
+				BS_TR(n, h, 0);
 				umma_f16_ts(d, a, db, idesc, 0u);
 				// tile n + 1: stage, descriptor, row block
 				const bool more = n + 1 < n_tiles;
@@ -253,7 +267,12 @@ filter_kernel(const __grid_constant__ CUtensorMap tmB, FilterArgs P) {
 				const bool got = need && mbar_try_wait(e_addr, e_par);
 				umma_f16_ts(d, a + 24, db + 6, idesc, 1u);
 				asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(full0 + 8u * par) : "memory");
+				BS_TR(n, h, 1);
 				if (need && !got) mbar_wait_addr(e_addr, e_par);
+				BS_TR(n, h, 2);
+#ifdef BS_TC_TRACE
+				if (blockIdx.x == 0 && n >= TR_N0 && n < TR_N0 + 32) g_tc_trace[((n - TR_N0) * 2 + h) * 8 + 6] = got ? 1 : 0;
+#endif
 				if (more) {
 					if (t1 == 0) {                                       // next row block: its A is written once the MMAs above have completed
 						mbar_wait(&bar->a_full, seg & 1);
@@ -350,6 +369,7 @@ filter_kernel(const __grid_constant__ CUtensorMap tmB, FilterArgs P) {
 			}
 			mbar_wait_addr(bfull_addr + 8u * st, sph);               // the stage's norms have landed (long since: the MMAs needed its tile)
 			mbar_wait_addr(accfull_addr, k & 1u);
+			if (q == 0 && lane == 0) BS_TR(n, h, 3);
 			tc_fence_after();
 			// The whole accumulator row in one round: 112 fp16 values, two per register (tcgen05.ld .pack::16b), and the slot goes back to the
 			// MMA issuer before any arithmetic.
@@ -358,9 +378,11 @@ filter_kernel(const __grid_constant__ CUtensorMap tmB, FilterArgs P) {
 			uint32_t r0[32], r1[16], r2[8];                              // columns [0, 64), [64, 96), [96, 112)
 			tmem_ld64p_issue(tbase, r0); tmem_ld32p_issue(tbase + 64, r1); tmem_ld16p_issue(tbase + 96, r2);
 			tmem_ld_wait(r0); tmem_ld_wait(r1); tmem_ld_wait(r2);
+			if (q == 0 && lane == 0) BS_TR(n, h, 4);
 			tc_fence_before();
 			__syncwarp();
 			if (lane == 0) mbar_arrive_addr(accempty_addr);
+			if (q == 0 && lane == 0) BS_TR(n, h, 5);
 			const uint32_t nb_addr = snb_addr + (uint32_t)(TC_NB * 4) * st;     // the tile's record: 112 norms, flag, 112 scales
 			// Candidate path of one 32-column chunk (16 registers; the last chunk of a tile has 16 columns) whose best column came within tol
 			// of the row's running minimum (per row ~1.3 / columns-seen per column; a 32-lane warp takes it whenever ONE of its rows does).
@@ -678,3 +700,6 @@ void launch_tc_rescore(const double* d_A, int nA, const double* d_B, const int* 
 }
 
 }  // namespace bs
+#ifdef BS_TC_TRACE
+extern "C" int bs_debug_tc_trace(long long* out) { return (int)cudaMemcpyFromSymbol(out, bs::g_tc_trace, sizeof(bs::g_tc_trace)); }
+#endif

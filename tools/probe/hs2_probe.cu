@@ -169,6 +169,7 @@ __global__ void __launch_bounds__(736, 1) hs2_kernel(int cols, int iters, long l
 // micro 2: two warps ping-pong through two mbarriers (arrive / try_wait) -> two signal hops per iteration
 // `pollers` other warps spin on a barrier that never completes (until the end), as the waiting epilogue warps of the filter do
 __global__ void __launch_bounds__(608, 1) micro_kernel(int which, int cols, int nmma, int iters, int pollers, long long* cycles, int mflags = 0) {
+	// mflags & 16: F16 inputs and an F16 accumulator (all format fields of the instruction descriptor 0) instead of BF16 inputs / F32 accumulator
 	extern __shared__ unsigned char raw[];
 	unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(raw) + 1023) & ~(uintptr_t)1023);
 	unsigned char* sB = smem;
@@ -251,7 +252,7 @@ __global__ void __launch_bounds__(608, 1) micro_kernel(int which, int cols, int 
 			const int relay = which >= 40;
 			const int D = which - (relay ? 40 : 30);
 			if (elect_one()) {
-				const uint32_t idesc = idesc_of(128, cols);
+				const uint32_t idesc = (mflags & 16) ? (((uint32_t)(cols >> 3) << 17) | (8u << 24)) : idesc_of(128, cols);
 				const uint64_t db = umma_desc_sw128(smem_u32(sB));
 				const long long t0 = clock64();
 				for (int n = 0; n < iters; n++) {
@@ -382,6 +383,9 @@ int main() {
 	    {62, 112, 1, 0, "shared-memory counter, depth 2, ONE MMA"}, {62, 112, 4, 12, "shared-memory counter, depth 2, 12 warps polling"},
 	    {51, 112, 4, 0, "no wait, 200-cycle clock spin per group"}, {52, 112, 4, 0, "MMAs + commit, then wait for the commit of 3 groups ago"},
 	    {52, 112, 1, 0, "ONE MMA + commit, then wait for the commit of 3 groups ago"},
+	    {34, 112, 4, 0, "free-running groups of four 128x112x16 MMAs, BF16 in / F32 accumulator", 2}, {34, 112, 4, 0, "free-running groups of four 128x112x16 MMAs, F16 in / F16 accumulator", 2 + 16},
+	    {34, 128, 4, 0, "free-running groups of four 128x128x16 MMAs (timing only), BF16 / F32", 2}, {34, 64, 4, 0, "free-running groups of four 128x64x16 MMAs, BF16 / F32", 2},
+	    {34, 112, 1, 0, "free-running single 128x112x16 MMAs into four accumulators in turn, BF16 / F32", 2}, {34, 112, 1, 0, "the same, F16 / F16", 2 + 16},
 	    {31, 112, 4, 0, "self-paced, depth 1"}, {32, 112, 4, 0, "self-paced, depth 2"}, {33, 112, 4, 0, "self-paced, depth 3"}, {34, 112, 4, 0, "self-paced, depth 4"},
 	    {41, 112, 4, 0, "relayed by one warp, depth 1"}, {42, 112, 4, 0, "relayed by one warp, depth 2"}, {43, 112, 4, 0, "relayed, depth 3"}, {44, 112, 4, 0, "relayed, depth 4"},
 	    {42, 112, 4, 12, "relayed, depth 2, 12 warps polling"}, {42, 32, 1, 0, "relayed, depth 2, one 128x32x16 MMA"},
