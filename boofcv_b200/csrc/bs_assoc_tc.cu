@@ -23,8 +23,8 @@
 // Shape: the 256 rows of a row block live in TMEM as the A operand (written there by the epilogue threads with tcgen05.st: 73 cycles per
 // UMMA against 97 with A in shared memory, tools/probe/tc_probe.cu), B tiles stream through an 8-stage TMA ring together with their records
 // (norms, flag, scales), four 112-column accumulators: slot = 2 * (A half) + (tile parity).
-// Roles inside the CTA (608 threads): warp 0 = TMA producer, warps 1 and 18 = MMA issuers (one elected thread each, one per A half), warps
-// 2-17 = epilogue in four groups of four warps (a group covers the four TMEM lane quarters): group (A half, tile parity) owns one slot and
+// Roles inside the CTA (608 threads): warp 0 = TMA producer, warps 1 and 2 = MMA issuers (one elected thread each, one per A half), warps
+// 3-18 = epilogue in four groups of four warps (a group covers the four TMEM lane quarters): group (A half, tile parity) owns one slot and
 // takes every other tile of its half — one TMEM lane = one row per thread, two threads per row (they exchange their running minima through
 // shared memory).  The work of a launch is the sequence of (row block, B tile) pairs in row-block-major order, cut into one contiguous
 // range per CTA.
@@ -53,7 +53,8 @@ constexpr int TC_SC = TC_BN + 4;           // float offset of the scales inside 
 constexpr int TC_SLOTS = 4;                // accumulators in flight: slot = 2 * (A half) + (tile parity)
 constexpr int TC_A_COL = TC_SLOTS * TC_BN; // TMEM columns [448, 512): the two A halves, 32 columns each
 constexpr int TC_EPI_WARPS = 16;           // four groups: (A half) x (tile parity), each the only reader of one slot
-constexpr int TC_ISSUER2 = 2 + TC_EPI_WARPS;  // warp index of the second MMA issuer (after the epilogue warps)
+constexpr int TC_ISSUER2 = 2;                 // warp index of the second MMA issuer.  The role warps take the LOWEST warp indices: with them at the
+                                              // highest (producer 16, issuers 17 / 18) the kernel was 10 % slower (2.72 against 2.45 ms per 100k x 100k)
 constexpr int TC_THREADS = 96 + 32 * TC_EPI_WARPS;
 constexpr int TC_CAND_CAP = 128;           // candidates kept per row; more -> the caller falls back to the exact kernel.  Real SURF
                                            // descriptors of a 1080p frame (10k x 10k, ~8 running-minimum chains per row: 4 CTAs x 2
@@ -218,7 +219,7 @@ filter_kernel(const __grid_constant__ CUtensorMap tmB, FilterArgs P) {
 			}
 		}
 	} else if (warp == 1 || warp == TC_ISSUER2) {
-		// ===== MMA issuers: warp 1 takes A half 0, warp 18 A half 1 (one elected thread each), two accumulator slots per half.  An accumulator is four MMAs
+		// ===== MMA issuers: warp 1 takes A half 0, warp 2 A half 1 (one elected thread each), two accumulator slots per half.  An accumulator is four MMAs
 		// (K = 64) between a wait and a commit: one thread's instruction stream for both halves (~45 dependent instructions per
 		// accumulator, sharing its scheduler with four epilogue warps) took longer than the MMAs themselves (measured with
 		// tools/probe/hs_probe.cu: 513 cycles per accumulator whatever the number of slots, 292 without the hand-off). =====
@@ -284,14 +285,14 @@ filter_kernel(const __grid_constant__ CUtensorMap tmB, FilterArgs P) {
 			}
 		}
 	} else {
-		// ===== epilogue: warps 2..17.  TMEM lane quarter = warp % 4 (hardware rule); group = (warp - 2) / 4 = (A half, tile parity):
+		// ===== epilogue: warps 3..18.  TMEM lane quarter = warp % 4 (hardware rule); group = (warp - 3) / 4 = (A half, tile parity):
 		// a group takes every OTHER tile of its half, reads the whole accumulator row in one round and hands the slot back before
 		// any arithmetic. =====
 		const int q = warp & 3;
-		const int g = (warp - 2) >> 2;
+		const int g = (warp - 3) >> 2;
 		const int h = g >> 1;                                        // A half (rows h*128 .. h*128+127 of the row block)
 		const int par = g & 1;                                       // tiles n = par, par + 2, ...
-		const int e = (warp - 2) * 32 + lane;                        // 0..511 among the epilogue threads
+		const int e = (warp - 3) * 32 + lane;                        // 0..511 among the epilogue threads
 		const int L = q * 32 + lane;                                 // TMEM lane = row inside the 128-row half
 		const uint32_t lane_base = tmem + ((uint32_t)(q * 32) << 16);
 		const uint32_t run_mine = smem_u32(s_run + (h * TC_BM + L) * 2 + par), run_other = smem_u32(s_run + (h * TC_BM + L) * 2 + (par ^ 1));
