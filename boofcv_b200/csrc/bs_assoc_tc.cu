@@ -84,11 +84,15 @@ __global__ void split_kernel(const double* __restrict__ x, int n, int n_pad, int
 	const float sqf = (float)sq;
 	if (sqf > 0.0f && sqf < INFINITY) e = ilogbf(sqf) >> 1;              // floor(log4 |x|^2) of the ROUNDED norm: rows with equal float norms get equal
 	                                                                     // scales (the fast path relies on it); the shift of a negative int is arithmetic
-	e = max(-60, min(60, e));                                            // 2^e stays a normal float; rows beyond that range end in the exact kernel anyway
+	// Norms beyond 1e-15 .. 1e15 (squared: 1e-30 .. 1e30) are outside what the estimate's error bound covers (the product of two scales must
+	// stay a normal float, a scaled row must stay in fp16's range): such a row is given the norm +inf, which makes tol infinite, every column a
+	// candidate of every row, the lists overflow and the caller redoes the whole problem with the exact kernel.  All-zero rows are exact.
+	const bool covered = sqf == 0.0f || (sqf >= 1e-30f && sqf <= 1e30f);
+	e = max(-60, min(60, e));
 	if (row < n_pad) reinterpret_cast<__half2*>(out + (size_t)row * TC_K)[lane] = __halves2half2(__double2half(scalbn(v.x, -e)), __double2half(scalbn(v.y, -e)));
 	if (lane == 0) {
 		const size_t i = norm_index(row);
-		norm[i] = row < n ? (float)sq : INFINITY;
+		norm[i] = row < n && covered ? sqf : INFINITY;
 		norm[i + TC_SC] = -2.0f * scalbnf(1.0f, e);
 	}
 }

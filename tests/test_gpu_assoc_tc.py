@@ -101,6 +101,23 @@ def test_mode1_rows_of_mixed_magnitude(bs, orc):
         tc.close(); ex.close()
 
 
+def test_mode1_norms_outside_the_filter_range_fall_back(bs, orc):
+    # rows of norm 1e-20 and 1e+20 (squared norms beyond 1e-30 .. 1e30): outside what the fp16 operands and the float scales cover ->
+    # the whole problem is redone with the exact kernel, results unchanged
+    rng = np.random.default_rng(21)
+    for scale in (1e-20, 1e20):
+        dst = _unit(rng, 400); src = _unit(rng, 300)
+        src[:100] = dst[rng.permutation(400)[:100]] + 0.01 * rng.normal(size=(100, 64))
+        dst[7] *= scale; src[3] *= scale
+        tc = _greedy(bs, True)
+        tc.setSource(src); tc.setDestination(dst); tc.associate()
+        op, of = orc.associate(src, dst, np.finfo(np.float64).max, True)
+        assert np.array_equal(tc.getPairs(), op) and np.array_equal(tc.getFitQuality(), of), scale
+        _, _, (runs, fallbacks) = tc.filterScores(src[:1], dst[:1], want_scores=False)
+        assert fallbacks >= 1
+        tc.close()
+
+
 def test_mode1_near_ties_duplicates_and_threshold(bs, orc):
     # adversarial for a low-precision filter: destinations that differ by 1e-9 .. 1e-4 (far below fp16 resolution), exact
     # duplicates (tie -> later index forward, rejected backward), duplicate sources, and an inclusive threshold
